@@ -1,0 +1,231 @@
+/*
+ * b200_vllm.h -- C ABI of libb200vllm.so: the B200 (sm_100a) kernels behind nm-vllm's
+ * custom-op surface (vllm/_custom_ops.py -> torch.ops._C / _C_cache_ops).
+ *
+ * This is the drop-in boundary.  Every entry point takes a POD parameter block holding raw
+ * device pointers, sizes and element strides -- no torch types -- plus the CUDA stream to
+ * launch on (a cudaStream_t passed as void*).  Entry points return 0 on success or a
+ * negative B200_E* code; b200_last_error() returns the message for the calling thread.
+ * No entry point synchronises, allocates device memory, or reads device data on the host,
+ * so all of them are CUDA-graph capturable (reference: worker/model_runner.py:910-1060).
+ *
+ * Each function cites the reference interface it replaces (paths relative to the reference
+ * checkout).  The torch-library registration that binds these to the reference's op schemas
+ * is neural_magic_vllm_b200/csrc/torch_bindings.cpp (replaces csrc/torch_bindings.cpp).
+ */
+#ifndef B200_VLLM_H_
+#define B200_VLLM_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_VLLM_ABI_VERSION 1
+
+/* error codes */
+#define B200_OK 0
+#define B200_EINVAL (-1)   /* bad argument (shape / stride / alignment / enum) */
+#define B200_ENOTSUP (-2)  /* combination the reference also rejects (head size, block size...) */
+#define B200_ECUDA (-3)    /* CUDA runtime error at launch */
+
+/* element types of activations / outputs */
+typedef enum { B200_F16 = 0, B200_BF16 = 1, B200_F32 = 2 } b200_dtype;
+
+/* kv_cache_dtype string of the reference (csrc/quantization/fp8/nvidia/quant_utils.cuh:516-565):
+ * "auto" -> B200_KV_AUTO, "fp8" / "fp8_e4m3" -> B200_KV_FP8_E4M3, "fp8_e5m2" -> B200_KV_FP8_E5M2 */
+typedef enum { B200_KV_AUTO = 0, B200_KV_FP8_E4M3 = 1, B200_KV_FP8_E5M2 = 2 } b200_kv_dtype;
+
+/* quantized element types for the W8A8 GEMM */
+typedef enum { B200_Q_INT8 = 0, B200_Q_FP8_E4M3 = 1 } b200_qtype;
+
+int b200_abi_version(void);
+const char* b200_last_error(void);
+/* parses the reference's kv_cache_dtype string; returns a b200_kv_dtype or B200_EINVAL */
+int b200_parse_kv_cache_dtype(const char* s);
+
+/* ------------------------------------------------------------------------------------------
+ * Paged attention (decode).  Replaces paged_attention_v1 / paged_attention_v2
+ * (csrc/attention/attention_kernels.cu:805-826, 966-990; schemas csrc/torch_bindings.cpp:24-48).
+ *
+ * Layouts (elements of the cache type; x = 16 / sizeof(cache element)):
+ *   query        [num_seqs, num_heads, head_size], row stride q_stride (may exceed H*D)
+ *   key_cache    [num_blocks, num_kv_heads, head_size/x, block_size, x]
+ *   value_cache  [num_blocks, num_kv_heads, head_size, block_size]
+ *   block_tables [num_seqs, max_num_blocks_per_seq] int32,  seq_lens [num_seqs] int32
+ *   out          [num_seqs, num_heads, head_size] contiguous
+ *   v2 scratch (caller-owned): tmp_out [num_seqs, num_heads, max_num_partitions, head_size],
+ *                exp_sums / max_logits [num_seqs, num_heads, max_num_partitions] fp32,
+ *                max_num_partitions = ceil(max_seq_len / 512)
+ * ------------------------------------------------------------------------------------------ */
+#define B200_PARTITION_SIZE 512
+
+typedef struct {
+  void* out;
+  const void* query;
+  const void* key_cache;
+  const void* value_cache;
+  const int32_t* block_tables;
+  const int32_t* seq_lens;
+  const float* alibi_slopes; /* [num_heads] or NULL */
+  /* v2 only (NULL for v1) */
+  float* exp_sums;
+  float* max_logits;
+  void* tmp_out;
+  int32_t num_seqs, num_heads, num_kv_heads, head_size, block_size;
+  int32_t max_num_blocks_per_seq, max_seq_len;
+  int64_t q_stride, kv_block_stride, kv_head_stride; /* elements */
+  float scale, kv_scale;
+  int32_t dtype;    /* b200_dtype of query/out */
+  int32_t kv_dtype; /* b200_kv_dtype */
+  /* block-sparse extension (attention_kernels.cu:209-256); vert_stride <= 1 disables it */
+  int32_t tp_rank, blocksparse_local_blocks, blocksparse_vert_stride;
+  int32_t blocksparse_block_size, blocksparse_head_sliding_step;
+} b200_paged_attention_params;
+
+int b200_paged_attention_v1(const b200_paged_attention_params* p, void* stream);
+int b200_paged_attention_v2(const b200_paged_attention_params* p, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Cache ops.  Replace csrc/cache_kernels.cu (schemas csrc/torch_bindings.cpp:207-244).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const void* key;   /* [num_tokens, num_heads, head_size], row stride key_stride */
+  const void* value; /* same, row stride value_stride */
+  void* key_cache;   /* [num_blocks, num_heads, head_size/x, block_size, x] */
+  void* value_cache; /* [num_blocks, num_heads, head_size, block_size] */
+  const int64_t* slot_mapping; /* [num_tokens]; < 0 = padding token, skipped */
+  int32_t num_tokens, num_heads, head_size, block_size, x;
+  int64_t key_stride, value_stride;
+  float kv_scale;
+  int32_t dtype;    /* b200_dtype of key/value */
+  int32_t kv_dtype; /* b200_kv_dtype of the caches */
+} b200_reshape_and_cache_params;
+
+/* reshape_and_cache (cache_kernels.cu:253-278) */
+int b200_reshape_and_cache(const b200_reshape_and_cache_params* p, void* stream);
+
+typedef struct {
+  const void* key;
+  const void* value;
+  void* k_cache; /* [num_blocks, block_size, num_heads, head_size] */
+  void* v_cache;
+  const int64_t* slot_mapping;
+  int32_t num_tokens, num_heads, head_size, block_size;
+  int64_t key_stride, value_stride, block_stride;
+  int32_t dtype;
+} b200_reshape_and_cache_flash_params;
+
+/* reshape_and_cache_flash (cache_kernels.cu:280-314); kv dtype "auto" only, as the reference */
+int b200_reshape_and_cache_flash(const b200_reshape_and_cache_flash_params* p, void* stream);
+
+/* copy_blocks (cache_kernels.cu:101-148).  key_cache_ptrs / value_cache_ptrs are DEVICE arrays of
+ * num_layers device pointers; block_mapping is a DEVICE [num_pairs, 2] int64 array (src, dst).
+ * bytes_per_block = numel_per_block * element size; must be a multiple of 16. */
+int b200_copy_blocks(const int64_t* key_cache_ptrs, const int64_t* value_cache_ptrs,
+                     const int64_t* block_mapping, int32_t num_layers, int32_t num_pairs,
+                     int64_t bytes_per_block, void* stream);
+
+/* swap_blocks (cache_kernels.cu:24-63).  block_mapping is a HOST [num_pairs, 2] int64 array.
+ * kind: 0 = device->device, 1 = device->host, 2 = host->device. One async copy per pair. */
+int b200_swap_blocks(const void* src, void* dst, const int64_t* block_mapping_host,
+                     int32_t num_pairs, int64_t bytes_per_block, int32_t kind, void* stream);
+
+/* convert_fp8 (cache_kernels.cu:339-389): exactly one of src/dst is uint8 (fp8). to_fp8 != 0
+ * quantises src (dtype) -> dst (fp8) as cvt_satfinite(x / scale); otherwise dequantises
+ * src (fp8) -> dst (dtype) as float(half(fp8)) * scale (quant_utils.cuh:295-301, 455-463). */
+int b200_convert_fp8(void* dst, const void* src, int64_t numel, float scale, int32_t dtype,
+                     int32_t kv_dtype, int32_t to_fp8, void* stream);
+
+/* _C_cuda_utils (csrc/cuda_utils_kernels.cu) */
+int b200_get_device_attribute(int32_t attribute, int32_t device_id, int32_t* value);
+int b200_get_max_shared_memory_per_block_device_attribute(int32_t device_id, int32_t* value);
+
+/* ------------------------------------------------------------------------------------------
+ * Activation quantisation feeding the W8A8 GEMM.
+ * Replaces csrc/quantization/compressed_tensors/int8_quant_kernels.cu:70-115 and
+ * csrc/quantization/fp8/common.cu:129-165.
+ * ------------------------------------------------------------------------------------------ */
+/* out int8 [num_tokens, hidden]; dynamic != 0: scales [num_tokens] written (absmax/127),
+ * else *scales (device scalar) read. */
+int b200_scaled_int8_quant(int8_t* out, const void* input, float* scales, int32_t num_tokens,
+                           int32_t hidden, int32_t dtype, int32_t dynamic, void* stream);
+/* out e4m3 [numel]; per-tensor scale (device scalar). dynamic != 0: *scale must be 0 on entry
+ * and receives absmax/448 (as fp8/common.cu:78-105), two launches. */
+int b200_scaled_fp8_quant(uint8_t* out, const void* input, float* scale, int64_t numel,
+                          int32_t dtype, int32_t dynamic, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * W8A8 GEMM with scale epilogue.  Replaces cutlass_scaled_mm
+ * (csrc/quantization/cutlass_w8a8/scaled_mm_entry.cu:48-100, scaled_mm_c3x.cu:539-556).
+ *   out[M,N] = a_scales[M or 1] * (b_scales[N or 1] * (a[M,K] . b[K,N])) (+ bias[N])
+ *   a row-major (lda), b column-major (ldb = stride between columns), out row-major (ldc).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  void* out;
+  const void* a;
+  const void* b;
+  const float* a_scales;
+  const float* b_scales;
+  const void* bias; /* NULL or [N] of out_dtype */
+  int32_t m, n, k;
+  int64_t lda, ldb, ldc;
+  int32_t a_scales_numel, b_scales_numel; /* 1 = per-tensor, m / n = per-token / per-channel */
+  int32_t qtype;     /* b200_qtype */
+  int32_t out_dtype; /* B200_F16 / B200_BF16 */
+} b200_scaled_mm_params;
+
+int b200_scaled_mm(const b200_scaled_mm_params* p, void* stream);
+/* cutlass_scaled_mm_supports_fp8 (scaled_mm_entry.cu:32-46): 1 for capability >= 89 */
+int b200_scaled_mm_supports_fp8(int32_t cuda_device_capability);
+
+/* ------------------------------------------------------------------------------------------
+ * GPTQ-Marlin W4A16 / W8A16.  Replaces gptq_marlin_repack
+ * (csrc/quantization/gptq_marlin/gptq_marlin_repack.cu:264-346) and gptq_marlin_gemm
+ * (csrc/quantization/gptq_marlin/gptq_marlin.cu:1726-1866).
+ * ------------------------------------------------------------------------------------------ */
+/* b_q_weight [size_k/pack, size_n] int32 (GPTQ, packed along K) -> out [size_k/16, size_n*16/pack]
+ * int32 (Marlin tiles); perm [size_k] int32 or NULL (act-order). pack = 32/num_bits. */
+int b200_gptq_marlin_repack(const uint32_t* b_q_weight, const int32_t* perm, uint32_t* out,
+                            int32_t size_k, int32_t size_n, int32_t num_bits, void* stream);
+
+typedef struct {
+  void* c;       /* [size_m, size_n] of dtype, contiguous */
+  const void* a; /* [size_m, size_k] of dtype, row stride lda */
+  const uint32_t* b_q_weight; /* Marlin-repacked [size_k/16, size_n*16/pack] */
+  const void* b_scales;       /* [num_groups, size_n] of dtype, marlin_permute_scales order */
+  const int32_t* g_idx;       /* [size_k] or NULL (no act-order) */
+  const int32_t* perm;        /* [size_k] or NULL */
+  void* a_tmp;                /* [size_m, size_k] scratch, required iff perm != NULL */
+  int32_t* workspace;         /* caller's lock buffer; left zeroed (never written here) */
+  int32_t size_m, size_n, size_k;
+  int64_t lda;
+  int32_t num_groups; /* b_scales rows; group_size = size_k / num_groups, or -1 semantics if 1 */
+  int32_t num_bits;   /* 4 or 8 */
+  int32_t is_k_full;
+  int32_t dtype;      /* B200_F16 / B200_BF16 */
+} b200_gptq_marlin_gemm_params;
+
+int b200_gptq_marlin_gemm(const b200_gptq_marlin_gemm_params* p, void* stream);
+
+/* 2:4-sparse Marlin.  Replaces gptq_marlin_24_gemm
+ * (csrc/quantization/marlin/sparse/marlin_24_cuda_kernel.cu:1015-1125). fp16 only. */
+typedef struct {
+  void* c;       /* [size_m, size_n] fp16 */
+  const void* a; /* [size_m, size_k] fp16, contiguous */
+  const uint32_t* b_q_weight; /* [size_k/2/16, size_n*16/pack] int32 */
+  const uint16_t* b_meta;     /* [size_k/2/... ] int16 metadata, reference layout */
+  const void* b_scales;       /* [num_groups, size_n] fp16 */
+  int32_t* workspace;
+  int32_t size_m, size_n, size_k;
+  int32_t num_groups;
+  int32_t num_bits;
+} b200_gptq_marlin_24_gemm_params;
+
+int b200_gptq_marlin_24_gemm(const b200_gptq_marlin_24_gemm_params* p, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_VLLM_H_ */
