@@ -24,6 +24,13 @@ extern "C" {
 
 #define B200_VLLM_ABI_VERSION 1
 
+/* every entry point is exported with default visibility (the library is built -fvisibility=hidden) */
+#if defined(__GNUC__)
+#define B200_API __attribute__((visibility("default")))
+#else
+#define B200_API
+#endif
+
 /* error codes */
 #define B200_OK 0
 #define B200_EINVAL (-1)   /* bad argument (shape / stride / alignment / enum) */
@@ -40,10 +47,10 @@ typedef enum { B200_KV_AUTO = 0, B200_KV_FP8_E4M3 = 1, B200_KV_FP8_E5M2 = 2 } b2
 /* quantized element types for the W8A8 GEMM */
 typedef enum { B200_Q_INT8 = 0, B200_Q_FP8_E4M3 = 1 } b200_qtype;
 
-int b200_abi_version(void);
-const char* b200_last_error(void);
+B200_API int b200_abi_version(void);
+B200_API const char* b200_last_error(void);
 /* parses the reference's kv_cache_dtype string; returns a b200_kv_dtype or B200_EINVAL */
-int b200_parse_kv_cache_dtype(const char* s);
+B200_API int b200_parse_kv_cache_dtype(const char* s);
 
 /* ------------------------------------------------------------------------------------------
  * Paged attention (decode).  Replaces paged_attention_v1 / paged_attention_v2
@@ -84,8 +91,8 @@ typedef struct {
   int32_t blocksparse_block_size, blocksparse_head_sliding_step;
 } b200_paged_attention_params;
 
-int b200_paged_attention_v1(const b200_paged_attention_params* p, void* stream);
-int b200_paged_attention_v2(const b200_paged_attention_params* p, void* stream);
+B200_API int b200_paged_attention_v1(const b200_paged_attention_params* p, void* stream);
+B200_API int b200_paged_attention_v2(const b200_paged_attention_params* p, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Cache ops.  Replace csrc/cache_kernels.cu (schemas csrc/torch_bindings.cpp:207-244).
@@ -104,7 +111,7 @@ typedef struct {
 } b200_reshape_and_cache_params;
 
 /* reshape_and_cache (cache_kernels.cu:253-278) */
-int b200_reshape_and_cache(const b200_reshape_and_cache_params* p, void* stream);
+B200_API int b200_reshape_and_cache(const b200_reshape_and_cache_params* p, void* stream);
 
 typedef struct {
   const void* key;
@@ -118,29 +125,29 @@ typedef struct {
 } b200_reshape_and_cache_flash_params;
 
 /* reshape_and_cache_flash (cache_kernels.cu:280-314); kv dtype "auto" only, as the reference */
-int b200_reshape_and_cache_flash(const b200_reshape_and_cache_flash_params* p, void* stream);
+B200_API int b200_reshape_and_cache_flash(const b200_reshape_and_cache_flash_params* p, void* stream);
 
 /* copy_blocks (cache_kernels.cu:101-148).  key_cache_ptrs / value_cache_ptrs are DEVICE arrays of
  * num_layers device pointers; block_mapping is a DEVICE [num_pairs, 2] int64 array (src, dst).
  * bytes_per_block = numel_per_block * element size; must be a multiple of 16. */
-int b200_copy_blocks(const int64_t* key_cache_ptrs, const int64_t* value_cache_ptrs,
+B200_API int b200_copy_blocks(const int64_t* key_cache_ptrs, const int64_t* value_cache_ptrs,
                      const int64_t* block_mapping, int32_t num_layers, int32_t num_pairs,
                      int64_t bytes_per_block, void* stream);
 
 /* swap_blocks (cache_kernels.cu:24-63).  block_mapping is a HOST [num_pairs, 2] int64 array.
  * kind: 0 = device->device, 1 = device->host, 2 = host->device. One async copy per pair. */
-int b200_swap_blocks(const void* src, void* dst, const int64_t* block_mapping_host,
+B200_API int b200_swap_blocks(const void* src, void* dst, const int64_t* block_mapping_host,
                      int32_t num_pairs, int64_t bytes_per_block, int32_t kind, void* stream);
 
 /* convert_fp8 (cache_kernels.cu:339-389): exactly one of src/dst is uint8 (fp8). to_fp8 != 0
  * quantises src (dtype) -> dst (fp8) as cvt_satfinite(x / scale); otherwise dequantises
  * src (fp8) -> dst (dtype) as float(half(fp8)) * scale (quant_utils.cuh:295-301, 455-463). */
-int b200_convert_fp8(void* dst, const void* src, int64_t numel, float scale, int32_t dtype,
+B200_API int b200_convert_fp8(void* dst, const void* src, int64_t numel, float scale, int32_t dtype,
                      int32_t kv_dtype, int32_t to_fp8, void* stream);
 
 /* _C_cuda_utils (csrc/cuda_utils_kernels.cu) */
-int b200_get_device_attribute(int32_t attribute, int32_t device_id, int32_t* value);
-int b200_get_max_shared_memory_per_block_device_attribute(int32_t device_id, int32_t* value);
+B200_API int b200_get_device_attribute(int32_t attribute, int32_t device_id, int32_t* value);
+B200_API int b200_get_max_shared_memory_per_block_device_attribute(int32_t device_id, int32_t* value);
 
 /* ------------------------------------------------------------------------------------------
  * Activation quantisation feeding the W8A8 GEMM.
@@ -149,11 +156,11 @@ int b200_get_max_shared_memory_per_block_device_attribute(int32_t device_id, int
  * ------------------------------------------------------------------------------------------ */
 /* out int8 [num_tokens, hidden]; dynamic != 0: scales [num_tokens] written (absmax/127),
  * else *scales (device scalar) read. */
-int b200_scaled_int8_quant(int8_t* out, const void* input, float* scales, int32_t num_tokens,
+B200_API int b200_scaled_int8_quant(int8_t* out, const void* input, float* scales, int32_t num_tokens,
                            int32_t hidden, int32_t dtype, int32_t dynamic, void* stream);
 /* out e4m3 [numel]; per-tensor scale (device scalar). dynamic != 0: *scale must be 0 on entry
  * and receives absmax/448 (as fp8/common.cu:78-105), two launches. */
-int b200_scaled_fp8_quant(uint8_t* out, const void* input, float* scale, int64_t numel,
+B200_API int b200_scaled_fp8_quant(uint8_t* out, const void* input, float* scale, int64_t numel,
                           int32_t dtype, int32_t dynamic, void* stream);
 
 /* ------------------------------------------------------------------------------------------
@@ -176,9 +183,9 @@ typedef struct {
   int32_t out_dtype; /* B200_F16 / B200_BF16 */
 } b200_scaled_mm_params;
 
-int b200_scaled_mm(const b200_scaled_mm_params* p, void* stream);
+B200_API int b200_scaled_mm(const b200_scaled_mm_params* p, void* stream);
 /* cutlass_scaled_mm_supports_fp8 (scaled_mm_entry.cu:32-46): 1 for capability >= 89 */
-int b200_scaled_mm_supports_fp8(int32_t cuda_device_capability);
+B200_API int b200_scaled_mm_supports_fp8(int32_t cuda_device_capability);
 
 /* ------------------------------------------------------------------------------------------
  * GPTQ-Marlin W4A16 / W8A16.  Replaces gptq_marlin_repack
@@ -187,7 +194,7 @@ int b200_scaled_mm_supports_fp8(int32_t cuda_device_capability);
  * ------------------------------------------------------------------------------------------ */
 /* b_q_weight [size_k/pack, size_n] int32 (GPTQ, packed along K) -> out [size_k/16, size_n*16/pack]
  * int32 (Marlin tiles); perm [size_k] int32 or NULL (act-order). pack = 32/num_bits. */
-int b200_gptq_marlin_repack(const uint32_t* b_q_weight, const int32_t* perm, uint32_t* out,
+B200_API int b200_gptq_marlin_repack(const uint32_t* b_q_weight, const int32_t* perm, uint32_t* out,
                             int32_t size_k, int32_t size_n, int32_t num_bits, void* stream);
 
 typedef struct {
@@ -207,7 +214,7 @@ typedef struct {
   int32_t dtype;      /* B200_F16 / B200_BF16 */
 } b200_gptq_marlin_gemm_params;
 
-int b200_gptq_marlin_gemm(const b200_gptq_marlin_gemm_params* p, void* stream);
+B200_API int b200_gptq_marlin_gemm(const b200_gptq_marlin_gemm_params* p, void* stream);
 
 /* 2:4-sparse Marlin.  Replaces gptq_marlin_24_gemm
  * (csrc/quantization/marlin/sparse/marlin_24_cuda_kernel.cu:1015-1125). fp16 only. */
@@ -223,7 +230,7 @@ typedef struct {
   int32_t num_bits;
 } b200_gptq_marlin_24_gemm_params;
 
-int b200_gptq_marlin_24_gemm(const b200_gptq_marlin_24_gemm_params* p, void* stream);
+B200_API int b200_gptq_marlin_24_gemm(const b200_gptq_marlin_24_gemm_params* p, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,324 @@
+// Host entry points of paged attention + the two kernels that are not dtype-specialised tensor
+// kernels: the split-KV reduce (replaces paged_attention_v2_reduce_kernel,
+// csrc/attention/attention_kernels.cu:567-669) and a SIMT kernel that covers what the tensor path
+// does not (fp32 activations, block-sparse masks, unaligned queries).
+#include <cfloat>
+#include <cstdlib>
+
+#include "paged_attention.cuh"
+
+namespace b200 {
+
+// -----------------------------------------------------------------------------------------------
+// v2 reduce: out = sum_p tmp_out[p] * exp_sums[p] * exp(max[p] - gmax) / (sum_p(...) + 1e-6)
+// grid (num_heads, num_seqs), one thread per output pair.
+// -----------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void paged_attn_reduce_kernel(T* __restrict__ out, const float* __restrict__ exp_sums,
+                                         const float* __restrict__ max_logits,
+                                         const T* __restrict__ tmp_out,
+                                         const int32_t* __restrict__ seq_lens, const int head_size,
+                                         const int max_num_partitions, const int partition_size) {
+  extern __shared__ float red_w[];  // [num_partitions] rescaled weights
+  __shared__ float s_inv;
+  const int head = blockIdx.x, seq = blockIdx.y, num_heads = gridDim.x;
+  const int seq_len = seq_lens[seq];
+  const int np = min((seq_len + partition_size - 1) / partition_size, max_num_partitions);
+  const int64_t row = (int64_t)seq * num_heads + head;
+  const float* ml = max_logits + row * max_num_partitions;
+  const float* es = exp_sums + row * max_num_partitions;
+  const T* tp = tmp_out + row * max_num_partitions * head_size;
+  T* op = out + row * head_size;
+  if (np <= 0) {
+    for (int d = threadIdx.x; d < head_size; d += blockDim.x) op[d] = DT<T>::from_f(0.f);
+    return;
+  }
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    float gmax = -FLT_MAX;
+    for (int p = lane; p < np; p += 32) gmax = fmaxf(gmax, ml[p]);
+    gmax = warp_max(gmax);
+    float gsum = 0.f;
+    for (int p = lane; p < np; p += 32) {
+      const float w = es[p] * __expf(ml[p] - gmax);
+      red_w[p] = w;
+      gsum += w;
+    }
+    gsum = warp_sum(gsum);
+    if (lane == 0) s_inv = __fdividef(1.f, gsum + 1e-6f);
+  }
+  __syncthreads();
+  const float inv = s_inv;
+  for (int d = threadIdx.x; d < head_size; d += blockDim.x) {
+    float acc = 0.f;
+    for (int p = 0; p < np; ++p) acc = fmaf(DT<T>::to_f(tp[(int64_t)p * head_size + d]), red_w[p], acc);
+    op[d] = DT<T>::from_f(acc * inv);
+  }
+}
+
+// -----------------------------------------------------------------------------------------------
+// SIMT kernel: one CTA per (query head, sequence, partition). Correctness-first: handles every
+// dtype / head size / block size / alibi / block-sparse combination of the reference.
+// -----------------------------------------------------------------------------------------------
+template <typename T, bool FP8>
+__device__ __forceinline__ float load_cache(const void* p, int64_t idx, int e5m2) {
+  if constexpr (FP8) {
+    const uint8_t v = reinterpret_cast<const uint8_t*>(p)[idx];
+    return e5m2 ? fp8_to_float<B200_KV_FP8_E5M2>(v) : fp8_to_float<B200_KV_FP8_E4M3>(v);
+  } else {
+    return DT<T>::to_f(reinterpret_cast<const T*>(p)[idx]);
+  }
+}
+
+template <typename T, bool FP8>
+__global__ void __launch_bounds__(128) paged_attn_simt_kernel(const AttnArgs a) {
+  extern __shared__ float sm[];  // [head_size] q | [tokens] logits
+  __shared__ float red[4];
+  const int head = blockIdx.x, seq = blockIdx.y, part = blockIdx.z;
+  const int tid = threadIdx.x;
+  const int D = a.head_size, BS = a.block_size;
+  const int G = a.num_heads / a.num_kv_heads;
+  const int kvh = head / G;
+  const int seq_len = a.sl[seq];
+  const bool partitioned = a.partition_size > 0;
+  const int tok_begin = partitioned ? part * a.partition_size : 0;
+  const int tok_end = partitioned ? min(seq_len, tok_begin + a.partition_size) : seq_len;
+  if (partitioned && tok_begin >= seq_len) return;
+  const int x = FP8 ? 16 : 16 / (int)sizeof(T);
+  float* qs = sm;
+  float* logits = sm + D;
+  const T* qp = reinterpret_cast<const T*>(a.q) + (int64_t)seq * a.q_stride + (int64_t)head * D;
+  for (int d = tid; d < D; d += blockDim.x) qs[d] = DT<T>::to_f(qp[d]);
+  __syncthreads();
+
+  const int32_t* bt_row = a.bt + (int64_t)seq * a.max_blocks_per_seq;
+  const bool sparse = a.bs_vert_stride > 1;
+  int bs_offset = 0, q_bs_block = 0;
+  if (sparse) {  // attention_kernels.cu:209-224
+    q_bs_block = (seq_len - 1) / a.bs_block_size;
+    bs_offset = a.bs_head_sliding_step >= 0
+                    ? (a.tp_rank * a.num_heads + head) * a.bs_head_sliding_step + 1
+                    : (a.tp_rank * a.num_kv_heads + kvh) * (-a.bs_head_sliding_step) + 1;
+  }
+  auto attended = [&](int block_idx) {
+    if (!sparse) return true;
+    const int kb = block_idx * BS / a.bs_block_size;
+    return ((kb + bs_offset) % a.bs_vert_stride == 0) || (kb > q_bs_block - a.bs_local_blocks);
+  };
+  const float alibi = a.alibi ? a.alibi[head] : 0.f;
+  const float sc = a.scale * a.k_scale;
+
+  float mx = -FLT_MAX;
+  for (int tok = tok_begin + tid; tok < tok_end; tok += blockDim.x) {
+    const int bi = tok / BS, off = tok - bi * BS;
+    float lg = -FLT_MAX;
+    if (attended(bi)) {
+      const int64_t kb = (int64_t)bt_row[bi] * a.kv_block_stride + (int64_t)kvh * a.kv_head_stride;
+      float dot = 0.f;
+      for (int d = 0; d < D; ++d) {
+        const int64_t idx = kb + ((int64_t)(d / x) * BS + off) * x + (d % x);
+        dot = fmaf(qs[d], load_cache<T, FP8>(a.kc, idx, a.e5m2), dot);
+      }
+      lg = dot * sc + (a.alibi ? alibi * (float)(tok - seq_len + 1) : 0.f);
+      mx = fmaxf(mx, lg);
+    }
+    logits[tok - tok_begin] = lg;
+  }
+  mx = warp_max(mx);
+  if ((tid & 31) == 0) red[tid >> 5] = mx;
+  __syncthreads();
+  mx = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+  __syncthreads();
+  float sum = 0.f;
+  for (int i = tid; i < tok_end - tok_begin; i += blockDim.x) {
+    const float p = __expf(logits[i] - mx);
+    logits[i] = p;
+    sum += p;
+  }
+  sum = warp_sum(sum);
+  if ((tid & 31) == 0) red[tid >> 5] = sum;
+  __syncthreads();
+  sum = red[0] + red[1] + red[2] + red[3];
+  const float inv = __fdividef(1.f, sum + 1e-6f);
+
+  T* dst;
+  if (partitioned && a.max_num_partitions > 1) {
+    const int64_t si = ((int64_t)seq * a.num_heads + head) * a.max_num_partitions + part;
+    dst = reinterpret_cast<T*>(a.tmp_out) + si * D;
+    if (tid == 0) {
+      a.exp_sums[si] = sum;
+      a.max_logits[si] = mx;
+    }
+  } else {
+    dst = reinterpret_cast<T*>(a.out) + ((int64_t)seq * a.num_heads + head) * D;
+  }
+  for (int d = tid; d < D; d += blockDim.x) {
+    float acc = 0.f;
+    for (int tok = tok_begin; tok < tok_end; ++tok) {
+      const int bi = tok / BS, off = tok - bi * BS;
+      if (!attended(bi)) continue;
+      const int64_t vb = (int64_t)bt_row[bi] * a.kv_block_stride + (int64_t)kvh * a.kv_head_stride;
+      // probabilities are rounded to the model dtype first (attention_kernels.cu:398-400)
+      const float p = DT<T>::to_f(DT<T>::from_f(logits[tok - tok_begin] * inv));
+      acc = fmaf(p, load_cache<T, FP8>(a.vc, vb + (int64_t)d * BS + off, a.e5m2), acc);
+    }
+    dst[d] = DT<T>::from_f(acc * a.v_scale);
+  }
+}
+
+template <typename T>
+static int launch_simt(const AttnArgs& a, bool fp8, dim3 grid, size_t smem, cudaStream_t stream) {
+  auto set = [&](auto kern) -> int {
+    if (smem > 48 * 1024) {
+      cudaError_t e =
+          cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        set_error("paged_attention: max_seq_len needs %zu B of shared memory: %s", smem,
+                  cudaGetErrorString(e));
+        return B200_ENOTSUP;
+      }
+    }
+    kern<<<grid, 128, smem, stream>>>(a);
+    return check_launch("paged_attention (simt)");
+  };
+  return fp8 ? set(paged_attn_simt_kernel<T, true>) : set(paged_attn_simt_kernel<T, false>);
+}
+
+static int run_paged_attention(const b200_paged_attention_params* p, bool v2, cudaStream_t stream) {
+  B200_REQUIRE(p != nullptr, B200_EINVAL, "paged_attention: null params");
+  if (p->num_seqs == 0) return B200_OK;
+  B200_REQUIRE(p->num_seqs > 0 && p->num_heads > 0 && p->num_kv_heads > 0 &&
+                   p->num_heads % p->num_kv_heads == 0,
+               B200_EINVAL, "paged_attention: bad head counts (%d q heads, %d kv heads)",
+               p->num_heads, p->num_kv_heads);
+  // the reference's supported sets (attention_kernels.cu:763-766, 800-802 / 899-927, 950-964)
+  const int hs = p->head_size;
+  B200_REQUIRE(hs == 64 || hs == 80 || hs == 96 || hs == 112 || hs == 128 || hs == 192 || hs == 256,
+               B200_ENOTSUP, "Unsupported head size: %d", hs);
+  B200_REQUIRE(p->block_size == 8 || p->block_size == 16 || p->block_size == 32, B200_ENOTSUP,
+               "Unsupported block size: %d", p->block_size);
+  B200_REQUIRE(p->kv_dtype >= B200_KV_AUTO && p->kv_dtype <= B200_KV_FP8_E5M2, B200_EINVAL,
+               "Unsupported data type of kv cache: %d", p->kv_dtype);
+  B200_REQUIRE(p->dtype >= B200_F16 && p->dtype <= B200_F32, B200_EINVAL,
+               "Unsupported data type: %d", p->dtype);
+  const bool fp8 = p->kv_dtype != B200_KV_AUTO;
+  if (v2) {
+    B200_REQUIRE(p->exp_sums && p->max_logits && p->tmp_out, B200_EINVAL,
+                 "paged_attention_v2: exp_sums / max_logits / tmp_out are required");
+  }
+
+  AttnArgs a{};
+  a.out = p->out;
+  a.q = p->query;
+  a.kc = p->key_cache;
+  a.vc = p->value_cache;
+  a.bt = p->block_tables;
+  a.sl = p->seq_lens;
+  a.alibi = p->alibi_slopes;
+  a.exp_sums = p->exp_sums;
+  a.max_logits = p->max_logits;
+  a.tmp_out = p->tmp_out;
+  a.num_seqs = p->num_seqs;
+  a.num_heads = p->num_heads;
+  a.num_kv_heads = p->num_kv_heads;
+  a.head_size = hs;
+  a.block_size = p->block_size;
+  a.max_blocks_per_seq = p->max_num_blocks_per_seq;
+  a.partition_size = v2 ? B200_PARTITION_SIZE : 0;
+  a.max_num_partitions =
+      v2 ? (p->max_seq_len + B200_PARTITION_SIZE - 1) / B200_PARTITION_SIZE : 1;
+  if (a.max_num_partitions < 1) a.max_num_partitions = 1;
+  a.e5m2 = p->kv_dtype == B200_KV_FP8_E5M2;
+  a.q_stride = p->q_stride;
+  a.kv_block_stride = p->kv_block_stride;
+  a.kv_head_stride = p->kv_head_stride;
+  a.scale = p->scale;
+  a.k_scale = fp8 ? p->kv_scale : 1.f;
+  a.v_scale = fp8 ? p->kv_scale : 1.f;
+  a.tp_rank = p->tp_rank;
+  a.bs_local_blocks = p->blocksparse_local_blocks;
+  a.bs_vert_stride = p->blocksparse_vert_stride;
+  a.bs_block_size = p->blocksparse_block_size;
+  a.bs_head_sliding_step = p->blocksparse_head_sliding_step;
+
+  const bool sparse = p->blocksparse_vert_stride > 1;
+  const int esz_q = p->dtype == B200_F32 ? 4 : 2;
+  const int esz_c = fp8 ? 1 : esz_q;
+  const bool aligned = (reinterpret_cast<uintptr_t>(p->query) % 8 == 0) &&
+                       ((p->q_stride * esz_q) % 8 == 0) &&
+                       (reinterpret_cast<uintptr_t>(p->key_cache) % 16 == 0) &&
+                       (reinterpret_cast<uintptr_t>(p->value_cache) % 16 == 0) &&
+                       ((p->kv_block_stride * esz_c) % 16 == 0) &&
+                       ((p->kv_head_stride * esz_c) % 16 == 0) &&
+                       (reinterpret_cast<uintptr_t>(p->out) % 4 == 0) &&
+                       (!v2 || reinterpret_cast<uintptr_t>(p->tmp_out) % 4 == 0);
+  const bool tensor_path = p->dtype != B200_F32 && !sparse && aligned;
+
+  int rc;
+  if (tensor_path) {
+    const int G = p->num_heads / p->num_kv_heads;
+    const int nt = G > 8 ? 2 : 1;
+    a.q_tiles = (G + 8 * nt - 1) / (8 * nt);
+    const int it_tokens = p->block_size < 16 ? 16 : p->block_size;
+    a.stage_bytes = 2 * hs * it_tokens * esz_c;
+    const int merge_bytes = 8 * nt * (hs + 4) * 4 + 8 * nt * 8;
+    // ~24 KiB of KV in flight per warp, 2-3 CTAs per SM
+    int stages = (24 * 1024) / a.stage_bytes;
+    if (stages < 2) stages = 2;
+    if (stages > kAttnMaxStages) stages = kAttnMaxStages;
+    if (const char* ev = getenv("B200_ATTN_STAGES")) {  // tuning knob (bench sweeps)
+      const int v = atoi(ev);
+      if (v >= 2 && v <= kAttnMaxStages) stages = v;
+    }
+    while (stages * a.stage_bytes < merge_bytes) ++stages;
+    B200_REQUIRE(stages <= kAttnMaxStages, B200_ENOTSUP, "paged_attention: internal stage sizing");
+    a.stages = stages;
+    const size_t smem = 256 + (size_t)kAttnWarps * stages * a.stage_bytes;
+    dim3 grid(p->num_kv_heads * a.q_tiles, p->num_seqs, a.max_num_partitions);
+    rc = p->dtype == B200_F16 ? launch_paged_attn_mma<__half>(a, fp8, grid, smem, stream)
+                              : launch_paged_attn_mma<__nv_bfloat16>(a, fp8, grid, smem, stream);
+  } else {
+    const int toks = v2 ? B200_PARTITION_SIZE : ((p->max_seq_len + 15) / 16) * 16;
+    const size_t smem = (size_t)(hs + toks) * sizeof(float);
+    dim3 grid(p->num_heads, p->num_seqs, a.max_num_partitions);
+    rc = p->dtype == B200_F16    ? launch_simt<__half>(a, fp8, grid, smem, stream)
+         : p->dtype == B200_BF16 ? launch_simt<__nv_bfloat16>(a, fp8, grid, smem, stream)
+                                 : launch_simt<float>(a, fp8, grid, smem, stream);
+  }
+  if (rc != B200_OK) return rc;
+
+  if (v2 && a.max_num_partitions > 1) {
+    dim3 grid(p->num_heads, p->num_seqs);
+    const int threads = hs <= 64 ? 64 : 128;
+    const size_t smem = (size_t)a.max_num_partitions * sizeof(float);
+#define B200_REDUCE(T)                                                                          \
+  paged_attn_reduce_kernel<T><<<grid, threads, smem, stream>>>(                                  \
+      (T*)p->out, p->exp_sums, p->max_logits, (const T*)p->tmp_out, p->seq_lens, hs,             \
+      a.max_num_partitions, B200_PARTITION_SIZE)
+    if (p->dtype == B200_F16) {
+      B200_REDUCE(__half);
+    } else if (p->dtype == B200_BF16) {
+      B200_REDUCE(__nv_bfloat16);
+    } else {
+      B200_REDUCE(float);
+    }
+#undef B200_REDUCE
+    return check_launch("paged_attention_v2 reduce");
+  }
+  return B200_OK;
+}
+
+}  // namespace b200
+
+extern "C" {
+
+int b200_paged_attention_v1(const b200_paged_attention_params* p, void* stream) {
+  return b200::run_paged_attention(p, false, (cudaStream_t)stream);
+}
+
+int b200_paged_attention_v2(const b200_paged_attention_params* p, void* stream) {
+  return b200::run_paged_attention(p, true, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,497 @@
+// Tensor-core paged decode attention kernel body (see paged_attention.cuh for the design).
+// Included by paged_attention_f16.cu / paged_attention_bf16.cu, which instantiate it per dtype.
+#pragma once
+
+#include "paged_attention.cuh"
+
+namespace b200 {
+
+template <typename T>
+__device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0,
+                                          uint32_t b1);
+template <>
+__device__ __forceinline__ void mma_16816<__half>(float (&d)[4], const uint32_t (&a)[4],
+                                                  uint32_t b0, uint32_t b1) {
+  mma_16816_f16(d, a, b0, b1);
+}
+template <>
+__device__ __forceinline__ void mma_16816<__nv_bfloat16>(float (&d)[4], const uint32_t (&a)[4],
+                                                         uint32_t b0, uint32_t b1) {
+  mma_16816_bf16(d, a, b0, b1);
+}
+
+__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t v) {
+  uint32_t o;
+  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(o) : "r"(v));
+  return o;
+}
+
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+
+// two packed fp8 (low 16 bits of v) -> two packed T
+template <typename T>
+__device__ __forceinline__ uint32_t fp8x2_to_T2(uint32_t v, int e5m2) {
+  uint32_t h;
+  if (e5m2) {
+    // e5m2 is the top byte of an fp16: (b1 b0) -> (b1<<8 | 0, b0<<8 | 0)
+    h = ((v & 0xff00u) << 16) | ((v & 0x00ffu) << 8);
+  } else {
+    unsigned short s = (unsigned short)(v & 0xffffu);
+    asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(h) : "h"(s));
+  }
+  if constexpr (sizeof(T) == 2 && DT<T>::id == B200_BF16) {
+    __half2 hh = *reinterpret_cast<__half2*>(&h);
+    float2 f = __half22float2(hh);
+    __nv_bfloat162 b = __floats2bfloat162_rn(f.x, f.y);  // exact: e4m3/e5m2 fit in bf16
+    return *reinterpret_cast<uint32_t*>(&b);
+  } else {
+    return h;
+  }
+}
+
+template <typename T, bool FP8, int NT, int HMAX, bool HEXACT>
+__global__ void __launch_bounds__(kAttnThreads)
+    paged_attn_mma_kernel(const AttnArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  constexpr int KS = HMAX / 16;  // k-steps of QK == d-tiles of PV
+  constexpr int ESZ = FP8 ? 1 : 2;
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int r = lane >> 2, t = lane & 3;
+  const int G = a.num_heads / a.num_kv_heads;
+  const int kvh = blockIdx.x / a.q_tiles;
+  const int qtile = blockIdx.x - kvh * a.q_tiles;
+  const int seq = blockIdx.y;
+  const int part = blockIdx.z;
+  const int BS = a.block_size;
+  const int D = HEXACT ? HMAX : a.head_size;
+  const int nks = D >> 4;
+  const int seq_len = a.sl[seq];
+  const bool partitioned = a.partition_size > 0;
+  const int tok_begin = partitioned ? part * a.partition_size : 0;
+  const int tok_end = partitioned ? min(seq_len, tok_begin + a.partition_size) : seq_len;
+  if (partitioned && tok_begin >= seq_len) return;  // attention_kernels.cu:128-131
+
+  const int IT = BS < 16 ? 16 : BS;  // tokens per pipeline item (stage)
+  const int item_begin = tok_begin / IT;
+  const int item_end = (tok_end + IT - 1) / IT;
+  const int n_total = max(item_end - item_begin, 0);
+  const int n_items = n_total > warp ? (n_total - warp + kAttnWarps - 1) / kAttnWarps : 0;
+  const int num_seq_blocks = (seq_len + BS - 1) / BS;
+
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);  // [kAttnWarps][kAttnMaxStages]
+  const int S = a.stages;
+  const uint32_t stage_bytes = a.stage_bytes;
+  const uint32_t tile_bytes = (uint32_t)D * BS * ESZ;  // one (block, kv head) K or V tile
+  uint8_t* wbase = smem + 256 + (size_t)warp * S * stage_bytes;
+  const uint32_t wbase_s = smem_u32(wbase);
+
+  if (tid == 0) {
+    for (int i = 0; i < kAttnWarps * kAttnMaxStages; ++i) mbar_init(&full[i], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  // ---- block-table window: lane i holds the physical block(s) of this warp's item 32*grp+i ----
+  const int32_t* bt_row = a.bt + (int64_t)seq * a.max_blocks_per_seq;
+  int bt0 = 0, bt1 = 0, bt_grp = -1;
+  auto load_bt = [&](int grp) {
+    const int item = item_begin + warp + kAttnWarps * (grp * 32 + lane);
+    if (BS >= 16) {
+      bt0 = item < num_seq_blocks ? __ldg(bt_row + item) : 0;
+    } else {
+      bt0 = 2 * item < num_seq_blocks ? __ldg(bt_row + 2 * item) : 0;
+      bt1 = 2 * item + 1 < num_seq_blocks ? __ldg(bt_row + 2 * item + 1) : 0;
+    }
+    bt_grp = grp;
+  };
+  const uint8_t* kc = reinterpret_cast<const uint8_t*>(a.kc) + (int64_t)kvh * a.kv_head_stride * ESZ;
+  const uint8_t* vc = reinterpret_cast<const uint8_t*>(a.vc) + (int64_t)kvh * a.kv_head_stride * ESZ;
+  const int64_t blk_bytes = a.kv_block_stride * ESZ;
+
+  auto issue = [&](int i) {  // whole warp calls; lane 0 issues
+    if ((i >> 5) != bt_grp) load_bt(i >> 5);
+    const int p0 = __shfl_sync(0xffffffffu, bt0, i & 31);
+    const int p1 = __shfl_sync(0xffffffffu, bt1, i & 31);
+    if (lane == 0) {
+      const int s = i % S;
+      uint8_t* dst = wbase + (size_t)s * stage_bytes;
+      uint64_t* bar = &full[warp * kAttnMaxStages + s];
+      if (BS >= 16) {
+        mbar_arrive_expect_tx(bar, 2 * tile_bytes);
+        bulk_g2s(dst, kc + p0 * blk_bytes, tile_bytes, bar);
+        bulk_g2s(dst + (stage_bytes >> 1), vc + p0 * blk_bytes, tile_bytes, bar);
+      } else {
+        const int item = item_begin + warp + kAttnWarps * i;
+        const bool two = 2 * item + 1 < num_seq_blocks;
+        mbar_arrive_expect_tx(bar, two ? 4 * tile_bytes : 2 * tile_bytes);
+        bulk_g2s(dst, kc + p0 * blk_bytes, tile_bytes, bar);
+        bulk_g2s(dst + (stage_bytes >> 1), vc + p0 * blk_bytes, tile_bytes, bar);
+        if (two) {
+          bulk_g2s(dst + tile_bytes, kc + p1 * blk_bytes, tile_bytes, bar);
+          bulk_g2s(dst + (stage_bytes >> 1) + tile_bytes, vc + p1 * blk_bytes, tile_bytes, bar);
+        }
+      }
+    }
+  };
+
+  // prologue: get the KV stream going before anything else
+  for (int i = 0; i < S && i < n_items; ++i) issue(i);
+
+  // ---- Q^T fragments (B operand): heads in N, head dim in K ----
+  const int head_in_group0 = qtile * (8 * NT);
+  uint32_t qf[NT][KS][2];
+  float alibi2[NT][2];
+#pragma unroll
+  for (int j = 0; j < NT; ++j) {
+    const int hg = head_in_group0 + 8 * j + r;  // B fragment: n = lane/4
+    const bool hv = hg < G;
+    const T* qp = reinterpret_cast<const T*>(a.q) + (int64_t)seq * a.q_stride +
+                  (int64_t)(kvh * G + hg) * D;
+#pragma unroll
+    for (int kk = 0; kk < KS; ++kk) {
+      uint32_t b0 = 0, b1 = 0;
+      if (hv && (HEXACT || kk < nks)) {
+        if constexpr (!FP8) {
+          b0 = *reinterpret_cast<const uint32_t*>(qp + 16 * kk + 2 * t);
+          b1 = *reinterpret_cast<const uint32_t*>(qp + 16 * kk + 8 + 2 * t);
+        } else {
+          const uint2 v = *reinterpret_cast<const uint2*>(qp + 16 * kk + 4 * t);
+          b0 = v.x;
+          b1 = v.y;
+        }
+      }
+      qf[j][kk][0] = b0;
+      qf[j][kk][1] = b1;
+    }
+    // softmax state is indexed by the C fragment: heads 2t, 2t+1
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int hc = head_in_group0 + 8 * j + 2 * t + e;
+      alibi2[j][e] = (a.alibi != nullptr && hc < G) ? a.alibi[kvh * G + hc] * kLog2e : 0.f;
+    }
+  }
+  const bool has_alibi = a.alibi != nullptr;
+  const float scale2 = a.scale * a.k_scale * kLog2e;
+
+  float m_run[NT][2], l_run[NT][2];
+  float acc[KS][NT][4];
+#pragma unroll
+  for (int j = 0; j < NT; ++j) {
+    m_run[j][0] = m_run[j][1] = -INFINITY;
+    l_run[j][0] = l_run[j][1] = 0.f;
+  }
+#pragma unroll
+  for (int dt = 0; dt < KS; ++dt)
+#pragma unroll
+    for (int j = 0; j < NT; ++j)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[dt][j][e] = 0.f;
+
+  // token owned by S^T row r (rho0) and row r+8 (rho1) inside a 16-token chunk
+  const int rho0 = FP8 ? (4 * (r >> 1) + (r & 1)) : r;
+  const int rho1 = FP8 ? rho0 + 2 : r + 8;
+
+  // ---- main loop over this warp's items ----
+  for (int it = 0; it < n_items; ++it) {
+    const int s = it % S;
+    mbar_wait(&full[warp * kAttnMaxStages + s], (uint32_t)((it / S) & 1));
+    const uint32_t st = wbase_s + (uint32_t)s * stage_bytes;
+    const int item = item_begin + warp + kAttnWarps * it;
+    const int n_chunks = BS <= 16 ? 1 : (BS >> 4);
+    for (int c = 0; c < n_chunks; ++c) {
+      const int tok0 = item * IT + 16 * c;
+      if (tok0 >= tok_end) break;
+      const bool tail = tok0 + 16 > tok_end;
+
+      // ---- S^T[16 tok][8*NT heads] = K . Q^T ----
+      float sacc[2][NT][4];
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int j = 0; j < NT; ++j)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) sacc[h][j][e] = 0.f;
+
+      if constexpr (!FP8) {
+        // ldmatrix.x4: lanes 0-7 rows of (tok 0-7, g), 8-15 (tok 8-15, g), 16-23 (tok 0-7, g+1), ...
+        const int o = (lane >> 3) & 1;
+        uint32_t kaddr;
+        uint32_t gstride;  // bytes between consecutive x-groups (x = 8 elements)
+        if (BS >= 16) {
+          gstride = (uint32_t)BS * 16;
+          kaddr = st + (uint32_t)(16 * c + 8 * o + (lane & 7)) * 16 + (lane >> 4) * gstride;
+        } else {
+          gstride = 8 * 16;
+          kaddr = st + o * tile_bytes + (uint32_t)(lane & 7) * 16 + (lane >> 4) * gstride;
+        }
+#pragma unroll
+        for (int kk = 0; kk < KS; ++kk) {
+          if (HEXACT || kk < nks) {
+            uint32_t af[4];
+            ldmatrix_x4(af[0], af[1], af[2], af[3], kaddr + (uint32_t)kk * 2 * gstride);
+#pragma unroll
+            for (int j = 0; j < NT; ++j) mma_16816<T>(sacc[kk & 1][j], af, qf[j][kk][0], qf[j][kk][1]);
+          }
+        }
+      } else {
+        // fp8: x = 16, one x-group per k-step; row = token, 16 bytes of head dim
+        uint32_t k0, k1, gstride;
+        if (BS >= 16) {
+          gstride = (uint32_t)BS * 16;
+          k0 = st + (uint32_t)(16 * c + rho0) * 16 + 4 * t;
+          k1 = st + (uint32_t)(16 * c + rho1) * 16 + 4 * t;
+        } else {
+          gstride = 8 * 16;
+          k0 = st + (rho0 >> 3) * tile_bytes + (uint32_t)(rho0 & 7) * 16 + 4 * t;
+          k1 = st + (rho1 >> 3) * tile_bytes + (uint32_t)(rho1 & 7) * 16 + 4 * t;
+        }
+#pragma unroll
+        for (int kk = 0; kk < KS; ++kk) {
+          if (HEXACT || kk < nks) {
+            const uint32_t w0 = lds32(k0 + (uint32_t)kk * gstride);
+            const uint32_t w1 = lds32(k1 + (uint32_t)kk * gstride);
+            uint32_t af[4];
+            af[0] = fp8x2_to_T2<T>(w0, a.e5m2);
+            af[2] = fp8x2_to_T2<T>(w0 >> 16, a.e5m2);
+            af[1] = fp8x2_to_T2<T>(w1, a.e5m2);
+            af[3] = fp8x2_to_T2<T>(w1 >> 16, a.e5m2);
+#pragma unroll
+            for (int j = 0; j < NT; ++j) mma_16816<T>(sacc[kk & 1][j], af, qf[j][kk][0], qf[j][kk][1]);
+          }
+        }
+      }
+
+      // ---- online softmax (per head; heads 2t, 2t+1 of every n-tile live in this thread) ----
+      const int tp0 = tok0 + rho0, tp1 = tok0 + rho1;
+      uint32_t pb0[NT], pb1[NT];
+      float corr[NT][2];
+#pragma unroll
+      for (int j = 0; j < NT; ++j) {
+        float sv[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) sv[e] = (sacc[0][j][e] + sacc[1][j][e]) * scale2;
+        if (has_alibi) {
+          const float d0 = (float)(tp0 - seq_len + 1), d1 = (float)(tp1 - seq_len + 1);
+          sv[0] = fmaf(alibi2[j][0], d0, sv[0]);
+          sv[1] = fmaf(alibi2[j][1], d0, sv[1]);
+          sv[2] = fmaf(alibi2[j][0], d1, sv[2]);
+          sv[3] = fmaf(alibi2[j][1], d1, sv[3]);
+        }
+        if (tail) {
+          if (tp0 >= tok_end) sv[0] = sv[1] = -INFINITY;
+          if (tp1 >= tok_end) sv[2] = sv[3] = -INFINITY;
+        }
+        float mx0 = fmaxf(sv[0], sv[2]), mx1 = fmaxf(sv[1], sv[3]);
+#pragma unroll
+        for (int off = 4; off <= 16; off <<= 1) {
+          mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, off));
+          mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, off));
+        }
+        const float mn0 = fmaxf(m_run[j][0], mx0), mn1 = fmaxf(m_run[j][1], mx1);
+        // every processed chunk has >= 1 valid token, so mn is finite
+        corr[j][0] = exp2f(m_run[j][0] - mn0);
+        corr[j][1] = exp2f(m_run[j][1] - mn1);
+        m_run[j][0] = mn0;
+        m_run[j][1] = mn1;
+        const float p0 = exp2f(sv[0] - mn0), p1 = exp2f(sv[1] - mn1);
+        const float p2 = exp2f(sv[2] - mn0), p3 = exp2f(sv[3] - mn1);
+        l_run[j][0] = fmaf(l_run[j][0], corr[j][0], p0 + p2);
+        l_run[j][1] = fmaf(l_run[j][1], corr[j][1], p1 + p3);
+        // probabilities are rounded to the model dtype before P.V (attention_kernels.cu:398-400)
+        pb0[j] = movmatrix_trans(DT<T>::pack2(p0, p1));
+        pb1[j] = movmatrix_trans(DT<T>::pack2(p2, p3));
+      }
+
+      // ---- O^T[D][8*NT heads] += V^T . P^T ----
+      uint32_t vaddr, dstride;  // fp16: ldmatrix lane address; fp8: row-r address
+      if constexpr (!FP8) {
+        const int o = lane >> 4;              // token octet of this lane's matrix
+        const int dsub = (lane >> 3) & 1;     // d octet inside the 16-row tile
+        if (BS >= 16) {
+          dstride = (uint32_t)BS * 2;
+          vaddr = st + (stage_bytes >> 1) + (uint32_t)(16 * c + 8 * o) * 2 +
+                  (uint32_t)(8 * dsub + (lane & 7)) * dstride;
+        } else {
+          dstride = 8 * 2;
+          vaddr = st + (stage_bytes >> 1) + o * tile_bytes +
+                  (uint32_t)(8 * dsub + (lane & 7)) * dstride;
+        }
+      } else {
+        if (BS >= 16) {
+          dstride = (uint32_t)BS;
+          vaddr = st + (stage_bytes >> 1) + (uint32_t)(16 * c) + 4 * t + (uint32_t)r * dstride;
+        } else {
+          dstride = 8;
+          vaddr = st + (stage_bytes >> 1) + (t >> 1) * tile_bytes + 4 * (t & 1) + (uint32_t)r * dstride;
+        }
+      }
+      // tail: zero V of tokens past the end (they may hold NaN; attention_kernels.cu:420-430)
+      uint32_t vm0 = 0xffffffffu, vm2 = 0xffffffffu;
+      if (tail) {
+        const int ta = tok0 + (FP8 ? 4 * t : 2 * t);      // tokens of af[0]/af[1]: ta, ta+1
+        const int tb = tok0 + (FP8 ? 4 * t + 2 : 2 * t + 8);  // tokens of af[2]/af[3]: tb, tb+1
+        vm0 = (ta < tok_end ? 0x0000ffffu : 0u) | (ta + 1 < tok_end ? 0xffff0000u : 0u);
+        vm2 = (tb < tok_end ? 0x0000ffffu : 0u) | (tb + 1 < tok_end ? 0xffff0000u : 0u);
+      }
+#pragma unroll
+      for (int dt = 0; dt < KS; ++dt) {
+        if (HEXACT || dt < nks) {
+          uint32_t af[4];
+          if constexpr (!FP8) {
+            ldmatrix_x4(af[0], af[1], af[2], af[3], vaddr + (uint32_t)dt * 16 * dstride);
+          } else {
+            const uint32_t w0 = lds32(vaddr + (uint32_t)(16 * dt) * dstride);
+            const uint32_t w1 = lds32(vaddr + (uint32_t)(16 * dt + 8) * dstride);
+            af[0] = fp8x2_to_T2<T>(w0, a.e5m2);
+            af[2] = fp8x2_to_T2<T>(w0 >> 16, a.e5m2);
+            af[1] = fp8x2_to_T2<T>(w1, a.e5m2);
+            af[3] = fp8x2_to_T2<T>(w1 >> 16, a.e5m2);
+          }
+          if (tail) {
+            af[0] &= vm0;
+            af[1] &= vm0;
+            af[2] &= vm2;
+            af[3] &= vm2;
+          }
+#pragma unroll
+          for (int j = 0; j < NT; ++j) {
+            acc[dt][j][0] *= corr[j][0];
+            acc[dt][j][1] *= corr[j][1];
+            acc[dt][j][2] *= corr[j][0];
+            acc[dt][j][3] *= corr[j][1];
+            mma_16816<T>(acc[dt][j], af, pb0[j], pb1[j]);
+          }
+        }
+      }
+    }
+    __syncwarp();
+    if (it + S < n_items) issue(it + S);
+  }
+
+  // ---- merge the 4 warps' partial softmax states through shared memory ----
+  // per-thread l is partial over the 8 lanes that share t: finish it
+#pragma unroll
+  for (int j = 0; j < NT; ++j)
+#pragma unroll
+    for (int e = 0; e < 2; ++e)
+#pragma unroll
+      for (int off = 4; off <= 16; off <<= 1)
+        l_run[j][e] += __shfl_xor_sync(0xffffffffu, l_run[j][e], off);
+
+  constexpr int NH = 8 * NT;
+  const int DP = D + 4;  // padded row: conflict-free fragment stores
+  // this warp's own ring is drained; reuse it: [NH][DP] fp32 acc, then m[NH], l[NH]
+  float* wacc = reinterpret_cast<float*>(wbase);
+  float* wm = wacc + NH * DP;
+  float* wl = wm + NH;
+#pragma unroll
+  for (int dt = 0; dt < KS; ++dt) {
+    if (HEXACT || dt < nks) {
+#pragma unroll
+      for (int j = 0; j < NT; ++j) {
+        const int h = 8 * j + 2 * t;
+        const int d = 16 * dt + r;
+        wacc[h * DP + d] = acc[dt][j][0];
+        wacc[(h + 1) * DP + d] = acc[dt][j][1];
+        wacc[h * DP + d + 8] = acc[dt][j][2];
+        wacc[(h + 1) * DP + d + 8] = acc[dt][j][3];
+      }
+    }
+  }
+  if (r == 0) {
+#pragma unroll
+    for (int j = 0; j < NT; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        wm[8 * j + 2 * t + e] = m_run[j][e];
+        wl[8 * j + 2 * t + e] = l_run[j][e];
+      }
+  }
+  __syncthreads();
+
+  const size_t wstride = (size_t)S * stage_bytes / sizeof(float);  // floats between warps' areas
+  const float* base = reinterpret_cast<const float*>(smem + 256);
+  const int half_d = D >> 1;
+  for (int idx = tid; idx < NH * half_d; idx += kAttnThreads) {
+    const int h = idx / half_d;
+    const int d2 = idx - h * half_d;
+    const int hg = head_in_group0 + h;
+    if (hg >= G) continue;
+    float mw[kAttnWarps], M = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < kAttnWarps; ++w) {
+      mw[w] = base[w * wstride + NH * DP + h];
+      M = fmaxf(M, mw[w]);
+    }
+    float L = 0.f, o0 = 0.f, o1 = 0.f;
+#pragma unroll
+    for (int w = 0; w < kAttnWarps; ++w) {
+      const float f = mw[w] == -INFINITY ? 0.f : exp2f(mw[w] - M);
+      L = fmaf(base[w * wstride + NH * DP + NH + h], f, L);
+      const float2 v = *reinterpret_cast<const float2*>(&base[w * wstride + h * DP + 2 * d2]);
+      o0 = fmaf(v.x, f, o0);
+      o1 = fmaf(v.y, f, o1);
+    }
+    // attention_kernels.cu:342: inv_sum = 1 / (exp_sum + 1e-6)
+    const float inv = a.v_scale * __fdividef(1.f, L + 1e-6f);
+    const int head = kvh * G + hg;
+    const uint32_t packed = DT<T>::pack2(o0 * inv, o1 * inv);
+    if (partitioned && a.max_num_partitions > 1) {
+      T* dst = reinterpret_cast<T*>(a.tmp_out) +
+               (((int64_t)seq * a.num_heads + head) * a.max_num_partitions + part) * D;
+      *reinterpret_cast<uint32_t*>(dst + 2 * d2) = packed;
+      if (d2 == 0) {
+        const int64_t si = ((int64_t)seq * a.num_heads + head) * a.max_num_partitions + part;
+        a.exp_sums[si] = L;
+        a.max_logits[si] = M * kLn2;  // back to natural-log units
+      }
+    } else {
+      T* dst = reinterpret_cast<T*>(a.out) + ((int64_t)seq * a.num_heads + head) * D;
+      *reinterpret_cast<uint32_t*>(dst + 2 * d2) = packed;
+    }
+  }
+}
+
+template <typename T, bool FP8, int NT, int HMAX, bool HEXACT>
+static int launch_one(const AttnArgs& a, dim3 grid, size_t smem, cudaStream_t stream) {
+  auto kern = paged_attn_mma_kernel<T, FP8, NT, HMAX, HEXACT>;
+  static size_t configured = 0;  // per instantiation; grows monotonically
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      set_error("paged_attention: cannot reserve %zu B of shared memory: %s", smem,
+                cudaGetErrorString(e));
+      return B200_ECUDA;
+    }
+    configured = smem;
+  }
+  kern<<<grid, kAttnThreads, smem, stream>>>(a);
+  return check_launch("paged_attention");
+}
+
+template <typename T>
+int launch_paged_attn_mma(const AttnArgs& a, bool fp8, dim3 grid, size_t smem,
+                          cudaStream_t stream) {
+  const int G = a.num_heads / a.num_kv_heads;
+  const int nt = (G > 8) ? 2 : 1;
+#define B200_ATTN_HEAD(FP8V, NTV)                                                        \
+  if (a.head_size == 128) return launch_one<T, FP8V, NTV, 128, true>(a, grid, smem, stream); \
+  if (a.head_size <= 128) return launch_one<T, FP8V, NTV, 128, false>(a, grid, smem, stream); \
+  return launch_one<T, FP8V, NTV, 256, false>(a, grid, smem, stream);
+  if (fp8) {
+    if (nt == 2) { B200_ATTN_HEAD(true, 2) }
+    B200_ATTN_HEAD(true, 1)
+  } else {
+    if (nt == 2) { B200_ATTN_HEAD(false, 2) }
+    B200_ATTN_HEAD(false, 1)
+  }
+#undef B200_ATTN_HEAD
+}
+
+}  // namespace b200
