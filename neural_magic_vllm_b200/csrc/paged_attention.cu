@@ -263,8 +263,9 @@ static int run_paged_attention(const b200_paged_attention_params* p, bool v2, cu
     const int it_tokens = p->block_size < 16 ? 16 : p->block_size;
     a.stage_bytes = 2 * hs * it_tokens * esz_c;
     const int merge_bytes = 8 * nt * (hs + 4) * 4 + 8 * nt * 8;
-    // ~24 KiB of KV in flight per warp, 2-3 CTAs per SM
-    int stages = (24 * 1024) / a.stage_bytes;
+    // <= 64 KiB of ring per CTA so that 3-4 CTAs (12-16 warps) share an SM: measured faster than
+    // deeper rings with fewer resident warps (profiles/r01_attention.md)
+    int stages = (12 * 1024) / a.stage_bytes;
     if (stages < 2) stages = 2;
     if (stages > kAttnMaxStages) stages = kAttnMaxStages;
     if (const char* ev = getenv("B200_ATTN_STAGES")) {  // tuning knob (bench sweeps)
@@ -272,12 +273,17 @@ static int run_paged_attention(const b200_paged_attention_params* p, bool v2, cu
       if (v >= 2 && v <= kAttnMaxStages) stages = v;
     }
     while (stages * a.stage_bytes < merge_bytes) ++stages;
-    B200_REQUIRE(stages <= kAttnMaxStages, B200_ENOTSUP, "paged_attention: internal stage sizing");
+    // 227 KiB of shared memory per CTA: very large tiles (head 256 x block 32) run single-stage,
+    // the 4 warps still overlap each other's copies
+    constexpr size_t kMaxSmem = 227 * 1024;
+    while (stages > 1 && 256 + (size_t)kAttnWarps * stages * a.stage_bytes > kMaxSmem) --stages;
+    B200_REQUIRE(stages <= kAttnMaxStages && stages * a.stage_bytes >= merge_bytes, B200_ENOTSUP,
+                 "paged_attention: internal stage sizing");
     a.stages = stages;
     const size_t smem = 256 + (size_t)kAttnWarps * stages * a.stage_bytes;
     dim3 grid(p->num_kv_heads * a.q_tiles, p->num_seqs, a.max_num_partitions);
-    rc = p->dtype == B200_F16 ? launch_paged_attn_mma<__half>(a, fp8, grid, smem, stream)
-                              : launch_paged_attn_mma<__nv_bfloat16>(a, fp8, grid, smem, stream);
+    rc = p->dtype == B200_F16 ? launch_paged_attn_mma<__half>(a, p->kv_dtype, grid, smem, stream)
+                              : launch_paged_attn_mma<__nv_bfloat16>(a, p->kv_dtype, grid, smem, stream);
   } else {
     const int toks = v2 ? B200_PARTITION_SIZE : ((p->max_seq_len + 15) / 16) * 16;
     const size_t smem = (size_t)(hs + toks) * sizeof(float);

@@ -50,10 +50,11 @@ struct AttnArgs {
 };
 
 // tensor-core kernels, instantiated in paged_attention_{f16,bf16}.cu
-template <typename T, bool FP8, int NT, int HMAX, bool HEXACT>
+template <typename T, int KV, int NT, int HMAX, bool FAST>
 __global__ void paged_attn_mma_kernel(const AttnArgs a);
 
 template <typename T>
-int launch_paged_attn_mma(const AttnArgs& a, bool fp8, dim3 grid, size_t smem, cudaStream_t stream);
+int launch_paged_attn_mma(const AttnArgs& a, int kv_dtype, dim3 grid, size_t smem,
+                          cudaStream_t stream);
 
 }  // namespace b200

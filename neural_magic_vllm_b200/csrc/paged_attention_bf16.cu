@@ -1,5 +1,5 @@
 // bf16 instantiations of the tensor-core paged attention kernel.
 #include "paged_attention_mma.cuh"
 namespace b200 {
-template int launch_paged_attn_mma<__nv_bfloat16>(const AttnArgs&, bool, dim3, size_t, cudaStream_t);
+template int launch_paged_attn_mma<__nv_bfloat16>(const AttnArgs&, int, dim3, size_t, cudaStream_t);
 }

@@ -1,5 +1,12 @@
 // Tensor-core paged decode attention kernel body (see paged_attention.cuh for the design).
 // Included by paged_attention_f16.cu / paged_attention_bf16.cu, which instantiate it per dtype.
+//
+// Template axes:
+//   T      __half / __nv_bfloat16 (query, output, P.V operand type)
+//   KV     B200_KV_AUTO (cache holds T), B200_KV_FP8_E4M3, B200_KV_FP8_E5M2 (cache holds bytes)
+//   NT     n-tiles of 8 query heads handled per CTA (GQA group <= 8 -> 1, <= 16 -> 2)
+//   HMAX   register budget for the head dimension (128 or 256)
+//   FAST   head_size == HMAX and block_size == 16: every shared-memory offset is an immediate
 #pragma once
 
 #include "paged_attention.cuh"
@@ -31,19 +38,25 @@ __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
   return v;
 }
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "r"(addr));
+  return v;
+}
 
-// two packed fp8 (low 16 bits of v) -> two packed T
-template <typename T>
-__device__ __forceinline__ uint32_t fp8x2_to_T2(uint32_t v, int e5m2) {
+// two packed fp8 (low 16 bits of v) -> two packed T. Exact for both fp8 flavours.
+template <typename T, int KV>
+__device__ __forceinline__ uint32_t fp8x2_to_T2(uint32_t v) {
   uint32_t h;
-  if (e5m2) {
-    // e5m2 is the top byte of an fp16: (b1 b0) -> (b1<<8 | 0, b0<<8 | 0)
-    h = ((v & 0xff00u) << 16) | ((v & 0x00ffu) << 8);
+  if constexpr (KV == B200_KV_FP8_E5M2) {
+    h = __byte_perm(v, 0, 0x1404);  // e5m2 is the top byte of an fp16: (b1 b0) -> (b1,0,b0,0)
   } else {
     unsigned short s = (unsigned short)(v & 0xffffu);
     asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(h) : "h"(s));
   }
-  if constexpr (sizeof(T) == 2 && DT<T>::id == B200_BF16) {
+  if constexpr (DT<T>::id == B200_BF16) {
     __half2 hh = *reinterpret_cast<__half2*>(&h);
     float2 f = __half22float2(hh);
     __nv_bfloat162 b = __floats2bfloat162_rn(f.x, f.y);  // exact: e4m3/e5m2 fit in bf16
@@ -53,12 +66,21 @@ __device__ __forceinline__ uint32_t fp8x2_to_T2(uint32_t v, int e5m2) {
   }
 }
 
-template <typename T, bool FP8, int NT, int HMAX, bool HEXACT>
+template <typename T, int KV>
+__device__ __forceinline__ void fp8x4_to_frag(uint32_t w, uint32_t& lo, uint32_t& hi) {
+  lo = fp8x2_to_T2<T, KV>(w);
+  hi = fp8x2_to_T2<T, KV>(w >> 16);
+}
+
+template <typename T, int KV, int NT, int HMAX, bool FAST>
 __global__ void __launch_bounds__(kAttnThreads)
     paged_attn_mma_kernel(const AttnArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
+  constexpr bool FP8 = KV != B200_KV_AUTO;
   constexpr int KS = HMAX / 16;  // k-steps of QK == d-tiles of PV
   constexpr int ESZ = FP8 ? 1 : 2;
+  // fp8 K rows are read 16 B at a time (4 k-steps per load) when the head dim is a multiple of 64
+  constexpr bool K128 = FP8 && FAST && (HMAX % 64 == 0);
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
   const int r = lane >> 2, t = lane & 3;
@@ -67,8 +89,8 @@ __global__ void __launch_bounds__(kAttnThreads)
   const int qtile = blockIdx.x - kvh * a.q_tiles;
   const int seq = blockIdx.y;
   const int part = blockIdx.z;
-  const int BS = a.block_size;
-  const int D = HEXACT ? HMAX : a.head_size;
+  const int BS = FAST ? 16 : a.block_size;
+  const int D = FAST ? HMAX : a.head_size;
   const int nks = D >> 4;
   const int seq_len = a.sl[seq];
   const bool partitioned = a.partition_size > 0;
@@ -85,10 +107,11 @@ __global__ void __launch_bounds__(kAttnThreads)
 
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);  // [kAttnWarps][kAttnMaxStages]
   const int S = a.stages;
-  const uint32_t stage_bytes = a.stage_bytes;
+  const uint32_t stage_bytes = FAST ? 2u * HMAX * 16 * ESZ : (uint32_t)a.stage_bytes;
   const uint32_t tile_bytes = (uint32_t)D * BS * ESZ;  // one (block, kv head) K or V tile
   uint8_t* wbase = smem + 256 + (size_t)warp * S * stage_bytes;
   const uint32_t wbase_s = smem_u32(wbase);
+  uint64_t* wbar = &full[warp * kAttnMaxStages];
 
   if (tid == 0) {
     for (int i = 0; i < kAttnWarps * kAttnMaxStages; ++i) mbar_init(&full[i], 1);
@@ -113,15 +136,18 @@ __global__ void __launch_bounds__(kAttnThreads)
   const uint8_t* vc = reinterpret_cast<const uint8_t*>(a.vc) + (int64_t)kvh * a.kv_head_stride * ESZ;
   const int64_t blk_bytes = a.kv_block_stride * ESZ;
 
-  auto issue = [&](int i) {  // whole warp calls; lane 0 issues
+  // producer state: item index -> ring slot, without divisions
+  int iss_i = 0, iss_s = 0;
+  auto issue_next = [&]() {  // whole warp calls; lane 0 issues
+    const int i = iss_i;
     if ((i >> 5) != bt_grp) load_bt(i >> 5);
     const int p0 = __shfl_sync(0xffffffffu, bt0, i & 31);
-    const int p1 = __shfl_sync(0xffffffffu, bt1, i & 31);
+    int p1 = 0;
+    if (!FAST && BS < 16) p1 = __shfl_sync(0xffffffffu, bt1, i & 31);
     if (lane == 0) {
-      const int s = i % S;
-      uint8_t* dst = wbase + (size_t)s * stage_bytes;
-      uint64_t* bar = &full[warp * kAttnMaxStages + s];
-      if (BS >= 16) {
+      uint8_t* dst = wbase + (size_t)iss_s * stage_bytes;
+      uint64_t* bar = &wbar[iss_s];
+      if (FAST || BS >= 16) {
         mbar_arrive_expect_tx(bar, 2 * tile_bytes);
         bulk_g2s(dst, kc + p0 * blk_bytes, tile_bytes, bar);
         bulk_g2s(dst + (stage_bytes >> 1), vc + p0 * blk_bytes, tile_bytes, bar);
@@ -137,12 +163,18 @@ __global__ void __launch_bounds__(kAttnThreads)
         }
       }
     }
+    ++iss_i;
+    if (++iss_s == S) iss_s = 0;
   };
 
   // prologue: get the KV stream going before anything else
-  for (int i = 0; i < S && i < n_items; ++i) issue(i);
+  for (int i = 0; i < S && i < n_items; ++i) issue_next();
 
   // ---- Q^T fragments (B operand): heads in N, head dim in K ----
+  // k-slot -> head-dim maps (the same permutation is applied to the K operand):
+  //   16-bit cache : slots {2t,2t+1 | 2t+8,2t+9} of step kk <-> d = 16kk + {2t,2t+1 | 2t+8,2t+9}
+  //   fp8, LDS.32  : d = 16kk + {4t,4t+1 | 4t+2,4t+3}
+  //   fp8, LDS.128 : step kk = 4g+j <-> d = 16(4g+t) + 4j + {0,1 | 2,3}
   const int head_in_group0 = qtile * (8 * NT);
   uint32_t qf[NT][KS][2];
   float alibi2[NT][2];
@@ -155,12 +187,13 @@ __global__ void __launch_bounds__(kAttnThreads)
 #pragma unroll
     for (int kk = 0; kk < KS; ++kk) {
       uint32_t b0 = 0, b1 = 0;
-      if (hv && (HEXACT || kk < nks)) {
+      if (hv && (FAST || kk < nks)) {
         if constexpr (!FP8) {
           b0 = *reinterpret_cast<const uint32_t*>(qp + 16 * kk + 2 * t);
           b1 = *reinterpret_cast<const uint32_t*>(qp + 16 * kk + 8 + 2 * t);
         } else {
-          const uint2 v = *reinterpret_cast<const uint2*>(qp + 16 * kk + 4 * t);
+          const int d0 = K128 ? 16 * (4 * (kk >> 2) + t) + 4 * (kk & 3) : 16 * kk + 4 * t;
+          const uint2 v = *reinterpret_cast<const uint2*>(qp + d0);
           b0 = v.x;
           b1 = v.y;
         }
@@ -197,12 +230,13 @@ __global__ void __launch_bounds__(kAttnThreads)
   const int rho1 = FP8 ? rho0 + 2 : r + 8;
 
   // ---- main loop over this warp's items ----
+  int cs = 0;
+  uint32_t cphase = 0;
   for (int it = 0; it < n_items; ++it) {
-    const int s = it % S;
-    mbar_wait(&full[warp * kAttnMaxStages + s], (uint32_t)((it / S) & 1));
-    const uint32_t st = wbase_s + (uint32_t)s * stage_bytes;
+    mbar_wait(&wbar[cs], cphase);
+    const uint32_t st = wbase_s + (uint32_t)cs * stage_bytes;
     const int item = item_begin + warp + kAttnWarps * it;
-    const int n_chunks = BS <= 16 ? 1 : (BS >> 4);
+    const int n_chunks = (FAST || BS <= 16) ? 1 : (BS >> 4);
     for (int c = 0; c < n_chunks; ++c) {
       const int tok0 = item * IT + 16 * c;
       if (tok0 >= tok_end) break;
@@ -222,7 +256,7 @@ __global__ void __launch_bounds__(kAttnThreads)
         const int o = (lane >> 3) & 1;
         uint32_t kaddr;
         uint32_t gstride;  // bytes between consecutive x-groups (x = 8 elements)
-        if (BS >= 16) {
+        if (FAST || BS >= 16) {
           gstride = (uint32_t)BS * 16;
           kaddr = st + (uint32_t)(16 * c + 8 * o + (lane & 7)) * 16 + (lane >> 4) * gstride;
         } else {
@@ -231,9 +265,29 @@ __global__ void __launch_bounds__(kAttnThreads)
         }
 #pragma unroll
         for (int kk = 0; kk < KS; ++kk) {
-          if (HEXACT || kk < nks) {
+          if (FAST || kk < nks) {
             uint32_t af[4];
             ldmatrix_x4(af[0], af[1], af[2], af[3], kaddr + (uint32_t)kk * 2 * gstride);
+#pragma unroll
+            for (int j = 0; j < NT; ++j) mma_16816<T>(sacc[kk & 1][j], af, qf[j][kk][0], qf[j][kk][1]);
+          }
+        }
+      } else if constexpr (K128) {
+        // one 16-byte row (token, x-group 4g+t) feeds four k-steps
+        const uint32_t k0 = st + (uint32_t)rho0 * 16 + (uint32_t)t * (16 * 16);
+        const uint32_t k1 = st + (uint32_t)rho1 * 16 + (uint32_t)t * (16 * 16);
+#pragma unroll
+        for (int g = 0; g < KS / 4; ++g) {
+          const uint4 w0 = lds128(k0 + g * (4 * 16 * 16));
+          const uint4 w1 = lds128(k1 + g * (4 * 16 * 16));
+          const uint32_t w0a[4] = {w0.x, w0.y, w0.z, w0.w};
+          const uint32_t w1a[4] = {w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const int kk = 4 * g + jj;
+            uint32_t af[4];
+            fp8x4_to_frag<T, KV>(w0a[jj], af[0], af[2]);
+            fp8x4_to_frag<T, KV>(w1a[jj], af[1], af[3]);
 #pragma unroll
             for (int j = 0; j < NT; ++j) mma_16816<T>(sacc[kk & 1][j], af, qf[j][kk][0], qf[j][kk][1]);
           }
@@ -252,14 +306,10 @@ __global__ void __launch_bounds__(kAttnThreads)
         }
 #pragma unroll
         for (int kk = 0; kk < KS; ++kk) {
-          if (HEXACT || kk < nks) {
-            const uint32_t w0 = lds32(k0 + (uint32_t)kk * gstride);
-            const uint32_t w1 = lds32(k1 + (uint32_t)kk * gstride);
+          if (FAST || kk < nks) {
             uint32_t af[4];
-            af[0] = fp8x2_to_T2<T>(w0, a.e5m2);
-            af[2] = fp8x2_to_T2<T>(w0 >> 16, a.e5m2);
-            af[1] = fp8x2_to_T2<T>(w1, a.e5m2);
-            af[3] = fp8x2_to_T2<T>(w1 >> 16, a.e5m2);
+            fp8x4_to_frag<T, KV>(lds32(k0 + (uint32_t)kk * gstride), af[0], af[2]);
+            fp8x4_to_frag<T, KV>(lds32(k1 + (uint32_t)kk * gstride), af[1], af[3]);
 #pragma unroll
             for (int j = 0; j < NT; ++j) mma_16816<T>(sacc[kk & 1][j], af, qf[j][kk][0], qf[j][kk][1]);
           }
@@ -270,6 +320,7 @@ __global__ void __launch_bounds__(kAttnThreads)
       const int tp0 = tok0 + rho0, tp1 = tok0 + rho1;
       uint32_t pb0[NT], pb1[NT];
       float corr[NT][2];
+      bool changed = false;
 #pragma unroll
       for (int j = 0; j < NT; ++j) {
         float sv[4];
@@ -293,6 +344,7 @@ __global__ void __launch_bounds__(kAttnThreads)
           mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, off));
         }
         const float mn0 = fmaxf(m_run[j][0], mx0), mn1 = fmaxf(m_run[j][1], mx1);
+        changed |= (mn0 != m_run[j][0]) | (mn1 != m_run[j][1]);
         // every processed chunk has >= 1 valid token, so mn is finite
         corr[j][0] = exp2f(m_run[j][0] - mn0);
         corr[j][1] = exp2f(m_run[j][1] - mn1);
@@ -306,13 +358,26 @@ __global__ void __launch_bounds__(kAttnThreads)
         pb0[j] = movmatrix_trans(DT<T>::pack2(p0, p1));
         pb1[j] = movmatrix_trans(DT<T>::pack2(p2, p3));
       }
+      // rescale the running output only when some head's maximum moved (rare after the first
+      // few blocks); the vote keeps the branch warp-uniform
+      if (__any_sync(0xffffffffu, changed)) {
+#pragma unroll
+        for (int dt = 0; dt < KS; ++dt)
+#pragma unroll
+          for (int j = 0; j < NT; ++j) {
+            acc[dt][j][0] *= corr[j][0];
+            acc[dt][j][1] *= corr[j][1];
+            acc[dt][j][2] *= corr[j][0];
+            acc[dt][j][3] *= corr[j][1];
+          }
+      }
 
       // ---- O^T[D][8*NT heads] += V^T . P^T ----
-      uint32_t vaddr, dstride;  // fp16: ldmatrix lane address; fp8: row-r address
+      uint32_t vaddr, dstride;  // 16-bit: ldmatrix lane address; fp8: row-r address
       if constexpr (!FP8) {
         const int o = lane >> 4;              // token octet of this lane's matrix
         const int dsub = (lane >> 3) & 1;     // d octet inside the 16-row tile
-        if (BS >= 16) {
+        if (FAST || BS >= 16) {
           dstride = (uint32_t)BS * 2;
           vaddr = st + (stage_bytes >> 1) + (uint32_t)(16 * c + 8 * o) * 2 +
                   (uint32_t)(8 * dsub + (lane & 7)) * dstride;
@@ -322,7 +387,7 @@ __global__ void __launch_bounds__(kAttnThreads)
                   (uint32_t)(8 * dsub + (lane & 7)) * dstride;
         }
       } else {
-        if (BS >= 16) {
+        if (FAST || BS >= 16) {
           dstride = (uint32_t)BS;
           vaddr = st + (stage_bytes >> 1) + (uint32_t)(16 * c) + 4 * t + (uint32_t)r * dstride;
         } else {
@@ -333,24 +398,20 @@ __global__ void __launch_bounds__(kAttnThreads)
       // tail: zero V of tokens past the end (they may hold NaN; attention_kernels.cu:420-430)
       uint32_t vm0 = 0xffffffffu, vm2 = 0xffffffffu;
       if (tail) {
-        const int ta = tok0 + (FP8 ? 4 * t : 2 * t);      // tokens of af[0]/af[1]: ta, ta+1
+        const int ta = tok0 + (FP8 ? 4 * t : 2 * t);          // tokens of af[0]/af[1]: ta, ta+1
         const int tb = tok0 + (FP8 ? 4 * t + 2 : 2 * t + 8);  // tokens of af[2]/af[3]: tb, tb+1
         vm0 = (ta < tok_end ? 0x0000ffffu : 0u) | (ta + 1 < tok_end ? 0xffff0000u : 0u);
         vm2 = (tb < tok_end ? 0x0000ffffu : 0u) | (tb + 1 < tok_end ? 0xffff0000u : 0u);
       }
 #pragma unroll
       for (int dt = 0; dt < KS; ++dt) {
-        if (HEXACT || dt < nks) {
+        if (FAST || dt < nks) {
           uint32_t af[4];
           if constexpr (!FP8) {
             ldmatrix_x4(af[0], af[1], af[2], af[3], vaddr + (uint32_t)dt * 16 * dstride);
           } else {
-            const uint32_t w0 = lds32(vaddr + (uint32_t)(16 * dt) * dstride);
-            const uint32_t w1 = lds32(vaddr + (uint32_t)(16 * dt + 8) * dstride);
-            af[0] = fp8x2_to_T2<T>(w0, a.e5m2);
-            af[2] = fp8x2_to_T2<T>(w0 >> 16, a.e5m2);
-            af[1] = fp8x2_to_T2<T>(w1, a.e5m2);
-            af[3] = fp8x2_to_T2<T>(w1 >> 16, a.e5m2);
+            fp8x4_to_frag<T, KV>(lds32(vaddr + (uint32_t)(16 * dt) * dstride), af[0], af[2]);
+            fp8x4_to_frag<T, KV>(lds32(vaddr + (uint32_t)(16 * dt + 8) * dstride), af[1], af[3]);
           }
           if (tail) {
             af[0] &= vm0;
@@ -359,18 +420,16 @@ __global__ void __launch_bounds__(kAttnThreads)
             af[3] &= vm2;
           }
 #pragma unroll
-          for (int j = 0; j < NT; ++j) {
-            acc[dt][j][0] *= corr[j][0];
-            acc[dt][j][1] *= corr[j][1];
-            acc[dt][j][2] *= corr[j][0];
-            acc[dt][j][3] *= corr[j][1];
-            mma_16816<T>(acc[dt][j], af, pb0[j], pb1[j]);
-          }
+          for (int j = 0; j < NT; ++j) mma_16816<T>(acc[dt][j], af, pb0[j], pb1[j]);
         }
       }
     }
     __syncwarp();
-    if (it + S < n_items) issue(it + S);
+    if (iss_i < n_items) issue_next();
+    if (++cs == S) {
+      cs = 0;
+      cphase ^= 1;
+    }
   }
 
   // ---- merge the 4 warps' partial softmax states through shared memory ----
@@ -391,7 +450,7 @@ __global__ void __launch_bounds__(kAttnThreads)
   float* wl = wm + NH;
 #pragma unroll
   for (int dt = 0; dt < KS; ++dt) {
-    if (HEXACT || dt < nks) {
+    if (FAST || dt < nks) {
 #pragma unroll
       for (int j = 0; j < NT; ++j) {
         const int h = 8 * j + 2 * t;
@@ -457,9 +516,9 @@ __global__ void __launch_bounds__(kAttnThreads)
   }
 }
 
-template <typename T, bool FP8, int NT, int HMAX, bool HEXACT>
+template <typename T, int KV, int NT, int HMAX, bool FAST>
 static int launch_one(const AttnArgs& a, dim3 grid, size_t smem, cudaStream_t stream) {
-  auto kern = paged_attn_mma_kernel<T, FP8, NT, HMAX, HEXACT>;
+  auto kern = paged_attn_mma_kernel<T, KV, NT, HMAX, FAST>;
   static size_t configured = 0;  // per instantiation; grows monotonically
   if (smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -475,23 +534,28 @@ static int launch_one(const AttnArgs& a, dim3 grid, size_t smem, cudaStream_t st
   return check_launch("paged_attention");
 }
 
-template <typename T>
-int launch_paged_attn_mma(const AttnArgs& a, bool fp8, dim3 grid, size_t smem,
-                          cudaStream_t stream) {
+template <typename T, int KV>
+static int launch_kv(const AttnArgs& a, dim3 grid, size_t smem, cudaStream_t stream) {
   const int G = a.num_heads / a.num_kv_heads;
-  const int nt = (G > 8) ? 2 : 1;
-#define B200_ATTN_HEAD(FP8V, NTV)                                                        \
-  if (a.head_size == 128) return launch_one<T, FP8V, NTV, 128, true>(a, grid, smem, stream); \
-  if (a.head_size <= 128) return launch_one<T, FP8V, NTV, 128, false>(a, grid, smem, stream); \
-  return launch_one<T, FP8V, NTV, 256, false>(a, grid, smem, stream);
-  if (fp8) {
-    if (nt == 2) { B200_ATTN_HEAD(true, 2) }
-    B200_ATTN_HEAD(true, 1)
-  } else {
-    if (nt == 2) { B200_ATTN_HEAD(false, 2) }
-    B200_ATTN_HEAD(false, 1)
+  const bool fast = a.head_size == 128 && a.block_size == 16;
+  if (G > 8) {
+    if (fast) return launch_one<T, KV, 2, 128, true>(a, grid, smem, stream);
+    if (a.head_size <= 128) return launch_one<T, KV, 2, 128, false>(a, grid, smem, stream);
+    return launch_one<T, KV, 2, 256, false>(a, grid, smem, stream);
   }
-#undef B200_ATTN_HEAD
+  if (fast) return launch_one<T, KV, 1, 128, true>(a, grid, smem, stream);
+  if (a.head_size <= 128) return launch_one<T, KV, 1, 128, false>(a, grid, smem, stream);
+  return launch_one<T, KV, 1, 256, false>(a, grid, smem, stream);
+}
+
+template <typename T>
+int launch_paged_attn_mma(const AttnArgs& a, int kv_dtype, dim3 grid, size_t smem,
+                          cudaStream_t stream) {
+  switch (kv_dtype) {
+    case B200_KV_AUTO: return launch_kv<T, B200_KV_AUTO>(a, grid, smem, stream);
+    case B200_KV_FP8_E4M3: return launch_kv<T, B200_KV_FP8_E4M3>(a, grid, smem, stream);
+    default: return launch_kv<T, B200_KV_FP8_E5M2>(a, grid, smem, stream);
+  }
 }
 
 }  // namespace b200
