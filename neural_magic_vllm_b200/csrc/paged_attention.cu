@@ -11,48 +11,107 @@ namespace b200 {
 
 // -----------------------------------------------------------------------------------------------
 // v2 reduce: out = sum_p tmp_out[p] * exp_sums[p] * exp(max[p] - gmax) / (sum_p(...) + 1e-6)
-// grid (num_heads, num_seqs), one thread per output pair.
+// One warp per (sequence, head) row; lanes own element pairs; the partition loop is unrolled so
+// all of a row's loads are in flight together.  Launched with programmatic dependent launch: the
+// grid is resident (indices computed, seq_len loaded) before the split-KV kernel drains and only
+// waits at griddepcontrol.wait for its results.
 // -----------------------------------------------------------------------------------------------
+constexpr int kReduceWarps = 4;
+
 template <typename T>
-__global__ void paged_attn_reduce_kernel(T* __restrict__ out, const float* __restrict__ exp_sums,
-                                         const float* __restrict__ max_logits,
-                                         const T* __restrict__ tmp_out,
-                                         const int32_t* __restrict__ seq_lens, const int head_size,
-                                         const int max_num_partitions, const int partition_size) {
-  extern __shared__ float red_w[];  // [num_partitions] rescaled weights
-  __shared__ float s_inv;
+__global__ void __launch_bounds__(kReduceWarps * 32)
+    paged_attn_reduce_kernel(T* __restrict__ out, const float* __restrict__ exp_sums,
+                             const float* __restrict__ max_logits, const T* __restrict__ tmp_out,
+                             const int32_t* __restrict__ seq_lens, const int num_rows,
+                             const int num_heads, const int head_size, const int max_num_partitions,
+                             const int partition_size) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * kReduceWarps + (threadIdx.x >> 5);
+  if (row >= num_rows) return;
+  const int seq = row / num_heads;
+  const int seq_len = seq_lens[seq];
+  const int np = min((seq_len + partition_size - 1) / partition_size, max_num_partitions);
+  const float* ml = max_logits + (int64_t)row * max_num_partitions;
+  const float* es = exp_sums + (int64_t)row * max_num_partitions;
+  const uint32_t* tp =
+      reinterpret_cast<const uint32_t*>(tmp_out + (int64_t)row * max_num_partitions * head_size);
+  uint32_t* op = reinterpret_cast<uint32_t*>(out + (int64_t)row * head_size);
+  const int half_d = head_size >> 1;  // element pairs per partition row
+  constexpr int MAXP = 4;             // pairs per lane: head_size <= 256
+
+  asm volatile("griddepcontrol.wait;" ::: "memory");  // results of the split-KV kernel are visible
+
+  float gmax = -FLT_MAX;
+  for (int p = lane; p < np; p += 32) gmax = fmaxf(gmax, ml[p]);
+  gmax = warp_max(gmax);
+  float acc[MAXP][2];
+#pragma unroll
+  for (int i = 0; i < MAXP; ++i) acc[i][0] = acc[i][1] = 0.f;
+  float gsum = 0.f;
+  for (int p0 = 0; p0 < np; p0 += 32) {
+    const int pl = p0 + lane;
+    const float w = pl < np ? es[pl] * __expf(ml[pl] - gmax) : 0.f;
+    gsum += w;
+    const int cnt = min(32, np - p0);
+    for (int q0 = 0; q0 < cnt; q0 += 8) {
+      uint32_t v[8][MAXP];
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i) {
+          const int d2 = lane + 32 * i;
+          v[q][i] = (q0 + q < cnt && d2 < half_d) ? tp[(int64_t)(p0 + q0 + q) * half_d + d2] : 0u;
+        }
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float wq = __shfl_sync(0xffffffffu, w, (q0 + q) & 31);
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i) {
+          if constexpr (sizeof(T) == 2) {
+            const T* e = reinterpret_cast<const T*>(&v[q][i]);
+            acc[i][0] = fmaf(DT<T>::to_f(e[0]), wq, acc[i][0]);
+            acc[i][1] = fmaf(DT<T>::to_f(e[1]), wq, acc[i][1]);
+          }
+        }
+      }
+    }
+  }
+  gsum = warp_sum(gsum);
+  const float inv = np > 0 ? __fdividef(1.f, gsum + 1e-6f) : 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXP; ++i) {
+    const int d2 = lane + 32 * i;
+    if constexpr (sizeof(T) == 2) {
+      if (d2 < half_d) op[d2] = DT<T>::pack2(acc[i][0] * inv, acc[i][1] * inv);
+    }
+  }
+}
+
+// fp32 rows (SIMT path only): one thread per element
+__global__ void paged_attn_reduce_f32_kernel(float* __restrict__ out,
+                                             const float* __restrict__ exp_sums,
+                                             const float* __restrict__ max_logits,
+                                             const float* __restrict__ tmp_out,
+                                             const int32_t* __restrict__ seq_lens,
+                                             const int head_size, const int max_num_partitions,
+                                             const int partition_size) {
   const int head = blockIdx.x, seq = blockIdx.y, num_heads = gridDim.x;
   const int seq_len = seq_lens[seq];
   const int np = min((seq_len + partition_size - 1) / partition_size, max_num_partitions);
   const int64_t row = (int64_t)seq * num_heads + head;
   const float* ml = max_logits + row * max_num_partitions;
   const float* es = exp_sums + row * max_num_partitions;
-  const T* tp = tmp_out + row * max_num_partitions * head_size;
-  T* op = out + row * head_size;
-  if (np <= 0) {
-    for (int d = threadIdx.x; d < head_size; d += blockDim.x) op[d] = DT<T>::from_f(0.f);
-    return;
-  }
-  if (threadIdx.x < 32) {
-    const int lane = threadIdx.x;
-    float gmax = -FLT_MAX;
-    for (int p = lane; p < np; p += 32) gmax = fmaxf(gmax, ml[p]);
-    gmax = warp_max(gmax);
-    float gsum = 0.f;
-    for (int p = lane; p < np; p += 32) {
-      const float w = es[p] * __expf(ml[p] - gmax);
-      red_w[p] = w;
-      gsum += w;
-    }
-    gsum = warp_sum(gsum);
-    if (lane == 0) s_inv = __fdividef(1.f, gsum + 1e-6f);
-  }
-  __syncthreads();
-  const float inv = s_inv;
+  const float* tp = tmp_out + row * max_num_partitions * head_size;
+  float gmax = -FLT_MAX;
+  for (int p = 0; p < np; ++p) gmax = fmaxf(gmax, ml[p]);
+  float gsum = 0.f;
+  for (int p = 0; p < np; ++p) gsum += es[p] * __expf(ml[p] - gmax);
+  const float inv = np > 0 ? __fdividef(1.f, gsum + 1e-6f) : 0.f;
   for (int d = threadIdx.x; d < head_size; d += blockDim.x) {
     float acc = 0.f;
-    for (int p = 0; p < np; ++p) acc = fmaf(DT<T>::to_f(tp[(int64_t)p * head_size + d]), red_w[p], acc);
-    op[d] = DT<T>::from_f(acc * inv);
+    for (int p = 0; p < np; ++p)
+      acc = fmaf(tp[(int64_t)p * head_size + d], es[p] * __expf(ml[p] - gmax), acc);
+    out[row * head_size + d] = acc * inv;
   }
 }
 
@@ -295,21 +354,41 @@ static int run_paged_attention(const b200_paged_attention_params* p, bool v2, cu
   if (rc != B200_OK) return rc;
 
   if (v2 && a.max_num_partitions > 1) {
-    dim3 grid(p->num_heads, p->num_seqs);
-    const int threads = hs <= 64 ? 64 : 128;
-    const size_t smem = (size_t)a.max_num_partitions * sizeof(float);
-#define B200_REDUCE(T)                                                                          \
-  paged_attn_reduce_kernel<T><<<grid, threads, smem, stream>>>(                                  \
-      (T*)p->out, p->exp_sums, p->max_logits, (const T*)p->tmp_out, p->seq_lens, hs,             \
-      a.max_num_partitions, B200_PARTITION_SIZE)
-    if (p->dtype == B200_F16) {
-      B200_REDUCE(__half);
-    } else if (p->dtype == B200_BF16) {
-      B200_REDUCE(__nv_bfloat16);
-    } else {
-      B200_REDUCE(float);
+    if (p->dtype == B200_F32) {
+      dim3 grid(p->num_heads, p->num_seqs);
+      paged_attn_reduce_f32_kernel<<<grid, 128, 0, stream>>>(
+          (float*)p->out, p->exp_sums, p->max_logits, (const float*)p->tmp_out, p->seq_lens, hs,
+          a.max_num_partitions, B200_PARTITION_SIZE);
+      return check_launch("paged_attention_v2 reduce");
     }
-#undef B200_REDUCE
+    const int rows = p->num_seqs * p->num_heads;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((rows + kReduceWarps - 1) / kReduceWarps);
+    cfg.blockDim = dim3(kReduceWarps * 32);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t le;
+    if (p->dtype == B200_F16) {
+      le = cudaLaunchKernelEx(&cfg, paged_attn_reduce_kernel<__half>, (__half*)p->out,
+                              (const float*)p->exp_sums, (const float*)p->max_logits,
+                              (const __half*)p->tmp_out, p->seq_lens, rows, (int)p->num_heads, hs,
+                              a.max_num_partitions, (int)B200_PARTITION_SIZE);
+    } else {
+      le = cudaLaunchKernelEx(&cfg, paged_attn_reduce_kernel<__nv_bfloat16>, (__nv_bfloat16*)p->out,
+                              (const float*)p->exp_sums, (const float*)p->max_logits,
+                              (const __nv_bfloat16*)p->tmp_out, p->seq_lens, rows,
+                              (int)p->num_heads, hs, a.max_num_partitions, (int)B200_PARTITION_SIZE);
+    }
+    if (le != cudaSuccess) {
+      cudaGetLastError();
+      set_error("paged_attention_v2 reduce: launch failed: %s", cudaGetErrorString(le));
+      return B200_ECUDA;
+    }
     return check_launch("paged_attention_v2 reduce");
   }
   return B200_OK;

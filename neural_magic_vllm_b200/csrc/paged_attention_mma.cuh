@@ -169,6 +169,9 @@ __global__ void __launch_bounds__(kAttnThreads)
 
   // prologue: get the KV stream going before anything else
   for (int i = 0; i < S && i < n_items; ++i) issue_next();
+  // programmatic dependent launch: the v2 reduce grid may become resident from here on (it
+  // still waits for this grid to finish before reading tmp_out)
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
   // ---- Q^T fragments (B operand): heads in N, head dim in K ----
   // k-slot -> head-dim maps (the same permutation is applied to the K operand):
