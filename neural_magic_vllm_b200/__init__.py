@@ -27,7 +27,7 @@ def load_extension() -> None:
     if not (os.path.exists(LIB_PATH) and os.path.exists(EXT_PATH)):
         raise ImportError(
             "neural_magic_vllm_b200: the CUDA extension is not built "
-            f"({LIB_PATH} / {EXT_PATH} missing). Run `python -m neural_magic_vllm_b200.build` "
+            f"({LIB_PATH} / {EXT_PATH} missing). Run `python neural_magic_vllm_b200/build.py` "
             "(needs nvcc; no GPU required). There is no CPU or eager fallback.")
     import torch
     torch.ops.load_library(EXT_PATH)
