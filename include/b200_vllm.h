@@ -181,9 +181,15 @@ typedef struct {
   int32_t a_scales_numel, b_scales_numel; /* 1 = per-tensor, m / n = per-token / per-channel */
   int32_t qtype;     /* b200_qtype */
   int32_t out_dtype; /* B200_F16 / B200_BF16 */
+  /* optional split-K scratch (device, 16-byte aligned) used only when m*n tiles cannot fill the
+   * GPU (weight-streaming decode); NULL / too small => no split-K. Contents are don't-care. */
+  void* workspace;
+  int64_t workspace_bytes;
 } b200_scaled_mm_params;
 
 B200_API int b200_scaled_mm(const b200_scaled_mm_params* p, void* stream);
+/* bytes of workspace that let b200_scaled_mm fill the GPU for this shape (0 = none needed) */
+B200_API int64_t b200_scaled_mm_workspace_bytes(int32_t m, int32_t n, int32_t k);
 /* cutlass_scaled_mm_supports_fp8 (scaled_mm_entry.cu:32-46): 1 for capability >= 89 */
 B200_API int b200_scaled_mm_supports_fp8(int32_t cuda_device_capability);
 
@@ -212,9 +218,19 @@ typedef struct {
   int32_t num_bits;   /* 4 or 8 */
   int32_t is_k_full;
   int32_t dtype;      /* B200_F16 / B200_BF16 */
+  /* optional split-K scratch (fp32 partials) for the weight-streaming regime; NULL => no split-K */
+  void* splitk_ws;
+  int64_t splitk_ws_bytes;
 } b200_gptq_marlin_gemm_params;
 
 B200_API int b200_gptq_marlin_gemm(const b200_gptq_marlin_gemm_params* p, void* stream);
+B200_API int64_t b200_gptq_marlin_gemm_workspace_bytes(int32_t m, int32_t n, int32_t k);
+/* test hook: out [size_k, size_n] (dtype) = dequantised weights, produced by the same unpack /
+ * scale device code the GEMM uses (bit-exact against the reference's w_ref,
+ * quant_utils.py:73). No act-order. */
+B200_API int b200_marlin_dequant(void* out, const uint32_t* b_q_weight, const void* b_scales,
+                                 int32_t size_k, int32_t size_n, int32_t num_groups,
+                                 int32_t num_bits, int32_t dtype, void* stream);
 
 /* 2:4-sparse Marlin.  Replaces gptq_marlin_24_gemm
  * (csrc/quantization/marlin/sparse/marlin_24_cuda_kernel.cu:1015-1125). fp16 only. */
@@ -228,6 +244,8 @@ typedef struct {
   int32_t size_m, size_n, size_k;
   int32_t num_groups;
   int32_t num_bits;
+  void* splitk_ws; /* optional fp32 split-K scratch, as in b200_gptq_marlin_gemm_params */
+  int64_t splitk_ws_bytes;
 } b200_gptq_marlin_24_gemm_params;
 
 B200_API int b200_gptq_marlin_24_gemm(const b200_gptq_marlin_24_gemm_params* p, void* stream);

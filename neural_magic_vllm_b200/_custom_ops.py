@@ -9,7 +9,7 @@ Reference line numbers refer to ``vllm/_custom_ops.py``.
 """
 from __future__ import annotations
 
-from typing import List, Optional, Tuple
+from typing import List, Optional, Tuple, Type
 
 import torch
 
@@ -48,6 +48,64 @@ def paged_attention_v2(out, exp_sum, max_logits, tmp_out, query, key_cache, valu
                           alibi_slopes, kv_cache_dtype, kv_scale, tp_rank,
                           blocksparse_local_blocks, blocksparse_vert_stride,
                           blocksparse_block_size, blocksparse_head_sliding_step)
+
+
+# ------------------------------------------------------------------ quantized linears (:208-352)
+def gptq_marlin_24_gemm(a, b_q_weight, b_meta, b_scales, workspace, num_bits: int, size_m: int,
+                        size_n: int, size_k: int) -> torch.Tensor:  # :208-215
+    return _C.gptq_marlin_24_gemm(a, b_q_weight, b_meta, b_scales, workspace, num_bits, size_m,
+                                  size_n, size_k)
+
+
+def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:  # :219-220
+    return _C.cutlass_scaled_mm_supports_fp8(cuda_device_capability)
+
+
+def cutlass_scaled_mm(a, b, scale_a, scale_b, out_dtype: Type[torch.dtype],
+                      bias: Optional[torch.Tensor] = None) -> torch.Tensor:  # :223-238
+    assert (b.shape[0] % 16 == 0 and b.shape[1] % 16 == 0)
+    assert (out_dtype is torch.bfloat16 or out_dtype is torch.float16)
+    out = torch.empty((a.shape[0], b.shape[1]), dtype=out_dtype, device=a.device)
+    _C.cutlass_scaled_mm(out, a, b, scale_a, scale_b, bias)
+    return out
+
+
+def gptq_marlin_repack(b_q_weight, perm, size_k: int, size_n: int, num_bits: int) -> torch.Tensor:
+    return _C.gptq_marlin_repack(b_q_weight, perm, size_k, size_n, num_bits)  # :257-261
+
+
+def gptq_marlin_gemm(a, b_q_weight, b_scales, g_idx, perm, workspace, num_bits: int, size_m: int,
+                     size_n: int, size_k: int, is_k_full: bool) -> torch.Tensor:  # :264-271
+    return _C.gptq_marlin_gemm(a, b_q_weight, b_scales, g_idx, perm, workspace, num_bits, size_m,
+                               size_n, size_k, is_k_full)
+
+
+def scaled_fp8_quant(input: torch.Tensor, scale: Optional[torch.Tensor] = None,
+                     batch_dim_padding: Optional[int] = None
+                     ) -> Tuple[torch.Tensor, torch.Tensor]:  # :284-320
+    if batch_dim_padding:
+        shape = (max(batch_dim_padding, input.shape[0]), *input.shape[1:])
+        output = torch.empty(shape, device=input.device, dtype=torch.float8_e4m3fn)
+    else:
+        output = torch.empty_like(input, dtype=torch.float8_e4m3fn)
+    if scale is None:
+        scale = torch.zeros(1, device=input.device, dtype=torch.float32)
+        _C.dynamic_scaled_fp8_quant(output, input, scale)
+    else:
+        _C.static_scaled_fp8_quant(output, input, scale)
+    return output, scale
+
+
+def scaled_int8_quant(input: torch.Tensor, scale: Optional[torch.Tensor] = None
+                      ) -> Tuple[torch.Tensor, torch.Tensor]:  # :324-350
+    output = torch.empty_like(input, dtype=torch.int8)
+    if scale is not None:
+        _C.static_scaled_int8_quant(output, input, scale)
+        return output, scale
+    input_scales = torch.empty((input.numel() // input.shape[-1], 1), device=input.device,
+                               dtype=torch.float32)
+    _C.dynamic_scaled_int8_quant(output, input, input_scales)
+    return output, input_scales
 
 
 # ------------------------------------------------------------------ cache ops (:370-420)

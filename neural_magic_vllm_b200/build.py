@@ -78,7 +78,7 @@ def build_lib(verbose: bool = False) -> str:
             list(ex.map(_run, jobs))
     if jobs or _newer(LIB, objs):
         _run([nvcc, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a",
-              "-Xcompiler", "-fPIC", "-lcuda"])
+              "-Xcompiler", "-fPIC"])
     return LIB
 
 

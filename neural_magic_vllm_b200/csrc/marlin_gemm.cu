@@ -1,0 +1,504 @@
+// gptq_marlin_gemm on tcgen05 / TMEM (sm_100a): C[M,N] = A[M,K] * dequant(W), W 4-bit or 8-bit
+// Marlin-repacked with fp16 / bf16 group scales, symmetric (zero point 8 / 128), optional
+// act-order.  Replaces csrc/quantization/gptq_marlin/gptq_marlin.cu:1726-1866 (mma.sync Marlin).
+//
+// One CTA computes a 128 (n) x BM (tokens) tile; the weights are the MMA *A* operand:
+//   warp 0      bulk-async (TMA engine) producer: packed weights (4 x 1 KiB rows of the Marlin
+//               tensor per 64-k stage), the group-scale rows of the stage, and the activation
+//               tile through a 2-D tensor map (128-byte swizzle)
+//   warps 2..9  dequant: LDS.128 packed words -> lop3 / hfma2 exact (q - zp) -> x group scale
+//               (one rounding: the dequantised tile is bit-identical to the reference's w_ref)
+//               -> stmatrix into the K-major swizzled operand tile -> fence.proxy.async
+//   warp 1      one thread issues tcgen05.mma (M=128, N=BM, K=16 x4 per stage), fp32 in TMEM
+//   warps 2..5  epilogue: tcgen05.ld -> fp16/bf16 -> C (or fp32 split-K partials)
+// Decode (small M) is weight streaming: BM = 16..64, split-K fills the 148 SMs; HBM traffic is
+// the packed bytes, read exactly once.
+#include "marlin_dequant.cuh"
+#include "umma.cuh"
+
+namespace b200 {
+namespace {
+
+using namespace umma;
+using namespace marlin;
+
+constexpr int kTileN = 128;
+constexpr int kStageK = 64;  // k per stage (128 bytes of fp16/bf16)
+constexpr int kDequantWarps = 8;
+constexpr int kThreads = 64 + kDequantWarps * 32;
+constexpr int kAStages = 3;             // dequantised operand ring
+constexpr int kATileBytes = kTileN * 128;  // 16 KiB
+constexpr int kMaxScaleRows = 4;        // group_size >= 16 -> at most 4 groups per 64-k stage
+
+struct MarlinArgs {
+  void* c;
+  float* partial;  // split-K partials [splits, M, N] or nullptr
+  const uint32_t* w;
+  const void* scales;
+  const int32_t* g_idx;  // act-order: group of every (sorted) k row; nullptr otherwise
+  int m, n, k;
+  int num_groups, group_size;  // group_size = k when num_groups == 1
+  int kb_per_split, num_kb;
+  int w_evict_first;
+};
+
+template <int BITS, int BM>
+struct Plan {
+  static constexpr int kPackedBytes = kStageK * kTileN * BITS / 8;  // 4 KiB / 8 KiB
+  static constexpr int kScaleBytes = kMaxScaleRows * kTileN * 2;    // 1 KiB
+  static constexpr int kXBytes = BM * 128;
+  static constexpr int kStageBytes = kPackedBytes + kScaleBytes + kXBytes;  // multiple of 1 KiB
+  static constexpr int kBudget = (BM <= 64 ? 100 : 200) * 1024 - kAStages * kATileBytes;
+  static constexpr int kStages = kBudget / kStageBytes > 8 ? 8 : kBudget / kStageBytes;
+  static constexpr int kBytes = kStages * kStageBytes + kAStages * kATileBytes + 1024 + 512;
+  static_assert(kStages >= 2, "pipeline too shallow");
+};
+
+template <int BITS, int BM, typename T, bool ACT_ORDER>
+__global__ void __launch_bounds__(kThreads, 1)
+marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs args) {
+  using P = Plan<BITS, BM>;
+  constexpr int kStages = P::kStages;
+  constexpr uint32_t kTmemCols = BM < 32 ? 32 : BM;
+  constexpr int KIND = DT<T>::id == B200_F16 ? KIND_F16 : KIND_BF16;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_tiles = smem;                               // kAStages x 16 KiB (1024-aligned)
+  uint8_t* stages = smem + kAStages * kATileBytes;       // kStages x {X | packed | scales}
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stages + kStages * P::kStageBytes);
+  uint64_t* full_p = bars;
+  uint64_t* empty_p = full_p + kStages;
+  uint64_t* full_a = empty_p + kStages;
+  uint64_t* empty_a = full_a + kAStages;
+  uint64_t* tmem_full = empty_a + kAStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM;
+  const int n0 = blockIdx.y * kTileN;
+  const int split = blockIdx.z;
+  const int kb_begin = split * args.kb_per_split;
+  const int kb_end = min(kb_begin + args.kb_per_split, args.num_kb);
+  const int n_valid = min(kTileN, args.n - n0);  // multiple of 64
+  const bool grouped = args.num_groups > 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_x);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_p[s], 1);
+      mbar_init(&empty_p[s], kDequantWarps + 1);
+    }
+    for (int s = 0; s < kAStages; ++s) {
+      mbar_init(&full_a[s], kDequantWarps);
+      mbar_init(&empty_a[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ======================= producer =======================
+    if (lane == 0) {
+      const uint64_t pol_w = args.w_evict_first ? l2_policy_evict_first() : l2_policy_evict_last();
+      const uint64_t pol_x = l2_policy_evict_last();
+      constexpr int kWordsPerN = 16 * BITS / 32;  // int32 per column per 16-row k-tile
+      const int64_t row_words = (int64_t)args.n * kWordsPerN;
+      const uint32_t row_bytes = (uint32_t)n_valid * kWordsPerN * 4;
+      const uint32_t scale_row_bytes = (uint32_t)n_valid * 2;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        mbar_wait_bounded(&empty_p[stage], phase ^ 1);
+        uint8_t* x_dst = stages + stage * P::kStageBytes;
+        uint8_t* w_dst = x_dst + P::kXBytes;
+        uint8_t* s_dst = w_dst + P::kPackedBytes;
+        int g_lo = 0, g_rows = 0;
+        if (grouped && !ACT_ORDER) {
+          g_lo = (kb * kStageK) / args.group_size;
+          g_rows = (kb * kStageK + kStageK - 1) / args.group_size - g_lo + 1;
+        }
+        mbar_arrive_expect_tx(&full_p[stage], P::kXBytes + 4 * row_bytes + g_rows * scale_row_bytes);
+        tma_load_2d(x_dst, &tm_x, kb * kStageK, m0, &full_p[stage], pol_x);
+#pragma unroll
+        for (int kt = 0; kt < 4; ++kt)
+          bulk_g2s_hint(w_dst + kt * (P::kPackedBytes / 4),
+                        args.w + (int64_t)(kb * 4 + kt) * row_words + (int64_t)n0 * kWordsPerN,
+                        row_bytes, &full_p[stage], pol_w);
+        for (int g = 0; g < g_rows; ++g)
+          bulk_g2s_hint(s_dst + g * (kTileN * 2),
+                        reinterpret_cast<const uint16_t*>(args.scales) + (int64_t)(g_lo + g) * args.n + n0,
+                        scale_row_bytes, &full_p[stage], pol_x);
+        if (++stage == kStages) stage = 0, phase ^= 1;
+      }
+    }
+  } else if (warp == 1) {
+    // ======================= MMA issuer =======================
+    if (lane == 0) {
+      constexpr uint32_t idesc = instr_desc<KIND>(kTileN, BM);
+      int stage = 0, as = 0;
+      uint32_t phase = 0, aphase = 0;
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        mbar_wait_bounded(&full_p[stage], phase);  // activation tile landed
+        mbar_wait_bounded(&full_a[as], aphase);    // dequantised weights written
+        fence_after_sync();
+        const uint64_t dw = smem_desc_sw128(smem_u32(a_tiles + as * kATileBytes));
+        const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          mma_ss<KIND>(tmem_base, desc_advance(dw, k * 32), desc_advance(dx, k * 32), idesc,
+                       (kb > kb_begin || k > 0) ? 1u : 0u);
+        mma_commit(&empty_a[as]);
+        mma_commit(&empty_p[stage]);
+        if (++stage == kStages) stage = 0, phase ^= 1;
+        if (++as == kAStages) as = 0, aphase ^= 1;
+      }
+      mma_commit(tmem_full);
+    }
+  } else {
+    // ======================= dequant (8 warps) + epilogue (first 4 of them) ==================
+    const int dw = warp - 2;      // 0..7
+    const int kt = dw >> 1;       // k-tile of the stage (16 rows)
+    const int nt = dw & 1;        // 64-column half of the tile
+    const int a_row = lane >> 2;  // n offset inside an 8-row group
+    const bool nt_valid = nt * 64 < n_valid;
+    // stmatrix row address of this lane: matrix q = lane/8 (b = q>>1, high-k = q&1), row r = lane%8
+    const int q = lane >> 3, r = lane & 7;
+    const uint32_t st_off = (uint32_t)((nt * 64 + 8 * (q >> 1) + r) * 128 + (((kt * 2 + (q & 1)) ^ r) << 4));
+    // single-group scales live in registers for the whole kernel
+    uint32_t sc[8];  // sc[2*j + b]: scale of n = 16 j + a_row + 8 b, duplicated in both halves
+#pragma unroll
+    for (int i = 0; i < 8; ++i) sc[i] = DT<T>::pack2(1.f, 1.f);
+    if (!grouped && nt_valid) {
+      const uint16_t* s = reinterpret_cast<const uint16_t*>(args.scales);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int n = n0 + nt * 64 + 16 * (i >> 1) + a_row + 8 * (i & 1);
+        const uint32_t v = s[scale_pos_single(n)];
+        sc[i] = v | (v << 16);
+      }
+    }
+    int cur_group = -1;
+    int stage = 0, as = 0;
+    uint32_t phase = 0, aphase = 0;
+    for (int kb = kb_begin; kb < kb_end; ++kb) {
+      mbar_wait_bounded(&full_p[stage], phase);
+      const uint8_t* w_src = stages + stage * P::kStageBytes + P::kXBytes;
+      const uint8_t* s_src = w_src + P::kPackedBytes;
+      uint32_t words[BITS == 4 ? 4 : 8];
+      {
+        const uint4* p = reinterpret_cast<const uint4*>(w_src + kt * (P::kPackedBytes / 4) +
+                                                        nt * (P::kPackedBytes / 8)) + lane * (BITS / 4);
+        uint4 v0 = p[0];
+        words[0] = v0.x, words[1] = v0.y, words[2] = v0.z, words[3] = v0.w;
+        if constexpr (BITS == 8) {
+          uint4 v1 = p[1];
+          words[4] = v1.x, words[5] = v1.y, words[6] = v1.z, words[7] = v1.w;
+        }
+      }
+      if (grouped && !ACT_ORDER) {
+        const int g = (kb * kStageK + kt * 16) / args.group_size;
+        if (g != cur_group) {  // warp-uniform
+          cur_group = g;
+          const int g_lo = (kb * kStageK) / args.group_size;
+          const uint4 v = *reinterpret_cast<const uint4*>(s_src + (g - g_lo) * (kTileN * 2) +
+                                                          (nt * 64 + 8 * a_row) * 2);
+          sc[0] = dup16(v.x, 0), sc[1] = dup16(v.x, 1), sc[2] = dup16(v.y, 0), sc[3] = dup16(v.y, 1);
+          sc[4] = dup16(v.z, 0), sc[5] = dup16(v.z, 1), sc[6] = dup16(v.w, 0), sc[7] = dup16(v.w, 1);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_p[stage]);  // packed words + scales are in registers
+      mbar_wait_bounded(&empty_a[as], aphase ^ 1);
+      const uint32_t a_base = smem_u32(a_tiles + as * kATileBytes) + st_off;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint32_t rg[4];
+        if constexpr (BITS == 4) {
+          unpack4<T>(words[j], rg);
+        } else {
+          unpack8<T>(words[2 * j], rg[0], rg[1]);
+          unpack8<T>(words[2 * j + 1], rg[2], rg[3]);
+        }
+        if constexpr (ACT_ORDER) {
+          // every k row may belong to a different group: scale each element separately
+          const uint16_t* s = reinterpret_cast<const uint16_t*>(args.scales);
+          const int kg = kb * kStageK + kt * 16 + 2 * (lane & 3);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int kk = kg + ((e & 1) << 3);
+            const int n = n0 + nt * 64 + 16 * j + a_row + 8 * (e >> 1);
+            uint32_t s2 = 0;
+            if (nt_valid) {
+              const int pos = scale_pos_grouped(n);
+              const uint32_t s_lo = s[(int64_t)args.g_idx[kk] * args.n + pos];
+              const uint32_t s_hi = s[(int64_t)args.g_idx[kk + 1] * args.n + pos];
+              s2 = s_lo | (s_hi << 16);
+            }
+            rg[e] = mul2<T>(rg[e], s2);
+          }
+        } else {
+          rg[0] = mul2<T>(rg[0], sc[2 * j]);
+          rg[1] = mul2<T>(rg[1], sc[2 * j]);
+          rg[2] = mul2<T>(rg[2], sc[2 * j + 1]);
+          rg[3] = mul2<T>(rg[3], sc[2 * j + 1]);
+        }
+        stmatrix_x4(a_base + j * (16 * 128), rg);
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full_a[as]);
+      if (++stage == kStages) stage = 0, phase ^= 1;
+      if (++as == kAStages) as = 0, aphase ^= 1;
+    }
+    if (dw < 4) {
+      const int quarter = warp & 3;
+      const int n = n0 + quarter * 32 + lane;
+      mbar_wait_bounded(tmem_full, 0);
+      fence_after_sync();
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll 1
+      for (int c = 0; c < BM / 16; ++c) {
+        uint32_t rr[16];
+        tmem_ld16(taddr + c * 16, rr);
+        tmem_ld_wait();
+        if (n < args.n) {
+          if (args.partial != nullptr) {
+            float* ws = args.partial + ((int64_t)split * args.m) * args.n;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int mm = m0 + c * 16 + j;
+              if (mm < args.m) ws[(int64_t)mm * args.n + n] = __uint_as_float(rr[j]);
+            }
+          } else {
+            T* out = reinterpret_cast<T*>(args.c);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int mm = m0 + c * 16 + j;
+              if (mm < args.m) out[(int64_t)mm * args.n + n] = DT<T>::from_f(__uint_as_float(rr[j]));
+            }
+          }
+        }
+      }
+      fence_before_sync();
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    fence_after_sync();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// act-order: a_tmp[m, k'] = a[m, perm[k']] (gptq_marlin.cu:345-394 permute_cols_kernel)
+template <typename T>
+__global__ void __launch_bounds__(256) permute_cols_kernel(T* __restrict__ dst, const T* __restrict__ src,
+                                                           const int32_t* __restrict__ perm, int m,
+                                                           int k, int64_t lda) {
+  const int row = blockIdx.x;
+  if (row >= m) return;
+  for (int c = threadIdx.x; c < k; c += blockDim.x) dst[(int64_t)row * k + c] = src[(int64_t)row * lda + perm[c]];
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) splitk_sum_kernel(T* __restrict__ out, const float* __restrict__ ws,
+                                                         int64_t total, int splits) {
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < total;
+       i += (int64_t)gridDim.x * blockDim.x * 4) {
+    float4 acc = *reinterpret_cast<const float4*>(ws + i);
+    for (int s = 1; s < splits; ++s) {
+      const float4 v = *reinterpret_cast<const float4*>(ws + (int64_t)s * total + i);
+      acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+    }
+    uint2 o;
+    o.x = DT<T>::pack2(acc.x, acc.y);
+    o.y = DT<T>::pack2(acc.z, acc.w);
+    *reinterpret_cast<uint2*>(out + i) = o;
+  }
+}
+
+// test hook: materialise the dequantised weight [K, N] with the SAME unpack/scale code the GEMM
+// uses, so tests can check it bit-for-bit against the reference's w_ref.
+template <int BITS, typename T>
+__global__ void __launch_bounds__(32) marlin_dequant_kernel(T* __restrict__ out, const uint32_t* __restrict__ w,
+                                                            const uint16_t* __restrict__ scales, int k,
+                                                            int n, int num_groups) {
+  const int kt = blockIdx.y, nt = blockIdx.x, lane = threadIdx.x;
+  constexpr int kWords = 16 * 64 * BITS / 32;
+  const uint32_t* src = w + (int64_t)kt * (n * 16 * BITS / 32) + (int64_t)nt * kWords + lane * (BITS == 4 ? 4 : 8);
+  const int group_size = k / num_groups;
+  const int g = (kt * 16) / group_size;
+  const int a_row = lane >> 2;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint32_t rg[4];
+    if constexpr (BITS == 4) {
+      unpack4<T>(src[j], rg);
+    } else {
+      unpack8<T>(src[2 * j], rg[0], rg[1]);
+      unpack8<T>(src[2 * j + 1], rg[2], rg[3]);
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int nn = nt * 64 + 16 * j + a_row + 8 * (e >> 1);
+      const int kk = kt * 16 + 2 * (lane & 3) + ((e & 1) << 3);
+      const uint32_t s = num_groups > 1 ? scales[(int64_t)g * n + scale_pos_grouped(nn)]
+                                        : scales[scale_pos_single(nn)];
+      const uint32_t v = mul2<T>(rg[e], s | (s << 16));
+      reinterpret_cast<uint16_t*>(out)[(int64_t)kk * n + nn] = (uint16_t)(v & 0xffff);
+      reinterpret_cast<uint16_t*>(out)[(int64_t)(kk + 1) * n + nn] = (uint16_t)(v >> 16);
+    }
+  }
+}
+
+inline int pick_bm(int m) { return m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : m <= 128 ? 128 : 256; }
+
+inline int pick_splits(int m, int n, int num_kb, int64_t ws_bytes) {
+  const int bm = pick_bm(m);
+  const int tiles = ((m + bm - 1) / bm) * ((n + kTileN - 1) / kTileN);
+  if (tiles >= kNumSMs || tiles == 0) return 1;
+  int splits = (2 * kNumSMs + tiles - 1) / tiles;
+  if (splits > num_kb / 4) splits = num_kb / 4;
+  const int64_t per = (int64_t)m * n * 4;
+  if (ws_bytes >= 0 && per > 0 && splits > ws_bytes / per) splits = (int)(ws_bytes / per);
+  return splits < 1 ? 1 : splits;
+}
+
+template <int BITS, int BM, typename T, bool ACT>
+int launch(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t lda, cudaStream_t st) {
+  using P = Plan<BITS, BM>;
+  CUtensorMap tm_x;
+  int rc = make_tmap_2d(&tm_x, a_used, (uint64_t)p.size_m, (uint64_t)p.size_k, (uint64_t)lda * 2, 2, BM);
+  if (rc != B200_OK) return rc;
+  MarlinArgs a{};
+  a.c = p.c;
+  a.w = p.b_q_weight;
+  a.scales = p.b_scales;
+  a.g_idx = p.g_idx;
+  a.m = p.size_m, a.n = p.size_n, a.k = p.size_k;
+  a.num_groups = p.num_groups;
+  a.group_size = p.num_groups > 1 ? p.size_k / p.num_groups : p.size_k;
+  a.num_kb = p.size_k / kStageK;
+  int splits = pick_splits(p.size_m, p.size_n, a.num_kb, p.splitk_ws ? p.splitk_ws_bytes : 0);
+  if ((int64_t)p.size_m * p.size_n % 4 != 0) splits = 1;
+  a.kb_per_split = (a.num_kb + splits - 1) / splits;
+  splits = (a.num_kb + a.kb_per_split - 1) / a.kb_per_split;
+  a.partial = splits > 1 ? reinterpret_cast<float*>(p.splitk_ws) : nullptr;
+  const int m_tiles = (p.size_m + BM - 1) / BM, n_tiles = (p.size_n + kTileN - 1) / kTileN;
+  a.w_evict_first = (m_tiles == 1);
+  auto kern = marlin_gemm_kernel<BITS, BM, T, ACT>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P::kBytes);
+  kern<<<dim3(m_tiles, n_tiles, splits), kThreads, P::kBytes, st>>>(tm_x, a);
+  rc = check_launch("gptq_marlin_gemm");
+  if (rc != B200_OK) return rc;
+  if (splits > 1) {
+    const int64_t total = (int64_t)p.size_m * p.size_n;
+    int blocks = (int)((total / 4 + 255) / 256);
+    if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
+    if (blocks < 1) blocks = 1;
+    splitk_sum_kernel<T><<<blocks, 256, 0, st>>>((T*)p.c, a.partial, total, splits);
+    rc = check_launch("gptq_marlin_gemm split-K sum");
+  }
+  return rc;
+}
+
+template <int BITS, typename T, bool ACT>
+int dispatch_bm(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t lda, cudaStream_t st) {
+  switch (pick_bm(p.size_m)) {
+    case 16: return launch<BITS, 16, T, ACT>(p, a_used, lda, st);
+    case 32: return launch<BITS, 32, T, ACT>(p, a_used, lda, st);
+    case 64: return launch<BITS, 64, T, ACT>(p, a_used, lda, st);
+    case 128: return launch<BITS, 128, T, ACT>(p, a_used, lda, st);
+    default: return launch<BITS, 256, T, ACT>(p, a_used, lda, st);
+  }
+}
+
+template <int BITS, typename T>
+int run(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
+  const bool act = p.g_idx != nullptr;
+  const void* a_used = p.a;
+  int64_t lda = p.lda;
+  if (act) {
+    B200_REQUIRE(p.perm != nullptr && p.a_tmp != nullptr, B200_EINVAL,
+                 "gptq_marlin_gemm: act-order needs perm and a_tmp");
+    permute_cols_kernel<T><<<p.size_m, 256, 0, st>>>((T*)p.a_tmp, (const T*)p.a, p.perm, p.size_m,
+                                                     p.size_k, p.lda);
+    int rc = check_launch("gptq_marlin_gemm permute_cols");
+    if (rc != B200_OK) return rc;
+    a_used = p.a_tmp;
+    lda = p.size_k;
+    return dispatch_bm<BITS, T, true>(p, a_used, lda, st);
+  }
+  return dispatch_bm<BITS, T, false>(p, a_used, lda, st);
+}
+
+}  // namespace
+}  // namespace b200
+
+extern "C" {
+
+int64_t b200_gptq_marlin_gemm_workspace_bytes(int32_t m, int32_t n, int32_t k) {
+  const int splits = b200::pick_splits(m, n, k / b200::kStageK, -1);
+  return splits > 1 ? (int64_t)splits * m * n * 4 : 0;
+}
+
+int b200_gptq_marlin_gemm(const b200_gptq_marlin_gemm_params* pp, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(pp != nullptr, B200_EINVAL, "gptq_marlin_gemm: null params");
+  const b200_gptq_marlin_gemm_params& p = *pp;
+  B200_REQUIRE(p.num_bits == 4 || p.num_bits == 8, B200_EINVAL, "num_bits must be 4 or 8. Got = %d",
+               p.num_bits);
+  B200_REQUIRE(p.size_m >= 0 && p.size_n > 0 && p.size_k > 0, B200_EINVAL, "gptq_marlin_gemm: bad sizes");
+  if (p.size_m == 0) return B200_OK;
+  B200_REQUIRE(p.size_n % 64 == 0, B200_EINVAL, "size_n = %d, is not divisible by min_thread_n = 64", p.size_n);
+  B200_REQUIRE(p.size_k % 64 == 0, B200_ENOTSUP, "size_k = %d is not divisible by 64", p.size_k);
+  B200_REQUIRE(p.c && p.a && p.b_q_weight && p.b_scales, B200_EINVAL, "gptq_marlin_gemm: null pointer");
+  B200_REQUIRE(p.num_groups >= 1, B200_EINVAL, "gptq_marlin_gemm: num_groups must be >= 1");
+  if (p.g_idx == nullptr && p.num_groups > 1) {
+    B200_REQUIRE(p.size_k % p.num_groups == 0, B200_EINVAL,
+                 "size_k = %d, is not divisible by b_scales.size(0) = %d", p.size_k, p.num_groups);
+    B200_REQUIRE((p.size_k / p.num_groups) % 16 == 0, B200_ENOTSUP,
+                 "group_size = %d must be a multiple of 16", p.size_k / p.num_groups);
+  }
+  B200_REQUIRE(((uintptr_t)p.a & 15) == 0 && (p.lda * 2) % 16 == 0, B200_EINVAL,
+               "gptq_marlin_gemm: a must be 16-byte aligned with a 16-byte aligned row stride");
+  B200_REQUIRE(((uintptr_t)p.b_q_weight & 15) == 0 && ((uintptr_t)p.b_scales & 15) == 0, B200_EINVAL,
+               "gptq_marlin_gemm: b_q_weight / b_scales must be 16-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (p.dtype == B200_F16) return p.num_bits == 4 ? run<4, __half>(p, st) : run<8, __half>(p, st);
+  if (p.dtype == B200_BF16)
+    return p.num_bits == 4 ? run<4, __nv_bfloat16>(p, st) : run<8, __nv_bfloat16>(p, st);
+  set_error("gpt_marlin_gemm only supports bfloat16 and float16");
+  return B200_EINVAL;
+}
+
+int b200_marlin_dequant(void* out, const uint32_t* b_q_weight, const void* b_scales, int32_t size_k,
+                        int32_t size_n, int32_t num_groups, int32_t num_bits, int32_t dtype,
+                        void* stream) {
+  using namespace b200;
+  B200_REQUIRE(size_k % 16 == 0 && size_n % 64 == 0 && num_groups >= 1 && size_k % num_groups == 0 &&
+                   (size_k / num_groups) % 16 == 0,
+               B200_EINVAL, "marlin_dequant: bad shape");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  dim3 grid(size_n / 64, size_k / 16);
+  const uint16_t* s = reinterpret_cast<const uint16_t*>(b_scales);
+  if (dtype == B200_F16 && num_bits == 4)
+    marlin_dequant_kernel<4, __half><<<grid, 32, 0, st>>>((__half*)out, b_q_weight, s, size_k, size_n, num_groups);
+  else if (dtype == B200_F16 && num_bits == 8)
+    marlin_dequant_kernel<8, __half><<<grid, 32, 0, st>>>((__half*)out, b_q_weight, s, size_k, size_n, num_groups);
+  else if (dtype == B200_BF16 && num_bits == 4)
+    marlin_dequant_kernel<4, __nv_bfloat16><<<grid, 32, 0, st>>>((__nv_bfloat16*)out, b_q_weight, s, size_k, size_n, num_groups);
+  else if (dtype == B200_BF16 && num_bits == 8)
+    marlin_dequant_kernel<8, __nv_bfloat16><<<grid, 32, 0, st>>>((__nv_bfloat16*)out, b_q_weight, s, size_k, size_n, num_groups);
+  else {
+    set_error("marlin_dequant: unsupported dtype/bits");
+    return B200_EINVAL;
+  }
+  return check_launch("marlin_dequant");
+}
+
+}  // extern "C"

@@ -30,6 +30,34 @@ namespace {
 
 using at::Tensor;
 
+// Message building without iostreams: every multi-part check message goes through cat().
+inline void cat_one(std::string& s, const char* v) { s += v; }
+inline void cat_one(std::string& s, const std::string& v) { s += v; }
+inline void cat_one(std::string& s, bool v) { s += v ? "true" : "false"; }
+inline void cat_one(std::string& s, int v) { s += std::to_string(v); }
+inline void cat_one(std::string& s, long v) { s += std::to_string(v); }
+inline void cat_one(std::string& s, long long v) { s += std::to_string(v); }
+inline void cat_one(std::string& s, unsigned long v) { s += std::to_string(v); }
+inline void cat_one(std::string& s, double v) { s += std::to_string(v); }
+inline void cat_one(std::string& s, at::ScalarType v) { s += c10::toString(v); }
+template <typename... A>
+std::string cat(const A&... a) {
+  std::string s;
+  (cat_one(s, a), ...);
+  return s;
+}
+template <typename... A>
+std::string cat_or(const char* dflt, const A&... a) {
+  if constexpr (sizeof...(A) == 0) return std::string(dflt);
+  else return cat(a...);
+}
+#define B200_TCHECK(cond, ...)                                                              \
+  do {                                                                                      \
+    if (!(cond)) {                                                                          \
+      TORCH_CHECK(false, cat_or("Expected " #cond " to be true, but got false.", ##__VA_ARGS__)); \
+    }                                                                                       \
+  } while (0)
+
 void* cur_stream() { return static_cast<void*>(at::cuda::getCurrentCUDAStream().stream()); }
 
 void check_rc(int rc) {
@@ -44,14 +72,14 @@ int dtype_of(const Tensor& t, const char* what) {
     case at::ScalarType::Half: return B200_F16;
     case at::ScalarType::BFloat16: return B200_BF16;
     case at::ScalarType::Float: return B200_F32;
-    default: TORCH_CHECK(false, what, ": unsupported data type ", t.scalar_type());
+    default: TORCH_CHECK(false, cat(what, ": unsupported data type ", t.scalar_type()));
   }
   return -1;
 }
 
 int kv_dtype_of(const std::string& s) {
   const int kv = b200_parse_kv_cache_dtype(s.c_str());
-  TORCH_CHECK(kv >= 0, "Unsupported data type of kv cache: ", s);
+  B200_TCHECK(kv >= 0, "Unsupported data type of kv cache: ", s);
   return kv;
 }
 
@@ -64,19 +92,19 @@ void fill_attention(b200_paged_attention_params& p, Tensor& out, Tensor& query, 
                     const c10::optional<Tensor>& alibi_slopes, const std::string& kv_cache_dtype,
                     double kv_scale, int64_t tp_rank, int64_t bs_local, int64_t bs_vert,
                     int64_t bs_block, int64_t bs_step) {
-  TORCH_CHECK(query.dim() == 3 && out.dim() == 3, "query/out must be [num_seqs, num_heads, head_size]");
-  TORCH_CHECK(query.stride(2) == 1 && query.stride(1) == query.size(2),
+  B200_TCHECK(query.dim() == 3 && out.dim() == 3, "query/out must be [num_seqs, num_heads, head_size]");
+  B200_TCHECK(query.stride(2) == 1 && query.stride(1) == query.size(2),
               "query heads must be contiguous");
-  TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
-  TORCH_CHECK(block_tables.scalar_type() == at::ScalarType::Int && block_tables.dim() == 2 &&
+  B200_TCHECK(out.is_contiguous(), "out must be contiguous");
+  B200_TCHECK(block_tables.scalar_type() == at::ScalarType::Int && block_tables.dim() == 2 &&
                   block_tables.stride(1) == 1,
               "block_tables must be a row-contiguous int32 [num_seqs, max_blocks] tensor");
-  TORCH_CHECK(seq_lens.scalar_type() == at::ScalarType::Int && seq_lens.is_contiguous(),
+  B200_TCHECK(seq_lens.scalar_type() == at::ScalarType::Int && seq_lens.is_contiguous(),
               "seq_lens must be a contiguous int32 tensor");
-  TORCH_CHECK(bs_vert <= 1 || bs_block > 0, "blocksparse_block_size must be positive");
+  B200_TCHECK(bs_vert <= 1 || bs_block > 0, "blocksparse_block_size must be positive");
   // attention_kernels.cu:984-986: blocksparse_block_size must divide into / by block_size
   if (bs_vert > 1) {
-    TORCH_CHECK(bs_block % block_size == 0, "Block sparse attention only supports "
+    B200_TCHECK(bs_block % block_size == 0, "Block sparse attention only supports "
                 "blocksparse_block_size being a multiple of block_size");
   }
   p = b200_paged_attention_params{};
@@ -88,7 +116,7 @@ void fill_attention(b200_paged_attention_params& p, Tensor& out, Tensor& query, 
   p.seq_lens = seq_lens.data_ptr<int32_t>();
   p.alibi_slopes = nullptr;
   if (alibi_slopes.has_value() && alibi_slopes->defined()) {
-    TORCH_CHECK(alibi_slopes->scalar_type() == at::ScalarType::Float && alibi_slopes->is_contiguous(),
+    B200_TCHECK(alibi_slopes->scalar_type() == at::ScalarType::Float && alibi_slopes->is_contiguous(),
                 "alibi_slopes must be a contiguous fp32 tensor");
     p.alibi_slopes = alibi_slopes->data_ptr<float>();
   }
@@ -107,11 +135,11 @@ void fill_attention(b200_paged_attention_params& p, Tensor& out, Tensor& query, 
   p.dtype = dtype_of(query, "paged_attention");
   p.kv_dtype = kv_dtype_of(kv_cache_dtype);
   if (p.kv_dtype == B200_KV_AUTO) {
-    TORCH_CHECK(key_cache.scalar_type() == query.scalar_type() &&
+    B200_TCHECK(key_cache.scalar_type() == query.scalar_type() &&
                     value_cache.scalar_type() == query.scalar_type(),
                 "kv_cache_dtype 'auto' requires caches of the query dtype");
   } else {
-    TORCH_CHECK(key_cache.scalar_type() == at::ScalarType::Byte &&
+    B200_TCHECK(key_cache.scalar_type() == at::ScalarType::Byte &&
                     value_cache.scalar_type() == at::ScalarType::Byte,
                 "fp8 kv caches must be uint8 tensors");
   }
@@ -148,14 +176,14 @@ void paged_attention_v2(Tensor& out, Tensor& exp_sums, Tensor& max_logits, Tenso
                  block_size, max_seq_len, alibi_slopes, kv_cache_dtype, kv_scale, tp_rank, bs_local,
                  bs_vert, bs_block, bs_step);
   const int64_t parts = (max_seq_len + B200_PARTITION_SIZE - 1) / B200_PARTITION_SIZE;
-  TORCH_CHECK(exp_sums.scalar_type() == at::ScalarType::Float && exp_sums.is_contiguous() &&
+  B200_TCHECK(exp_sums.scalar_type() == at::ScalarType::Float && exp_sums.is_contiguous() &&
                   max_logits.scalar_type() == at::ScalarType::Float && max_logits.is_contiguous(),
               "exp_sums / max_logits must be contiguous fp32 tensors");
-  TORCH_CHECK(exp_sums.numel() >= query.size(0) * query.size(1) * parts &&
+  B200_TCHECK(exp_sums.numel() >= query.size(0) * query.size(1) * parts &&
                   max_logits.numel() >= query.size(0) * query.size(1) * parts &&
                   tmp_out.numel() >= query.size(0) * query.size(1) * parts * query.size(2),
               "paged_attention_v2 scratch tensors are too small for max_seq_len=", max_seq_len);
-  TORCH_CHECK(tmp_out.scalar_type() == query.scalar_type() && tmp_out.is_contiguous(),
+  B200_TCHECK(tmp_out.scalar_type() == query.scalar_type() && tmp_out.is_contiguous(),
               "tmp_out must be a contiguous tensor of the query dtype");
   p.exp_sums = exp_sums.data_ptr<float>();
   p.max_logits = max_logits.data_ptr<float>();
@@ -169,14 +197,14 @@ void paged_attention_v2(Tensor& out, Tensor& exp_sums, Tensor& max_logits, Tenso
 void reshape_and_cache(Tensor& key, Tensor& value, Tensor& key_cache, Tensor& value_cache,
                        Tensor& slot_mapping, const std::string& kv_cache_dtype, double kv_scale) {
   const at::cuda::OptionalCUDAGuard guard(device_of(key));
-  TORCH_CHECK(key.dim() == 3 && value.dim() == 3, "key/value must be [num_tokens, num_heads, head_size]");
-  TORCH_CHECK(key_cache.dim() == 5 && value_cache.dim() == 4, "bad kv cache rank");
-  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long && slot_mapping.is_contiguous(),
+  B200_TCHECK(key.dim() == 3 && value.dim() == 3, "key/value must be [num_tokens, num_heads, head_size]");
+  B200_TCHECK(key_cache.dim() == 5 && value_cache.dim() == 4, "bad kv cache rank");
+  B200_TCHECK(slot_mapping.scalar_type() == at::ScalarType::Long && slot_mapping.is_contiguous(),
               "slot_mapping must be a contiguous int64 tensor");
-  TORCH_CHECK(key.stride(2) == 1 && key.stride(1) == key.size(2) && value.stride(2) == 1 &&
+  B200_TCHECK(key.stride(2) == 1 && key.stride(1) == key.size(2) && value.stride(2) == 1 &&
                   value.stride(1) == value.size(2),
               "key/value heads must be contiguous");
-  TORCH_CHECK(key_cache.is_contiguous() && value_cache.is_contiguous(), "kv caches must be contiguous");
+  B200_TCHECK(key_cache.is_contiguous() && value_cache.is_contiguous(), "kv caches must be contiguous");
   b200_reshape_and_cache_params p{};
   p.key = key.data_ptr();
   p.value = value.data_ptr();
@@ -194,9 +222,9 @@ void reshape_and_cache(Tensor& key, Tensor& value, Tensor& key_cache, Tensor& va
   p.dtype = dtype_of(key, "reshape_and_cache");
   p.kv_dtype = kv_dtype_of(kv_cache_dtype);
   if (p.kv_dtype == B200_KV_AUTO) {
-    TORCH_CHECK(key_cache.scalar_type() == key.scalar_type(), "cache dtype must match key dtype");
+    B200_TCHECK(key_cache.scalar_type() == key.scalar_type(), "cache dtype must match key dtype");
   } else {
-    TORCH_CHECK(key_cache.scalar_type() == at::ScalarType::Byte, "fp8 kv caches must be uint8");
+    B200_TCHECK(key_cache.scalar_type() == at::ScalarType::Byte, "fp8 kv caches must be uint8");
   }
   check_rc(b200_reshape_and_cache(&p, cur_stream()));
 }
@@ -204,9 +232,9 @@ void reshape_and_cache(Tensor& key, Tensor& value, Tensor& key_cache, Tensor& va
 void reshape_and_cache_flash(Tensor& key, Tensor& value, Tensor& k_cache, Tensor& v_cache,
                              Tensor& slot_mapping, const std::string& kv_cache_dtype) {
   // cache_kernels.cu:288-290
-  TORCH_CHECK(kv_cache_dtype == "auto", "unsupported kv_cache_dtype (str), supported kv_cache_dtype: auto");
+  B200_TCHECK(kv_cache_dtype == "auto", "unsupported kv_cache_dtype (str), supported kv_cache_dtype: auto");
   const at::cuda::OptionalCUDAGuard guard(device_of(key));
-  TORCH_CHECK(k_cache.stride(0) == v_cache.stride(0), "k/v cache block strides differ");
+  B200_TCHECK(k_cache.stride(0) == v_cache.stride(0), "k/v cache block strides differ");
   b200_reshape_and_cache_flash_params p{};
   p.key = key.data_ptr();
   p.value = value.data_ptr();
@@ -227,10 +255,10 @@ void reshape_and_cache_flash(Tensor& key, Tensor& value, Tensor& k_cache, Tensor
 void copy_blocks(std::vector<Tensor> const& key_caches, std::vector<Tensor> const& value_caches,
                  const Tensor& block_mapping) {
   const int64_t num_layers = (int64_t)key_caches.size();
-  TORCH_CHECK(num_layers == (int64_t)value_caches.size(), "key/value cache lists differ in length");
+  B200_TCHECK(num_layers == (int64_t)value_caches.size(), "key/value cache lists differ in length");
   if (num_layers == 0) return;
   const auto dev = key_caches[0].device();
-  TORCH_CHECK(dev.is_cuda(), "copy_blocks: caches must be CUDA tensors");
+  B200_TCHECK(dev.is_cuda(), "copy_blocks: caches must be CUDA tensors");
   const at::cuda::OptionalCUDAGuard guard(dev);
   const int64_t num_pairs = block_mapping.size(0);
   if (num_pairs == 0) return;
@@ -253,7 +281,7 @@ void swap_blocks(Tensor& src, Tensor& dst, const Tensor& block_mapping) {
   const auto sd = src.device(), dd = dst.device();
   int kind;
   if (sd.is_cuda() && dd.is_cuda()) {
-    TORCH_CHECK(sd.index() == dd.index(), "src and dst must be on the same GPU");
+    B200_TCHECK(sd.index() == dd.index(), "src and dst must be on the same GPU");
     kind = 0;
   } else if (sd.is_cuda() && dd.is_cpu()) {
     kind = 1;
@@ -262,7 +290,7 @@ void swap_blocks(Tensor& src, Tensor& dst, const Tensor& block_mapping) {
   } else {
     TORCH_CHECK(false, "Invalid device combination");
   }
-  TORCH_CHECK(block_mapping.device().is_cpu(), "block_mapping must be on CPU");
+  B200_TCHECK(block_mapping.device().is_cpu(), "block_mapping must be on CPU");
   Tensor bm = block_mapping.to(at::kLong).contiguous();
   const int64_t bytes = src.element_size() * src[0].numel();
   const at::cuda::OptionalCUDAGuard guard(sd.is_cuda() ? sd : dd);
@@ -273,22 +301,22 @@ void swap_blocks(Tensor& src, Tensor& dst, const Tensor& block_mapping) {
 void convert_fp8(Tensor& dst_cache, Tensor& src_cache, double scale, const std::string& kv_cache_dtype) {
   // cache_kernels.cu:339-389
   const auto sd = src_cache.device(), dd = dst_cache.device();
-  TORCH_CHECK(sd.is_cuda(), "src must be on a GPU");
-  TORCH_CHECK(dd.is_cuda(), "dst must be on a GPU");
-  TORCH_CHECK(sd.index() == dd.index(), "src and dst must be on the same GPU");
+  B200_TCHECK(sd.is_cuda(), "src must be on a GPU");
+  B200_TCHECK(dd.is_cuda(), "dst must be on a GPU");
+  B200_TCHECK(sd.index() == dd.index(), "src and dst must be on the same GPU");
   const at::cuda::OptionalCUDAGuard guard(sd);
-  TORCH_CHECK(src_cache.is_contiguous() && dst_cache.is_contiguous(), "caches must be contiguous");
-  TORCH_CHECK(src_cache.numel() == dst_cache.numel(), "src and dst sizes differ");
+  B200_TCHECK(src_cache.is_contiguous() && dst_cache.is_contiguous(), "caches must be contiguous");
+  B200_TCHECK(src_cache.numel() == dst_cache.numel(), "src and dst sizes differ");
   int kv;
   if (kv_cache_dtype == "auto") {
     kv = B200_KV_FP8_E4M3;  // cache_kernels.cu:359-371: "auto" converts with the e4m3 routines
   } else {
     kv = kv_dtype_of(kv_cache_dtype);
-    TORCH_CHECK(kv != B200_KV_AUTO, "Unsupported data type: ", kv_cache_dtype);
+    B200_TCHECK(kv != B200_KV_AUTO, "Unsupported data type: ", kv_cache_dtype);
   }
   const bool to_fp8 = dst_cache.scalar_type() == at::ScalarType::Byte;
   const Tensor& wide = to_fp8 ? src_cache : dst_cache;
-  TORCH_CHECK((to_fp8 ? src_cache : dst_cache).scalar_type() != at::ScalarType::Byte &&
+  B200_TCHECK((to_fp8 ? src_cache : dst_cache).scalar_type() != at::ScalarType::Byte &&
                   (to_fp8 || src_cache.scalar_type() == at::ScalarType::Byte),
               "convert_fp8: exactly one of src/dst must be uint8");
   check_rc(b200_convert_fp8(dst_cache.data_ptr(), src_cache.data_ptr(), src_cache.numel(),
