@@ -27,7 +27,7 @@ constexpr int kStageK = 64;  // k per stage (128 bytes of fp16/bf16)
 constexpr int kDequantWarps = 8;
 constexpr int kThreads = 64 + kDequantWarps * 32;
 constexpr int kAStages = 3;             // dequantised operand ring
-constexpr int kATileBytes = kTileN * 128;  // 16 KiB
+constexpr int kSubTileBytes = kTileN * 128;  // 16 KiB: one 128(n) x 64(k) operand sub-tile
 constexpr int kMaxScaleRows = 4;        // group_size >= 16 -> at most 4 groups per 64-k stage
 
 struct MarlinArgs {
@@ -38,28 +38,47 @@ struct MarlinArgs {
   const int32_t* g_idx;  // act-order: group of every (sorted) k row; nullptr otherwise
   int m, n, k;
   int num_groups, group_size;  // group_size = k when num_groups == 1
+  int group_shift;             // log2(group_size) when it is a power of two, else -1
   int kb_per_split, num_kb;
   int w_evict_first;
 };
 
-template <int BITS, int BM>
+// NT = 128-row sub-tiles of n per CTA: large-M tiles take 2 so every activation tile fetched from
+// L2 feeds two MMAs (the X tile, not the packed weights, is what loads L2 at prefill)
+template <int BITS, int BM, int NT>
 struct Plan {
-  static constexpr int kPackedBytes = kStageK * kTileN * BITS / 8;  // 4 KiB / 8 KiB
-  static constexpr int kScaleBytes = kMaxScaleRows * kTileN * 2;    // 1 KiB
+  static constexpr int kCtaN = kTileN * NT;
+  static constexpr int kATileBytes = NT * kSubTileBytes;
+  static constexpr int kPackedBytes = kStageK * kCtaN * BITS / 8;  // 4 KiB / 8 KiB per sub-tile
+  static constexpr int kScaleBytes = kMaxScaleRows * kCtaN * 2;    // 1 KiB per sub-tile
   static constexpr int kXBytes = BM * 128;
   static constexpr int kStageBytes = kPackedBytes + kScaleBytes + kXBytes;  // multiple of 1 KiB
-  static constexpr int kBudget = (BM <= 64 ? 100 : 200) * 1024 - kAStages * kATileBytes;
+  static constexpr int kBudget = (BM <= 64 ? 100 : 225) * 1024 - kAStages * kATileBytes;
   static constexpr int kStages = kBudget / kStageBytes > 8 ? 8 : kBudget / kStageBytes;
   static constexpr int kBytes = kStages * kStageBytes + kAStages * kATileBytes + 1024 + 512;
   static_assert(kStages >= 2, "pipeline too shallow");
 };
 
-template <int BITS, int BM, typename T, bool ACT_ORDER>
+__device__ __forceinline__ int group_of(const MarlinArgs& a, int k) {
+  return a.group_shift >= 0 ? (k >> a.group_shift) : (k / a.group_size);
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "r"(addr));
+  return v;
+}
+
+template <int BITS, int BM, int NT, typename T, bool ACT_ORDER>
 __global__ void __launch_bounds__(kThreads, 1)
 marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs args) {
-  using P = Plan<BITS, BM>;
+  using P = Plan<BITS, BM, NT>;
   constexpr int kStages = P::kStages;
-  constexpr uint32_t kTmemCols = BM < 32 ? 32 : BM;
+  constexpr int kATileBytes = P::kATileBytes;
+  constexpr int kCtaN = P::kCtaN;
+  constexpr uint32_t kTmemCols = NT * BM < 32 ? 32 : NT * BM;
+  static_assert(kTmemCols <= 512 && (kTmemCols & (kTmemCols - 1)) == 0, "TMEM columns");
   constexpr int KIND = DT<T>::id == B200_F16 ? KIND_F16 : KIND_BF16;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -75,11 +94,11 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs ar
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * BM;
-  const int n0 = blockIdx.y * kTileN;
+  const int n0 = blockIdx.y * kCtaN;
   const int split = blockIdx.z;
   const int kb_begin = split * args.kb_per_split;
   const int kb_end = min(kb_begin + args.kb_per_split, args.num_kb);
-  const int n_valid = min(kTileN, args.n - n0);  // multiple of 64
+  const int n_valid = min(kCtaN, args.n - n0);  // multiple of 64
   const bool grouped = args.num_groups > 1;
 
   if (warp == 0 && lane == 0) {
@@ -119,8 +138,8 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs ar
         uint8_t* s_dst = w_dst + P::kPackedBytes;
         int g_lo = 0, g_rows = 0;
         if (grouped && !ACT_ORDER) {
-          g_lo = (kb * kStageK) / args.group_size;
-          g_rows = (kb * kStageK + kStageK - 1) / args.group_size - g_lo + 1;
+          g_lo = group_of(args, kb * kStageK);
+          g_rows = group_of(args, kb * kStageK + kStageK - 1) - g_lo + 1;
         }
         mbar_arrive_expect_tx(&full_p[stage], P::kXBytes + 4 * row_bytes + g_rows * scale_row_bytes);
         tma_load_2d(x_dst, &tm_x, kb * kStageK, m0, &full_p[stage], pol_x);
@@ -130,7 +149,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs ar
                         args.w + (int64_t)(kb * 4 + kt) * row_words + (int64_t)n0 * kWordsPerN,
                         row_bytes, &full_p[stage], pol_w);
         for (int g = 0; g < g_rows; ++g)
-          bulk_g2s_hint(s_dst + g * (kTileN * 2),
+          bulk_g2s_hint(s_dst + g * (kCtaN * 2),
                         reinterpret_cast<const uint16_t*>(args.scales) + (int64_t)(g_lo + g) * args.n + n0,
                         scale_row_bytes, &full_p[stage], pol_x);
         if (++stage == kStages) stage = 0, phase ^= 1;
@@ -146,12 +165,15 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs ar
         mbar_wait_bounded(&full_p[stage], phase);  // activation tile landed
         mbar_wait_bounded(&full_a[as], aphase);    // dequantised weights written
         fence_after_sync();
-        const uint64_t dw = smem_desc_sw128(smem_u32(a_tiles + as * kATileBytes));
         const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          mma_ss<KIND>(tmem_base, desc_advance(dw, k * 32), desc_advance(dx, k * 32), idesc,
-                       (kb > kb_begin || k > 0) ? 1u : 0u);
+        for (int h = 0; h < NT; ++h) {
+          const uint64_t dw = smem_desc_sw128(smem_u32(a_tiles + as * kATileBytes + h * kSubTileBytes));
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            mma_ss<KIND>(tmem_base + h * BM, desc_advance(dw, k * 32), desc_advance(dx, k * 32), idesc,
+                         (kb > kb_begin || k > 0) ? 1u : 0u);
+        }
         mma_commit(&empty_a[as]);
         mma_commit(&empty_p[stage]);
         if (++stage == kStages) stage = 0, phase ^= 1;
@@ -163,91 +185,102 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs ar
     // ======================= dequant (8 warps) + epilogue (first 4 of them) ==================
     const int dw = warp - 2;      // 0..7
     const int kt = dw >> 1;       // k-tile of the stage (16 rows)
-    const int nt = dw & 1;        // 64-column half of the tile
+    const int nt0 = dw & 1;       // 64-column half of every 128-row sub-tile
     const int a_row = lane >> 2;  // n offset inside an 8-row group
-    const bool nt_valid = nt * 64 < n_valid;
     // stmatrix row address of this lane: matrix q = lane/8 (b = q>>1, high-k = q&1), row r = lane%8
     const int q = lane >> 3, r = lane & 7;
-    const uint32_t st_off = (uint32_t)((nt * 64 + 8 * (q >> 1) + r) * 128 + (((kt * 2 + (q & 1)) ^ r) << 4));
+    const uint32_t st_off = (uint32_t)((nt0 * 64 + 8 * (q >> 1) + r) * 128 + (((kt * 2 + (q & 1)) ^ r) << 4));
     // single-group scales live in registers for the whole kernel
-    uint32_t sc[8];  // sc[2*j + b]: scale of n = 16 j + a_row + 8 b, duplicated in both halves
+    uint32_t sc[NT][8];  // sc[h][2*j + b]: scale of n = 128 h + 64 nt0 + 16 j + a_row + 8 b, in both halves
 #pragma unroll
-    for (int i = 0; i < 8; ++i) sc[i] = DT<T>::pack2(1.f, 1.f);
-    if (!grouped && nt_valid) {
-      const uint16_t* s = reinterpret_cast<const uint16_t*>(args.scales);
+    for (int h = 0; h < NT; ++h) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int n = n0 + nt * 64 + 16 * (i >> 1) + a_row + 8 * (i & 1);
-        const uint32_t v = s[scale_pos_single(n)];
-        sc[i] = v | (v << 16);
+      for (int i = 0; i < 8; ++i) sc[h][i] = DT<T>::pack2(1.f, 1.f);
+      if (!grouped && (h * 128 + nt0 * 64) < n_valid) {
+        const uint16_t* s = reinterpret_cast<const uint16_t*>(args.scales);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int n = n0 + h * 128 + nt0 * 64 + 16 * (i >> 1) + a_row + 8 * (i & 1);
+          const uint32_t v = s[scale_pos_single(n)];
+          sc[h][i] = v | (v << 16);
+        }
       }
     }
+    constexpr int kChunkBytes = 128 * BITS;  // packed bytes of one 16(k) x 64(n) tile
     int cur_group = -1;
     int stage = 0, as = 0;
     uint32_t phase = 0, aphase = 0;
+    const uint32_t stages_u32 = smem_u32(stages);
+    const uint32_t a_tiles_u32 = smem_u32(a_tiles) + st_off;
     for (int kb = kb_begin; kb < kb_end; ++kb) {
       mbar_wait_bounded(&full_p[stage], phase);
-      const uint8_t* w_src = stages + stage * P::kStageBytes + P::kXBytes;
-      const uint8_t* s_src = w_src + P::kPackedBytes;
-      uint32_t words[BITS == 4 ? 4 : 8];
-      {
-        const uint4* p = reinterpret_cast<const uint4*>(w_src + kt * (P::kPackedBytes / 4) +
-                                                        nt * (P::kPackedBytes / 8)) + lane * (BITS / 4);
-        uint4 v0 = p[0];
-        words[0] = v0.x, words[1] = v0.y, words[2] = v0.z, words[3] = v0.w;
+      const uint32_t w_src = stages_u32 + stage * P::kStageBytes + P::kXBytes;
+      const uint32_t s_src = w_src + P::kPackedBytes;
+      uint32_t words[NT][BITS == 4 ? 4 : 8];
+#pragma unroll
+      for (int h = 0; h < NT; ++h) {
+        const uint32_t p = w_src + kt * (P::kPackedBytes / 4) + (2 * h + nt0) * kChunkBytes + lane * (BITS * 4);
+        uint4 v0 = lds128(p);
+        words[h][0] = v0.x, words[h][1] = v0.y, words[h][2] = v0.z, words[h][3] = v0.w;
         if constexpr (BITS == 8) {
-          uint4 v1 = p[1];
-          words[4] = v1.x, words[5] = v1.y, words[6] = v1.z, words[7] = v1.w;
+          uint4 v1 = lds128(p + 16);
+          words[h][4] = v1.x, words[h][5] = v1.y, words[h][6] = v1.z, words[h][7] = v1.w;
         }
       }
       if (grouped && !ACT_ORDER) {
-        const int g = (kb * kStageK + kt * 16) / args.group_size;
+        const int g = group_of(args, kb * kStageK + kt * 16);
         if (g != cur_group) {  // warp-uniform
           cur_group = g;
-          const int g_lo = (kb * kStageK) / args.group_size;
-          const uint4 v = *reinterpret_cast<const uint4*>(s_src + (g - g_lo) * (kTileN * 2) +
-                                                          (nt * 64 + 8 * a_row) * 2);
-          sc[0] = dup16(v.x, 0), sc[1] = dup16(v.x, 1), sc[2] = dup16(v.y, 0), sc[3] = dup16(v.y, 1);
-          sc[4] = dup16(v.z, 0), sc[5] = dup16(v.z, 1), sc[6] = dup16(v.w, 0), sc[7] = dup16(v.w, 1);
+          const int g_lo = group_of(args, kb * kStageK);
+#pragma unroll
+          for (int h = 0; h < NT; ++h) {
+            const uint4 v = lds128(s_src + (g - g_lo) * (kCtaN * 2) + (h * 128 + nt0 * 64 + 8 * a_row) * 2);
+            sc[h][0] = dup16(v.x, 0), sc[h][1] = dup16(v.x, 1), sc[h][2] = dup16(v.y, 0), sc[h][3] = dup16(v.y, 1);
+            sc[h][4] = dup16(v.z, 0), sc[h][5] = dup16(v.z, 1), sc[h][6] = dup16(v.w, 0), sc[h][7] = dup16(v.w, 1);
+          }
         }
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty_p[stage]);  // packed words + scales are in registers
       mbar_wait_bounded(&empty_a[as], aphase ^ 1);
-      const uint32_t a_base = smem_u32(a_tiles + as * kATileBytes) + st_off;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        uint32_t rg[4];
-        if constexpr (BITS == 4) {
-          unpack4<T>(words[j], rg);
-        } else {
-          unpack8<T>(words[2 * j], rg[0], rg[1]);
-          unpack8<T>(words[2 * j + 1], rg[2], rg[3]);
-        }
-        if constexpr (ACT_ORDER) {
-          // every k row may belong to a different group: scale each element separately
-          const uint16_t* s = reinterpret_cast<const uint16_t*>(args.scales);
-          const int kg = kb * kStageK + kt * 16 + 2 * (lane & 3);
+      for (int h = 0; h < NT; ++h) {
+        const uint32_t a_base = a_tiles_u32 + as * kATileBytes + h * kSubTileBytes;
+        const bool nt_valid = (h * 128 + nt0 * 64) < n_valid;
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int kk = kg + ((e & 1) << 3);
-            const int n = n0 + nt * 64 + 16 * j + a_row + 8 * (e >> 1);
-            uint32_t s2 = 0;
-            if (nt_valid) {
-              const int pos = scale_pos_grouped(n);
-              const uint32_t s_lo = s[(int64_t)args.g_idx[kk] * args.n + pos];
-              const uint32_t s_hi = s[(int64_t)args.g_idx[kk + 1] * args.n + pos];
-              s2 = s_lo | (s_hi << 16);
-            }
-            rg[e] = mul2<T>(rg[e], s2);
+        for (int j = 0; j < 4; ++j) {
+          uint32_t rg[4];
+          if constexpr (BITS == 4) {
+            unpack4<T>(words[h][j], rg);
+          } else {
+            unpack8<T>(words[h][2 * j], rg[0], rg[1]);
+            unpack8<T>(words[h][2 * j + 1], rg[2], rg[3]);
           }
-        } else {
-          rg[0] = mul2<T>(rg[0], sc[2 * j]);
-          rg[1] = mul2<T>(rg[1], sc[2 * j]);
-          rg[2] = mul2<T>(rg[2], sc[2 * j + 1]);
-          rg[3] = mul2<T>(rg[3], sc[2 * j + 1]);
+          if constexpr (ACT_ORDER) {
+            // every k row may belong to a different group: scale each element separately
+            const uint16_t* s = reinterpret_cast<const uint16_t*>(args.scales);
+            const int kg = kb * kStageK + kt * 16 + 2 * (lane & 3);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int kk = kg + ((e & 1) << 3);
+              const int n = n0 + h * 128 + nt0 * 64 + 16 * j + a_row + 8 * (e >> 1);
+              uint32_t s2 = 0;
+              if (nt_valid) {
+                const int pos = scale_pos_grouped(n);
+                const uint32_t s_lo = s[(int64_t)args.g_idx[kk] * args.n + pos];
+                const uint32_t s_hi = s[(int64_t)args.g_idx[kk + 1] * args.n + pos];
+                s2 = s_lo | (s_hi << 16);
+              }
+              rg[e] = mul2<T>(rg[e], s2);
+            }
+          } else {
+            rg[0] = mul2<T>(rg[0], sc[h][2 * j]);
+            rg[1] = mul2<T>(rg[1], sc[h][2 * j]);
+            rg[2] = mul2<T>(rg[2], sc[h][2 * j + 1]);
+            rg[3] = mul2<T>(rg[3], sc[h][2 * j + 1]);
+          }
+          stmatrix_x4(a_base + j * (16 * 128), rg);
         }
-        stmatrix_x4(a_base + j * (16 * 128), rg);
       }
       fence_proxy_async();
       __syncwarp();
@@ -257,29 +290,32 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs ar
     }
     if (dw < 4) {
       const int quarter = warp & 3;
-      const int n = n0 + quarter * 32 + lane;
       mbar_wait_bounded(tmem_full, 0);
       fence_after_sync();
-      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
 #pragma unroll 1
-      for (int c = 0; c < BM / 16; ++c) {
-        uint32_t rr[16];
-        tmem_ld16(taddr + c * 16, rr);
-        tmem_ld_wait();
-        if (n < args.n) {
-          if (args.partial != nullptr) {
-            float* ws = args.partial + ((int64_t)split * args.m) * args.n;
+      for (int h = 0; h < NT; ++h) {
+        const int n = n0 + h * 128 + quarter * 32 + lane;
+        const uint32_t taddr = tmem_base + h * BM + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll 1
+        for (int c = 0; c < BM / 16; ++c) {
+          uint32_t rr[16];
+          tmem_ld16(taddr + c * 16, rr);
+          tmem_ld_wait();
+          if (n < args.n) {
+            if (args.partial != nullptr) {
+              float* ws = args.partial + ((int64_t)split * args.m) * args.n;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const int mm = m0 + c * 16 + j;
-              if (mm < args.m) ws[(int64_t)mm * args.n + n] = __uint_as_float(rr[j]);
-            }
-          } else {
-            T* out = reinterpret_cast<T*>(args.c);
+              for (int j = 0; j < 16; ++j) {
+                const int mm = m0 + c * 16 + j;
+                if (mm < args.m) ws[(int64_t)mm * args.n + n] = __uint_as_float(rr[j]);
+              }
+            } else {
+              T* out = reinterpret_cast<T*>(args.c);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const int mm = m0 + c * 16 + j;
-              if (mm < args.m) out[(int64_t)mm * args.n + n] = DT<T>::from_f(__uint_as_float(rr[j]));
+              for (int j = 0; j < 16; ++j) {
+                const int mm = m0 + c * 16 + j;
+                if (mm < args.m) out[(int64_t)mm * args.n + n] = DT<T>::from_f(__uint_as_float(rr[j]));
+              }
             }
           }
         }
@@ -357,9 +393,12 @@ __global__ void __launch_bounds__(32) marlin_dequant_kernel(T* __restrict__ out,
 
 inline int pick_bm(int m) { return m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : m <= 128 ? 128 : 256; }
 
+inline int pick_nt(int bm) { return bm >= 128 ? 2 : 1; }
+
 inline int pick_splits(int m, int n, int num_kb, int64_t ws_bytes) {
   const int bm = pick_bm(m);
-  const int tiles = ((m + bm - 1) / bm) * ((n + kTileN - 1) / kTileN);
+  const int cta_n = kTileN * pick_nt(bm);
+  const int tiles = ((m + bm - 1) / bm) * ((n + cta_n - 1) / cta_n);
   if (tiles >= kNumSMs || tiles == 0) return 1;
   int splits = (2 * kNumSMs + tiles - 1) / tiles;
   if (splits > num_kb / 4) splits = num_kb / 4;
@@ -368,9 +407,9 @@ inline int pick_splits(int m, int n, int num_kb, int64_t ws_bytes) {
   return splits < 1 ? 1 : splits;
 }
 
-template <int BITS, int BM, typename T, bool ACT>
+template <int BITS, int BM, int NT, typename T, bool ACT>
 int launch(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t lda, cudaStream_t st) {
-  using P = Plan<BITS, BM>;
+  using P = Plan<BITS, BM, NT>;
   CUtensorMap tm_x;
   int rc = make_tmap_2d(&tm_x, a_used, (uint64_t)p.size_m, (uint64_t)p.size_k, (uint64_t)lda * 2, 2, BM);
   if (rc != B200_OK) return rc;
@@ -382,15 +421,16 @@ int launch(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t ld
   a.m = p.size_m, a.n = p.size_n, a.k = p.size_k;
   a.num_groups = p.num_groups;
   a.group_size = p.num_groups > 1 ? p.size_k / p.num_groups : p.size_k;
+  a.group_shift = (a.group_size & (a.group_size - 1)) == 0 ? __builtin_ctz(a.group_size) : -1;
   a.num_kb = p.size_k / kStageK;
   int splits = pick_splits(p.size_m, p.size_n, a.num_kb, p.splitk_ws ? p.splitk_ws_bytes : 0);
   if ((int64_t)p.size_m * p.size_n % 4 != 0) splits = 1;
   a.kb_per_split = (a.num_kb + splits - 1) / splits;
   splits = (a.num_kb + a.kb_per_split - 1) / a.kb_per_split;
   a.partial = splits > 1 ? reinterpret_cast<float*>(p.splitk_ws) : nullptr;
-  const int m_tiles = (p.size_m + BM - 1) / BM, n_tiles = (p.size_n + kTileN - 1) / kTileN;
+  const int m_tiles = (p.size_m + BM - 1) / BM, n_tiles = (p.size_n + P::kCtaN - 1) / P::kCtaN;
   a.w_evict_first = (m_tiles == 1);
-  auto kern = marlin_gemm_kernel<BITS, BM, T, ACT>;
+  auto kern = marlin_gemm_kernel<BITS, BM, NT, T, ACT>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P::kBytes);
   kern<<<dim3(m_tiles, n_tiles, splits), kThreads, P::kBytes, st>>>(tm_x, a);
   rc = check_launch("gptq_marlin_gemm");
@@ -409,11 +449,11 @@ int launch(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t ld
 template <int BITS, typename T, bool ACT>
 int dispatch_bm(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t lda, cudaStream_t st) {
   switch (pick_bm(p.size_m)) {
-    case 16: return launch<BITS, 16, T, ACT>(p, a_used, lda, st);
-    case 32: return launch<BITS, 32, T, ACT>(p, a_used, lda, st);
-    case 64: return launch<BITS, 64, T, ACT>(p, a_used, lda, st);
-    case 128: return launch<BITS, 128, T, ACT>(p, a_used, lda, st);
-    default: return launch<BITS, 256, T, ACT>(p, a_used, lda, st);
+    case 16: return launch<BITS, 16, 1, T, ACT>(p, a_used, lda, st);
+    case 32: return launch<BITS, 32, 1, T, ACT>(p, a_used, lda, st);
+    case 64: return launch<BITS, 64, 1, T, ACT>(p, a_used, lda, st);
+    case 128: return launch<BITS, 128, 2, T, ACT>(p, a_used, lda, st);
+    default: return launch<BITS, 256, 2, T, ACT>(p, a_used, lda, st);
   }
 }
 
