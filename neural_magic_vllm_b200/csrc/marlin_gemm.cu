@@ -39,6 +39,7 @@ struct MarlinArgs {
   int m, n, k;
   int num_groups, group_size;  // group_size = k when num_groups == 1
   int group_shift;             // log2(group_size) when it is a power of two, else -1
+  int s_rows;                  // scale rows fetched per stage (0: scales are not staged)
   int kb_per_split, num_kb;
   int w_evict_first;
 };
@@ -70,9 +71,19 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   return v;
 }
 
+// packed weights arrive as TMA boxes of 4 k-tile rows x 1 KiB (256 int32: 128 columns at 4 bits,
+// 64 at 8 bits), box l of a stage at l * 4 KiB.  Offset of the 16(k) x 64(n) Marlin tile
+// (k-tile kt, 64-column chunk c of the CTA's n range) inside the stage's packed area:
+template <int BITS>
+__device__ __forceinline__ uint32_t chunk_off(int kt, int c) {
+  return BITS == 4 ? (uint32_t)((c >> 1) * 4096 + kt * 1024 + (c & 1) * 512)
+                   : (uint32_t)(c * 4096 + kt * 1024);
+}
+
 template <int BITS, int BM, int NT, typename T, bool ACT_ORDER>
 __global__ void __launch_bounds__(kThreads, 1)
-marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs args) {
+marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+                   const __grid_constant__ CUtensorMap tm_s, const MarlinArgs args) {
   using P = Plan<BITS, BM, NT>;
   constexpr int kStages = P::kStages;
   constexpr int kATileBytes = P::kATileBytes;
@@ -122,38 +133,31 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs ar
 
   if (warp == 0) {
     // ======================= producer =======================
-    if (lane == 0) {
-      const uint64_t pol_w = args.w_evict_first ? l2_policy_evict_first() : l2_policy_evict_last();
-      const uint64_t pol_x = l2_policy_evict_last();
-      constexpr int kWordsPerN = 16 * BITS / 32;  // int32 per column per 16-row k-tile
-      const int64_t row_words = (int64_t)args.n * kWordsPerN;
-      const uint32_t row_bytes = (uint32_t)n_valid * kWordsPerN * 4;
-      const uint32_t scale_row_bytes = (uint32_t)n_valid * 2;
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = kb_begin; kb < kb_end; ++kb) {
-        mbar_wait_bounded(&empty_p[stage], phase ^ 1);
+    // the whole warp runs the loop (uniform control flow keeps every operand in uniform
+    // registers); lane 0 issues: one TMA per operand per stage
+    const uint64_t pol_w = args.w_evict_first ? l2_policy_evict_first() : l2_policy_evict_last();
+    const uint64_t pol_x = l2_policy_evict_last();
+    constexpr int kWordsPerN = 16 * BITS / 32;
+    constexpr int kLoadsW = kCtaN * kWordsPerN / 256;
+    const uint32_t tx_bytes = P::kXBytes + P::kPackedBytes + (uint32_t)args.s_rows * (kCtaN * 2);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = kb_begin; kb < kb_end; ++kb) {
+      mbar_wait_bounded(&empty_p[stage], phase ^ 1);
+      if (lane == 0) {
         uint8_t* x_dst = stages + stage * P::kStageBytes;
         uint8_t* w_dst = x_dst + P::kXBytes;
         uint8_t* s_dst = w_dst + P::kPackedBytes;
-        int g_lo = 0, g_rows = 0;
-        if (grouped && !ACT_ORDER) {
-          g_lo = group_of(args, kb * kStageK);
-          g_rows = group_of(args, kb * kStageK + kStageK - 1) - g_lo + 1;
-        }
-        mbar_arrive_expect_tx(&full_p[stage], P::kXBytes + 4 * row_bytes + g_rows * scale_row_bytes);
+        mbar_arrive_expect_tx(&full_p[stage], tx_bytes);
         tma_load_2d(x_dst, &tm_x, kb * kStageK, m0, &full_p[stage], pol_x);
 #pragma unroll
-        for (int kt = 0; kt < 4; ++kt)
-          bulk_g2s_hint(w_dst + kt * (P::kPackedBytes / 4),
-                        args.w + (int64_t)(kb * 4 + kt) * row_words + (int64_t)n0 * kWordsPerN,
-                        row_bytes, &full_p[stage], pol_w);
-        for (int g = 0; g < g_rows; ++g)
-          bulk_g2s_hint(s_dst + g * (kCtaN * 2),
-                        reinterpret_cast<const uint16_t*>(args.scales) + (int64_t)(g_lo + g) * args.n + n0,
-                        scale_row_bytes, &full_p[stage], pol_x);
-        if (++stage == kStages) stage = 0, phase ^= 1;
+        for (int l = 0; l < kLoadsW; ++l)
+          tma_load_2d(w_dst + l * 4096, &tm_w, n0 * kWordsPerN + l * 256, kb * 4, &full_p[stage], pol_w);
+        if (args.s_rows > 0)
+          tma_load_2d(s_dst, &tm_s, n0, group_of(args, kb * kStageK), &full_p[stage], pol_x);
       }
+      __syncwarp();
+      if (++stage == kStages) stage = 0, phase ^= 1;
     }
   } else if (warp == 1) {
     // ======================= MMA issuer =======================
@@ -206,7 +210,6 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs ar
         }
       }
     }
-    constexpr int kChunkBytes = 128 * BITS;  // packed bytes of one 16(k) x 64(n) tile
     int cur_group = -1;
     int stage = 0, as = 0;
     uint32_t phase = 0, aphase = 0;
@@ -219,7 +222,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs ar
       uint32_t words[NT][BITS == 4 ? 4 : 8];
 #pragma unroll
       for (int h = 0; h < NT; ++h) {
-        const uint32_t p = w_src + kt * (P::kPackedBytes / 4) + (2 * h + nt0) * kChunkBytes + lane * (BITS * 4);
+        const uint32_t p = w_src + chunk_off<BITS>(kt, 2 * h + nt0) + lane * (BITS * 4);
         uint4 v0 = lds128(p);
         words[h][0] = v0.x, words[h][1] = v0.y, words[h][2] = v0.z, words[h][3] = v0.w;
         if constexpr (BITS == 8) {
@@ -330,6 +333,253 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const MarlinArgs ar
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Decode kernel (BM <= 64, no act-order): the dequantised weights never touch shared memory.
+// The dequant warps write their mma-fragment registers straight into TMEM (tcgen05.st 16x128b.x2,
+// whose thread->(lane, column) map IS the Marlin fragment order) and the MMA takes A from TMEM:
+// no stmatrix traffic, no proxy fence, half the shared-memory bandwidth per stage.
+//   TMEM columns: [0, 96) = ring of 3 A stages (64 k = 32 columns each), [96, 96 + BM) = D.
+//   warp w's TMEM quadrant is w % 4 = rows 32 q .. 32 q + 31 of the 128-row n tile, so the two
+//   warps of a quadrant split the four 16-row k tiles of a stage between them.
+// ------------------------------------------------------------------------------------------------
+constexpr int kTmemAStageCols = kStageK / 2;  // 32
+constexpr int kTmemDCol = kAStages * kTmemAStageCols;
+
+template <int BITS, int BM>
+struct PlanT {
+  static constexpr int kPackedBytes = kStageK * kTileN * BITS / 8;
+  static constexpr int kScaleBytes = kMaxScaleRows * kTileN * 2;
+  static constexpr int kXBytes = BM * 128;
+  static constexpr int kStageBytes = kPackedBytes + kScaleBytes + kXBytes;
+  static constexpr int kStages = 6;
+  static constexpr int kBytes = kStages * kStageBytes + 1024 + 512;
+  static constexpr uint32_t kTmemCols = kTmemDCol + BM <= 128 ? 128 : 256;
+};
+
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.b32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+  return v;
+}
+
+template <int BITS, int BM, typename T>
+__global__ void __launch_bounds__(kThreads, (BM <= 32 ? 3 : 2))
+marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+                        const __grid_constant__ CUtensorMap tm_s, const MarlinArgs args) {
+  using P = PlanT<BITS, BM>;
+  constexpr int kStages = P::kStages;
+  constexpr int KIND = DT<T>::id == B200_F16 ? KIND_F16 : KIND_BF16;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stages + kStages * P::kStageBytes);
+  uint64_t* full_p = bars;
+  uint64_t* empty_p = full_p + kStages;
+  uint64_t* full_a = empty_p + kStages;
+  uint64_t* empty_a = full_a + kAStages;
+  uint64_t* tmem_full = empty_a + kAStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM;
+  const int n0 = blockIdx.y * kTileN;
+  const int split = blockIdx.z;
+  const int kb_begin = split * args.kb_per_split;
+  const int kb_end = min(kb_begin + args.kb_per_split, args.num_kb);
+  const int n_valid = min(kTileN, args.n - n0);  // multiple of 64
+  const bool grouped = args.num_groups > 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_x);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_p[s], 1);
+      mbar_init(&empty_p[s], kDequantWarps + 1);
+    }
+    for (int s = 0; s < kAStages; ++s) {
+      mbar_init(&full_a[s], kDequantWarps);
+      mbar_init(&empty_a[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, P::kTmemCols);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // the whole warp runs the loop (uniform control flow keeps every operand in uniform
+    // registers); lane 0 issues: one TMA per operand per stage
+    const uint64_t pol_w = args.w_evict_first ? l2_policy_evict_first() : l2_policy_evict_last();
+    const uint64_t pol_x = l2_policy_evict_last();
+    constexpr int kWordsPerN = 16 * BITS / 32;
+    constexpr int kLoadsW = kTileN * kWordsPerN / 256;
+    const uint32_t tx_bytes = P::kXBytes + P::kPackedBytes + (uint32_t)args.s_rows * (kTileN * 2);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = kb_begin; kb < kb_end; ++kb) {
+      mbar_wait_bounded(&empty_p[stage], phase ^ 1);
+      if (lane == 0) {
+        uint8_t* x_dst = stages + stage * P::kStageBytes;
+        uint8_t* w_dst = x_dst + P::kXBytes;
+        uint8_t* s_dst = w_dst + P::kPackedBytes;
+        mbar_arrive_expect_tx(&full_p[stage], tx_bytes);
+        tma_load_2d(x_dst, &tm_x, kb * kStageK, m0, &full_p[stage], pol_x);
+#pragma unroll
+        for (int l = 0; l < kLoadsW; ++l)
+          tma_load_2d(w_dst + l * 4096, &tm_w, n0 * kWordsPerN + l * 256, kb * 4, &full_p[stage], pol_w);
+        if (args.s_rows > 0)
+          tma_load_2d(s_dst, &tm_s, n0, group_of(args, kb * kStageK), &full_p[stage], pol_x);
+      }
+      __syncwarp();
+      if (++stage == kStages) stage = 0, phase ^= 1;
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = instr_desc<KIND>(kTileN, BM);
+      int stage = 0, as = 0;
+      uint32_t phase = 0, aphase = 0;
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        mbar_wait_bounded(&full_p[stage], phase);
+        mbar_wait_bounded(&full_a[as], aphase);
+        fence_after_sync();
+        const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          mma_ts_f16(tmem_base + kTmemDCol, tmem_base + as * kTmemAStageCols + k * 8,
+                     desc_advance(dx, k * 32), idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
+        mma_commit(&empty_a[as]);
+        mma_commit(&empty_p[stage]);
+        if (++stage == kStages) stage = 0, phase ^= 1;
+        if (++as == kAStages) as = 0, aphase ^= 1;
+      }
+      mma_commit(tmem_full);
+    }
+  } else {
+    const int qd = warp & 3;          // TMEM quadrant = rows 32 qd .. 32 qd + 31
+    const int kt0 = ((warp - 2) >> 2) * 2;  // this warp's two k tiles of every stage
+    const int nt = qd >> 1;           // 64-column Marlin tile inside the 128-row n tile
+    const int j0 = (qd & 1) * 2;      // first of its two 16-row fragments
+    const int a_row = lane >> 2;
+    const bool nt_valid = nt * 64 < n_valid;
+    uint32_t sc[4];  // sc[2*jj + b]: scale of n = 64 nt + 16 (j0 + jj) + a_row + 8 b, in both halves
+#pragma unroll
+    for (int i = 0; i < 4; ++i) sc[i] = DT<T>::pack2(1.f, 1.f);
+    if (!grouped && nt_valid) {
+      const uint16_t* s = reinterpret_cast<const uint16_t*>(args.scales);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int n = n0 + nt * 64 + 16 * (j0 + (i >> 1)) + a_row + 8 * (i & 1);
+        const uint32_t v = s[scale_pos_single(n)];
+        sc[i] = v | (v << 16);
+      }
+    }
+    int cur_group = -1;
+    int stage = 0, as = 0;
+    uint32_t phase = 0, aphase = 0;
+    const uint32_t stages_u32 = smem_u32(stages);
+    const uint32_t t_lane = (uint32_t)(qd * 32) << 16;
+    for (int kb = kb_begin; kb < kb_end; ++kb) {
+      mbar_wait_bounded(&full_p[stage], phase);
+      const uint32_t w_src = stages_u32 + stage * P::kStageBytes + P::kXBytes;
+      const uint32_t s_src = w_src + P::kPackedBytes;
+      uint32_t words[2][BITS == 4 ? 2 : 4];
+#pragma unroll
+      for (int kk = 0; kk < 2; ++kk) {
+        const uint32_t p = w_src + chunk_off<BITS>(kt0 + kk, nt) + lane * (BITS * 4) + (qd & 1) * (BITS * 2);
+        if constexpr (BITS == 4) {
+          const uint2 v = lds64(p);
+          words[kk][0] = v.x, words[kk][1] = v.y;
+        } else {
+          const uint4 v = lds128(p);
+          words[kk][0] = v.x, words[kk][1] = v.y, words[kk][2] = v.z, words[kk][3] = v.w;
+        }
+      }
+      uint32_t scs[2][4];
+#pragma unroll
+      for (int kk = 0; kk < 2; ++kk) {
+        if (grouped) {
+          const int g = group_of(args, kb * kStageK + (kt0 + kk) * 16);
+          if (g != cur_group) {  // warp-uniform
+            cur_group = g;
+            const int g_lo = group_of(args, kb * kStageK);
+            const uint2 v = lds64(s_src + (g - g_lo) * (kTileN * 2) + (nt * 64 + 8 * a_row) * 2 + (qd & 1) * 8);
+            sc[0] = dup16(v.x, 0), sc[1] = dup16(v.x, 1), sc[2] = dup16(v.y, 0), sc[3] = dup16(v.y, 1);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) scs[kk][i] = sc[i];
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_p[stage]);  // packed words + scales are in registers
+      mbar_wait_bounded(&empty_a[as], aphase ^ 1);
+      fence_after_sync();
+#pragma unroll
+      for (int kk = 0; kk < 2; ++kk) {
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          uint32_t rg[4];
+          if constexpr (BITS == 4) {
+            unpack4<T>(words[kk][jj], rg);
+          } else {
+            unpack8<T>(words[kk][2 * jj], rg[0], rg[1]);
+            unpack8<T>(words[kk][2 * jj + 1], rg[2], rg[3]);
+          }
+          rg[0] = mul2<T>(rg[0], scs[kk][2 * jj]);
+          rg[1] = mul2<T>(rg[1], scs[kk][2 * jj]);
+          rg[2] = mul2<T>(rg[2], scs[kk][2 * jj + 1]);
+          rg[3] = mul2<T>(rg[3], scs[kk][2 * jj + 1]);
+          // rg = {b0 k-lo, b0 k-hi, b1 k-lo, b1 k-hi} -> st order {b0 lo, b1 lo, b0 hi, b1 hi}
+          tmem_st_16x128b_x2(tmem_base + t_lane + ((uint32_t)(16 * jj) << 16) + as * kTmemAStageCols +
+                                 (kt0 + kk) * 8,
+                             rg[0], rg[2], rg[1], rg[3]);
+        }
+      }
+      tmem_st_wait();
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full_a[as]);
+      if (++stage == kStages) stage = 0, phase ^= 1;
+      if (++as == kAStages) as = 0, aphase ^= 1;
+    }
+    if (warp < 6) {
+      const int n = n0 + qd * 32 + lane;
+      mbar_wait_bounded(tmem_full, 0);
+      fence_after_sync();
+      const uint32_t taddr = tmem_base + t_lane + kTmemDCol;
+#pragma unroll 1
+      for (int c = 0; c < BM / 16; ++c) {
+        uint32_t rr[16];
+        tmem_ld16(taddr + c * 16, rr);
+        tmem_ld_wait();
+        if (n < args.n) {
+          if (args.partial != nullptr) {
+            float* ws = args.partial + ((int64_t)split * args.m) * args.n;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int mm = m0 + c * 16 + j;
+              if (mm < args.m) ws[(int64_t)mm * args.n + n] = __uint_as_float(rr[j]);
+            }
+          } else {
+            T* out = reinterpret_cast<T*>(args.c);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int mm = m0 + c * 16 + j;
+              if (mm < args.m) out[(int64_t)mm * args.n + n] = DT<T>::from_f(__uint_as_float(rr[j]));
+            }
+          }
+        }
+      }
+      fence_before_sync();
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    fence_after_sync();
+    tmem_dealloc(tmem_base, P::kTmemCols);
+  }
+}
+
 // act-order: a_tmp[m, k'] = a[m, perm[k']] (gptq_marlin.cu:345-394 permute_cols_kernel)
 template <typename T>
 __global__ void __launch_bounds__(256) permute_cols_kernel(T* __restrict__ dst, const T* __restrict__ src,
@@ -423,6 +673,9 @@ int launch(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t ld
   a.group_size = p.num_groups > 1 ? p.size_k / p.num_groups : p.size_k;
   a.group_shift = (a.group_size & (a.group_size - 1)) == 0 ? __builtin_ctz(a.group_size) : -1;
   a.num_kb = p.size_k / kStageK;
+  CUtensorMap tm_w, tm_s;
+  rc = make_weight_maps(p, p.num_groups > 1 && !ACT, P::kCtaN, &tm_w, &tm_s, &a);
+  if (rc != B200_OK) return rc;
   int splits = pick_splits(p.size_m, p.size_n, a.num_kb, p.splitk_ws ? p.splitk_ws_bytes : 0);
   if ((int64_t)p.size_m * p.size_n % 4 != 0) splits = 1;
   a.kb_per_split = (a.num_kb + splits - 1) / splits;
@@ -432,7 +685,68 @@ int launch(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t ld
   a.w_evict_first = (m_tiles == 1);
   auto kern = marlin_gemm_kernel<BITS, BM, NT, T, ACT>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P::kBytes);
-  kern<<<dim3(m_tiles, n_tiles, splits), kThreads, P::kBytes, st>>>(tm_x, a);
+  kern<<<dim3(m_tiles, n_tiles, splits), kThreads, P::kBytes, st>>>(tm_x, tm_w, tm_s, a);
+  rc = check_launch("gptq_marlin_gemm");
+  if (rc != B200_OK) return rc;
+  if (splits > 1) {
+    const int64_t total = (int64_t)p.size_m * p.size_n;
+    int blocks = (int)((total / 4 + 255) / 256);
+    if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
+    if (blocks < 1) blocks = 1;
+    splitk_sum_kernel<T><<<blocks, 256, 0, st>>>((T*)p.c, a.partial, total, splits);
+    rc = check_launch("gptq_marlin_gemm split-K sum");
+  }
+  return rc;
+}
+
+// tensor maps of the packed weights ([K/16, N * words] int32, box 4 x 256) and of the group scales
+// ([groups, N] 16-bit, box s_rows x cta_n); s_rows = scale rows a 64-k stage can touch
+inline int make_weight_maps(const b200_gptq_marlin_gemm_params& p, bool staged_scales, int cta_n,
+                            CUtensorMap* tm_w, CUtensorMap* tm_s, MarlinArgs* a) {
+  const uint64_t words = (uint64_t)p.size_n * (16 * p.num_bits / 32);
+  int rc = make_tmap_2d_ex(tm_w, p.b_q_weight, (uint64_t)p.size_k / 16, words, words * 4,
+                           CU_TENSOR_MAP_DATA_TYPE_INT32, 256, 4, CU_TENSOR_MAP_SWIZZLE_NONE);
+  if (rc != B200_OK) return rc;
+  a->s_rows = 0;
+  if (staged_scales) {
+    const int gs = a->group_size;
+    a->s_rows = a->group_shift >= 0 ? (gs >= kStageK ? 1 : kStageK / gs) : (kStageK / gs + 2 > 4 ? 4 : kStageK / gs + 2);
+    return make_tmap_2d_ex(tm_s, p.b_scales, (uint64_t)p.num_groups, (uint64_t)p.size_n, (uint64_t)p.size_n * 2,
+                           CU_TENSOR_MAP_DATA_TYPE_UINT16, (uint32_t)cta_n, (uint32_t)a->s_rows,
+                           CU_TENSOR_MAP_SWIZZLE_NONE);
+  }
+  *tm_s = *tm_w;  // never dereferenced
+  return B200_OK;
+}
+
+template <int BITS, int BM, typename T>
+int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
+  using P = PlanT<BITS, BM>;
+  CUtensorMap tm_x;
+  int rc = make_tmap_2d(&tm_x, p.a, (uint64_t)p.size_m, (uint64_t)p.size_k, (uint64_t)p.lda * 2, 2, BM);
+  if (rc != B200_OK) return rc;
+  MarlinArgs a{};
+  a.c = p.c;
+  a.w = p.b_q_weight;
+  a.scales = p.b_scales;
+  a.m = p.size_m, a.n = p.size_n, a.k = p.size_k;
+  a.num_groups = p.num_groups;
+  a.group_size = p.num_groups > 1 ? p.size_k / p.num_groups : p.size_k;
+  a.group_shift = (a.group_size & (a.group_size - 1)) == 0 ? __builtin_ctz(a.group_size) : -1;
+  a.num_kb = p.size_k / kStageK;
+  CUtensorMap tm_w, tm_s;
+  rc = make_weight_maps(p, p.num_groups > 1, kTileN, &tm_w, &tm_s, &a);
+  if (rc != B200_OK) return rc;
+  int splits = pick_splits(p.size_m, p.size_n, a.num_kb, p.splitk_ws ? p.splitk_ws_bytes : 0);
+  if ((int64_t)p.size_m * p.size_n % 4 != 0) splits = 1;
+  a.kb_per_split = (a.num_kb + splits - 1) / splits;
+  splits = (a.num_kb + a.kb_per_split - 1) / a.kb_per_split;
+  a.partial = splits > 1 ? reinterpret_cast<float*>(p.splitk_ws) : nullptr;
+  const int m_tiles = (p.size_m + BM - 1) / BM, n_tiles = (p.size_n + kTileN - 1) / kTileN;
+  a.w_evict_first = (m_tiles == 1);
+  auto kern = marlin_gemm_tmem_kernel<BITS, BM, T>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P::kBytes);
+  kern<<<dim3(m_tiles, n_tiles, splits), kThreads, P::kBytes, st>>>(tm_x, tm_w, tm_s, a);
   rc = check_launch("gptq_marlin_gemm");
   if (rc != B200_OK) return rc;
   if (splits > 1) {
@@ -448,6 +762,14 @@ int launch(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t ld
 
 template <int BITS, typename T, bool ACT>
 int dispatch_bm(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t lda, cudaStream_t st) {
+  if constexpr (!ACT) {
+    switch (pick_bm(p.size_m)) {
+      case 16: return launch_tmem<BITS, 16, T>(p, st);
+      case 32: return launch_tmem<BITS, 32, T>(p, st);
+      case 64: return launch_tmem<BITS, 64, T>(p, st);
+      default: break;
+    }
+  }
   switch (pick_bm(p.size_m)) {
     case 16: return launch<BITS, 16, 1, T, ACT>(p, a_used, lda, st);
     case 32: return launch<BITS, 32, 1, T, ACT>(p, a_used, lda, st);

@@ -94,6 +94,31 @@ __device__ __forceinline__ void mma_ss(uint32_t tmem_d, uint64_t desc_a, uint64_
   }
 }
 
+// D[tmem] (+)= A[tmem] * B[smem] (kind::f16): A is M x K with row m in TMEM lane m and the 16-bit
+// elements packed two per 32-bit column (K = 16 -> 8 columns at `tmem_a`); A cannot be transposed
+__device__ __forceinline__ void mma_ts_f16(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b,
+                                           uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// registers -> TMEM, shape 16x128b.x2: 16 lanes x 8 columns starting at `taddr`.  Thread t supplies
+//   r0 = (lane t/4,     col t%4)   r1 = (lane t/4 + 8, col t%4)
+//   r2 = (lane t/4,     col 4+t%4) r3 = (lane t/4 + 8, col 4+t%4)
+// (cute/atom/copy_traits_sm100.hpp, SM100_TMEM_*_16dp128b2x) -- the m16n8k16 fragment order.
+__device__ __forceinline__ void tmem_st_16x128b_x2(uint32_t taddr, uint32_t r0, uint32_t r1,
+                                                   uint32_t r2, uint32_t r3) {
+  asm volatile("tcgen05.st.sync.aligned.16x128b.x2.b32 [%0], {%1,%2,%3,%4};" ::"r"(taddr), "r"(r0),
+               "r"(r1), "r"(r2), "r"(r3)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() {
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
 // all previously issued MMAs of this thread arrive on `bar` when they complete
 // (implies tcgen05.fence::before_thread_sync)
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
@@ -135,16 +160,15 @@ __device__ __forceinline__ uint64_t l2_policy_evict_last() {
   return pol;
 }
 
-// ---- host: tensor map for a row-major [rows, cols] matrix of `elem_bytes` elements ----------------
-// box = box_rows x 128 bytes (one swizzle atom along the contiguous dimension), SWIZZLE_128B,
-// out-of-bounds elements read as zero (tails in every dimension need no special code).
-inline int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols,
-                        uint64_t row_stride_bytes, int elem_bytes, uint32_t box_rows) {
-  CUtensorMapDataType dt = elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
-                                           : CU_TENSOR_MAP_DATA_TYPE_UINT16;
+// ---- host: tensor maps -------------------------------------------------------------------------------
+// generic 2-D tiled map over a row-major [rows, cols] matrix; out-of-bounds elements read as zero
+// (tails in every dimension need no special code) and still count towards the mbarrier's tx bytes.
+inline int make_tmap_2d_ex(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols,
+                           uint64_t row_stride_bytes, CUtensorMapDataType dt, uint32_t box_cols,
+                           uint32_t box_rows, CUtensorMapSwizzle swz) {
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {row_stride_bytes};
-  cuuint32_t box[2] = {(cuuint32_t)(128 / elem_bytes), box_rows};
+  cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
   // the driver entry point is resolved through the runtime: the library has no link-time
   // dependency on libcuda.so.1, so it loads (and exports its symbols) on a box without a driver
@@ -165,15 +189,24 @@ inline int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint6
     encode = reinterpret_cast<EncodeFn>(fn);
   }
   CUresult r = encode(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr,
-                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                      CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    set_error("cuTensorMapEncodeTiled failed: CUresult %d (rows=%llu cols=%llu stride=%llu box_rows=%u)",
+    set_error("cuTensorMapEncodeTiled failed: CUresult %d (rows=%llu cols=%llu stride=%llu box=%ux%u)",
               (int)r, (unsigned long long)rows, (unsigned long long)cols,
-              (unsigned long long)row_stride_bytes, box_rows);
+              (unsigned long long)row_stride_bytes, box_cols, box_rows);
     return B200_ECUDA;
   }
   return B200_OK;
+}
+
+// K-major MMA operand: box = box_rows x 128 bytes (one swizzle atom along the contiguous
+// dimension), SWIZZLE_128B
+inline int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols,
+                        uint64_t row_stride_bytes, int elem_bytes, uint32_t box_rows) {
+  return make_tmap_2d_ex(map, base, rows, cols, row_stride_bytes,
+                         elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16,
+                         (uint32_t)(128 / elem_bytes), box_rows, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
 }  // namespace umma
