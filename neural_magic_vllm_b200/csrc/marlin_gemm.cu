@@ -343,6 +343,8 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 //   warps of a quadrant split the four 16-row k tiles of a stage between them.
 // ------------------------------------------------------------------------------------------------
 constexpr int kTmemAStageCols = kStageK / 2;  // 32
+constexpr int kTDequantWarps = 4;          // one per TMEM quadrant
+constexpr int kTThreads = 64 + kTDequantWarps * 32;
 constexpr int kTmemDCol = kAStages * kTmemAStageCols;
 
 template <int BITS, int BM>
@@ -363,7 +365,7 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
 }
 
 template <int BITS, int BM, typename T>
-__global__ void __launch_bounds__(kThreads, (BM <= 32 ? 3 : 2))
+__global__ void __launch_bounds__(kTThreads, (BM <= 32 ? 4 : 2))
 marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                         const __grid_constant__ CUtensorMap tm_s, const MarlinArgs args) {
   using P = PlanT<BITS, BM>;
@@ -392,10 +394,10 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
     tma_prefetch_desc(&tm_x);
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&full_p[s], 1);
-      mbar_init(&empty_p[s], kDequantWarps + 1);
+      mbar_init(&empty_p[s], kTDequantWarps + 1);
     }
     for (int s = 0; s < kAStages; ++s) {
-      mbar_init(&full_a[s], kDequantWarps);
+      mbar_init(&full_a[s], kTDequantWarps);
       mbar_init(&empty_a[s], 1);
     }
     mbar_init(tmem_full, 1);
@@ -457,7 +459,6 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
     }
   } else {
     const int qd = warp & 3;          // TMEM quadrant = rows 32 qd .. 32 qd + 31
-    const int kt0 = ((warp - 2) >> 2) * 2;  // this warp's two k tiles of every stage
     const int nt = qd >> 1;           // 64-column Marlin tile inside the 128-row n tile
     const int j0 = (qd & 1) * 2;      // first of its two 16-row fragments
     const int a_row = lane >> 2;
@@ -474,65 +475,59 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
         sc[i] = v | (v << 16);
       }
     }
+    // one group per 64-k stage (group_size >= 64; smaller groups take the shared-memory kernel)
     int cur_group = -1;
     int stage = 0, as = 0;
     uint32_t phase = 0, aphase = 0;
-    const uint32_t stages_u32 = smem_u32(stages);
-    const uint32_t t_lane = (uint32_t)(qd * 32) << 16;
+    const uint32_t lane_src = smem_u32(stages) + P::kXBytes + chunk_off<BITS>(0, nt) + lane * (BITS * 4) +
+                              (qd & 1) * (BITS * 2);
+    const uint32_t scale_src = smem_u32(stages) + P::kXBytes + P::kPackedBytes + (nt * 64 + 8 * a_row) * 2 +
+                               (qd & 1) * 8;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16);
     for (int kb = kb_begin; kb < kb_end; ++kb) {
       mbar_wait_bounded(&full_p[stage], phase);
-      const uint32_t w_src = stages_u32 + stage * P::kStageBytes + P::kXBytes;
-      const uint32_t s_src = w_src + P::kPackedBytes;
-      uint32_t words[2][BITS == 4 ? 2 : 4];
+      const uint32_t w_src = lane_src + stage * P::kStageBytes;
+      uint32_t words[4][BITS == 4 ? 2 : 4];
 #pragma unroll
-      for (int kk = 0; kk < 2; ++kk) {
-        const uint32_t p = w_src + chunk_off<BITS>(kt0 + kk, nt) + lane * (BITS * 4) + (qd & 1) * (BITS * 2);
+      for (int kt = 0; kt < 4; ++kt) {
         if constexpr (BITS == 4) {
-          const uint2 v = lds64(p);
-          words[kk][0] = v.x, words[kk][1] = v.y;
+          const uint2 v = lds64(w_src + kt * 1024);
+          words[kt][0] = v.x, words[kt][1] = v.y;
         } else {
-          const uint4 v = lds128(p);
-          words[kk][0] = v.x, words[kk][1] = v.y, words[kk][2] = v.z, words[kk][3] = v.w;
+          const uint4 v = lds128(w_src + kt * 1024);
+          words[kt][0] = v.x, words[kt][1] = v.y, words[kt][2] = v.z, words[kt][3] = v.w;
         }
       }
-      uint32_t scs[2][4];
-#pragma unroll
-      for (int kk = 0; kk < 2; ++kk) {
-        if (grouped) {
-          const int g = group_of(args, kb * kStageK + (kt0 + kk) * 16);
-          if (g != cur_group) {  // warp-uniform
-            cur_group = g;
-            const int g_lo = group_of(args, kb * kStageK);
-            const uint2 v = lds64(s_src + (g - g_lo) * (kTileN * 2) + (nt * 64 + 8 * a_row) * 2 + (qd & 1) * 8);
-            sc[0] = dup16(v.x, 0), sc[1] = dup16(v.x, 1), sc[2] = dup16(v.y, 0), sc[3] = dup16(v.y, 1);
-          }
+      if (grouped) {
+        const int g = group_of(args, kb * kStageK);
+        if (g != cur_group) {  // warp-uniform
+          cur_group = g;
+          const uint2 v = lds64(scale_src + stage * P::kStageBytes);
+          sc[0] = dup16(v.x, 0), sc[1] = dup16(v.x, 1), sc[2] = dup16(v.y, 0), sc[3] = dup16(v.y, 1);
         }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) scs[kk][i] = sc[i];
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty_p[stage]);  // packed words + scales are in registers
       mbar_wait_bounded(&empty_a[as], aphase ^ 1);
       fence_after_sync();
+      const uint32_t t_dst = t_lane + as * kTmemAStageCols;
 #pragma unroll
-      for (int kk = 0; kk < 2; ++kk) {
+      for (int kt = 0; kt < 4; ++kt) {
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {
           uint32_t rg[4];
           if constexpr (BITS == 4) {
-            unpack4<T>(words[kk][jj], rg);
+            unpack4<T>(words[kt][jj], rg);
           } else {
-            unpack8<T>(words[kk][2 * jj], rg[0], rg[1]);
-            unpack8<T>(words[kk][2 * jj + 1], rg[2], rg[3]);
+            unpack8<T>(words[kt][2 * jj], rg[0], rg[1]);
+            unpack8<T>(words[kt][2 * jj + 1], rg[2], rg[3]);
           }
-          rg[0] = mul2<T>(rg[0], scs[kk][2 * jj]);
-          rg[1] = mul2<T>(rg[1], scs[kk][2 * jj]);
-          rg[2] = mul2<T>(rg[2], scs[kk][2 * jj + 1]);
-          rg[3] = mul2<T>(rg[3], scs[kk][2 * jj + 1]);
+          rg[0] = mul2<T>(rg[0], sc[2 * jj]);
+          rg[1] = mul2<T>(rg[1], sc[2 * jj]);
+          rg[2] = mul2<T>(rg[2], sc[2 * jj + 1]);
+          rg[3] = mul2<T>(rg[3], sc[2 * jj + 1]);
           // rg = {b0 k-lo, b0 k-hi, b1 k-lo, b1 k-hi} -> st order {b0 lo, b1 lo, b0 hi, b1 hi}
-          tmem_st_16x128b_x2(tmem_base + t_lane + ((uint32_t)(16 * jj) << 16) + as * kTmemAStageCols +
-                                 (kt0 + kk) * 8,
-                             rg[0], rg[2], rg[1], rg[3]);
+          tmem_st_16x128b_x2(t_dst + ((uint32_t)(16 * jj) << 16) + kt * 8, rg[0], rg[2], rg[1], rg[3]);
         }
       }
       tmem_st_wait();
@@ -542,11 +537,11 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
       if (++stage == kStages) stage = 0, phase ^= 1;
       if (++as == kAStages) as = 0, aphase ^= 1;
     }
-    if (warp < 6) {
+    {
       const int n = n0 + qd * 32 + lane;
       mbar_wait_bounded(tmem_full, 0);
       fence_after_sync();
-      const uint32_t taddr = tmem_base + t_lane + kTmemDCol;
+      const uint32_t taddr = t_lane + kTmemDCol;
 #pragma unroll 1
       for (int c = 0; c < BM / 16; ++c) {
         uint32_t rr[16];
@@ -649,8 +644,13 @@ inline int pick_splits(int m, int n, int num_kb, int64_t ws_bytes) {
   const int bm = pick_bm(m);
   const int cta_n = kTileN * pick_nt(bm);
   const int tiles = ((m + bm - 1) / bm) * ((n + cta_n - 1) / cta_n);
-  if (tiles >= kNumSMs || tiles == 0) return 1;
-  int splits = (2 * kNumSMs + tiles - 1) / tiles;
+  // CTAs that are resident at once: 4 per SM for the decode kernel at BM <= 32, 2 at BM = 64, 1 for
+  // the large tiles.  Split K until one resident wave covers the grid (never past it: a second,
+  // partial wave costs more than idle SM slots).
+  const int per_sm = bm <= 32 ? 4 : bm <= 64 ? 2 : 1;
+  const int target = per_sm * kNumSMs;
+  if (tiles >= target || tiles == 0) return 1;
+  int splits = target / tiles;
   if (splits > num_kb / 4) splits = num_kb / 4;
   const int64_t per = (int64_t)m * n * 4;
   if (ws_bytes >= 0 && per > 0 && splits > ws_bytes / per) splits = (int)(ws_bytes / per);
@@ -746,7 +746,7 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   a.w_evict_first = (m_tiles == 1);
   auto kern = marlin_gemm_tmem_kernel<BITS, BM, T>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P::kBytes);
-  kern<<<dim3(m_tiles, n_tiles, splits), kThreads, P::kBytes, st>>>(tm_x, tm_w, tm_s, a);
+  kern<<<dim3(m_tiles, n_tiles, splits), kTThreads, P::kBytes, st>>>(tm_x, tm_w, tm_s, a);
   rc = check_launch("gptq_marlin_gemm");
   if (rc != B200_OK) return rc;
   if (splits > 1) {
@@ -762,7 +762,9 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
 
 template <int BITS, typename T, bool ACT>
 int dispatch_bm(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t lda, cudaStream_t st) {
-  if constexpr (!ACT) {
+  // decode kernel: ungrouped, or groups that never change inside a 64-k stage
+  const bool one_group_per_stage = p.num_groups == 1 || (p.size_k / p.num_groups) % kStageK == 0;
+  if (!ACT && one_group_per_stage) {
     switch (pick_bm(p.size_m)) {
       case 16: return launch_tmem<BITS, 16, T>(p, st);
       case 32: return launch_tmem<BITS, 32, T>(p, st);
