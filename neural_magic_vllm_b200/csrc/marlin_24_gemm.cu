@@ -1,8 +1,400 @@
-// gptq_marlin_24_gemm placeholder (kernel lands in the next commit).
-#include "common.cuh"
-extern "C" int b200_gptq_marlin_24_gemm(const b200_gptq_marlin_24_gemm_params* p, void* stream) {
-  (void)p;
-  (void)stream;
-  b200::set_error("gptq_marlin_24_gemm: not implemented yet");
-  return B200_ENOTSUP;
+// gptq_marlin_24_gemm on tcgen05 / TMEM (sm_100a): C[M,N] = A[M,K] * W, W 4-bit, 2:4 sparse along K,
+// in the reference's Marlin-24 layout (values [K/32, 2N] int32, metadata [K/32, 2N] int16, scales
+// [K/128 | 1, N] fp16).  Replaces csrc/quantization/marlin/sparse/marlin_24_cuda_kernel.cu:1015-1125
+// (mma.sp.m16n8k32).  fp16 only, like the reference (:1100-1103: group 128 or channelwise).
+//
+// HBM traffic is the compressed stream (0.375 B per dense weight) read once, through three 2-D TMA
+// boxes per 64-k stage (values, metadata, scales) plus the activation tile.  Four dequant warps (one
+// per TMEM quadrant) unpack q - 8 with the lop3/hfma2 trick, apply the group scale (one rounding,
+// bit-identical to the reference's w_24_ref), scatter each kept pair to its two of four k positions
+// with two PRMTs whose selectors come from a 16-entry shared-memory table indexed by the 4-bit
+// metadata, and write the dense fragment straight into TMEM (tcgen05.st 16x256b); the MMA
+// (kind::f16, A from TMEM, B = activations in shared memory, fp32 accumulate in TMEM) is issued by
+// one thread.  The dense MMA spends 2x the tensor work of mma.sp, which is irrelevant at the
+// decode sizes this op serves (M <= 128 in C5: weight streaming); a tcgen05.mma.sp variant is the
+// next step for prefill.
+//
+// Layout facts used below (re-derived from marlin_24_perms.py:16-48 and format_24.py:22-49, and
+// checked bit-exactly against tests/golden/marlin_24.npz):
+//   values   tile = 16 compressed k rows (32 dense k) x 64 n = 128 int32; lane i (c = i/4, r = i%4)
+//            owns words 4i..4i+3; word j holds n = 8c + 4b + j for b = 0,1 and the kept pairs of the
+//            4-groups g = r and g = r + 4:  nibbles (0,4) = (b0, g=r), (1,5) = (b0, g=r+4),
+//            (2,6) = (b1, g=r), (3,7) = (b1, g=r+4)
+//   metadata per (32-k row, 64-n chunk) 256 bytes; the 8 bytes at unit u = (j%2) + 16 (j/2) + 2c are
+//            four int16 [b0 groups 0-3, b1 groups 0-3, b0 groups 4-7, b1 groups 4-7] for n = 8c+4b+j;
+//            group g's nibble = idx0 | idx1 << 2 (positions of the two kept values)
+//   scales   grouped rows: position 8c + 2j + b holds column 8c + 4b + j; single row: natural order
+// A TMEM quadrant q = 2 nt + b takes the 32 columns {64 nt + 8c + 4b + j}: TMEM lane p of the
+// quadrant holds column 64 nt + 8 (p%8) + 4b + 2 (p/16) + (p%16)/8 (undone by the epilogue).
+#include "marlin_dequant.cuh"
+#include "umma.cuh"
+
+namespace b200 {
+namespace {
+
+using namespace umma;
+using namespace marlin;
+
+constexpr int kTileN = 128;
+constexpr int kStageK = 64;
+constexpr int kStages = 6;
+constexpr int kAStages = 3;
+constexpr int kACols = kStageK / 2;          // 32 TMEM columns per dense 64-k stage
+constexpr int kDCol = kAStages * kACols;     // accumulator behind the A ring
+constexpr int kWarps = 4;                    // dequant warps
+constexpr int kThreads = 64 + kWarps * 32;
+constexpr int kValBytes = 2 * 1024;          // 2 rows of 32 dense k x 128 n
+constexpr int kMetaBytes = 2 * 512;
+constexpr int kScaleBytes = 1024;            // one row (256 B) padded: stages stay 1 KiB aligned
+
+struct Args24 {
+  void* c;
+  float* partial;
+  const uint16_t* scales;
+  int m, n, k;
+  int num_groups, group_shift;
+  int kb_per_split, num_kb;
+};
+
+template <int BM>
+struct Plan24 {
+  static constexpr int kXBytes = BM * 128;
+  static constexpr int kStageBytes = kXBytes + kValBytes + kMetaBytes + kScaleBytes;
+  static constexpr int kBytes = kStages * kStageBytes + 1024 + 512;
+  static constexpr uint32_t kTmemCols = kDCol + BM <= 128 ? 128 : 256;
+};
+
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.b32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void tmem_st_16x256b(uint32_t taddr, uint32_t r0, uint32_t r1, uint32_t r2,
+                                                uint32_t r3) {
+  // thread t: r0,r1 = (lane t/4, columns 2(t%4), 2(t%4)+1), r2,r3 = (lane t/4 + 8, same columns)
+  asm volatile("tcgen05.st.sync.aligned.16x256b.x1.b32 [%0], {%1,%2,%3,%4};" ::"r"(taddr), "r"(r0),
+               "r"(r1), "r"(r2), "r"(r3)
+               : "memory");
+}
+
+// PRMT selectors that place the kept pair (v0 = bytes 1:0, v1 = bytes 3:2 of the source, zero =
+// bytes of the second operand) at positions idx0, idx1 of a 4-group: .x builds k positions 0,1,
+// .y builds positions 2,3
+__device__ __forceinline__ uint2 expand_selectors(int m4) {
+  const int i0 = m4 & 3, i1 = m4 >> 2;
+  auto sel = [&](int pos) -> uint32_t { return i0 == pos ? 0x10u : (i1 == pos ? 0x32u : 0x44u); };
+  return make_uint2(sel(0) | (sel(1) << 8), sel(2) | (sel(3) << 8));
+}
+
+template <int BM>
+__global__ void __launch_bounds__(kThreads, (BM <= 32 ? 4 : 2))
+marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+                     const __grid_constant__ CUtensorMap tm_m, const __grid_constant__ CUtensorMap tm_s,
+                     const Args24 args) {
+  using P = Plan24<BM>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stages + kStages * P::kStageBytes);
+  uint64_t* full_p = bars;
+  uint64_t* empty_p = full_p + kStages;
+  uint64_t* full_a = empty_p + kStages;
+  uint64_t* empty_a = full_a + kAStages;
+  uint64_t* tmem_full = empty_a + kAStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint2* lut = reinterpret_cast<uint2*>(bars + 32);  // 16 x 8 bytes, 256 bytes into the barrier block
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM;
+  const int n0 = blockIdx.y * kTileN;
+  const int split = blockIdx.z;
+  const int kb_begin = split * args.kb_per_split;
+  const int kb_end = min(kb_begin + args.kb_per_split, args.num_kb);
+  const bool grouped = args.num_groups > 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_x);
+    tma_prefetch_desc(&tm_w);
+    tma_prefetch_desc(&tm_m);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_p[s], 1);
+      mbar_init(&empty_p[s], kWarps + 1);
+    }
+    for (int s = 0; s < kAStages; ++s) {
+      mbar_init(&full_a[s], kWarps);
+      mbar_init(&empty_a[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_mbar_init();
+  }
+  if (threadIdx.x < 16) lut[threadIdx.x] = expand_selectors(threadIdx.x);
+  if (warp == 1) tmem_alloc(tmem_slot, P::kTmemCols);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    const uint64_t pol_w = l2_policy_evict_first();
+    const uint64_t pol_x = l2_policy_evict_last();
+    const uint32_t tx_bytes = P::kXBytes + kValBytes + kMetaBytes + (grouped ? kTileN * 2 : 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = kb_begin; kb < kb_end; ++kb) {
+      mbar_wait_bounded(&empty_p[stage], phase ^ 1);
+      if (lane == 0) {
+        uint8_t* x_dst = stages + stage * P::kStageBytes;
+        uint8_t* w_dst = x_dst + P::kXBytes;
+        mbar_arrive_expect_tx(&full_p[stage], tx_bytes);
+        tma_load_2d(x_dst, &tm_x, kb * kStageK, m0, &full_p[stage], pol_x);
+        tma_load_2d(w_dst, &tm_w, n0 * 2, kb * 2, &full_p[stage], pol_w);
+        tma_load_2d(w_dst + kValBytes, &tm_m, n0 * 2, kb * 2, &full_p[stage], pol_w);
+        if (grouped)
+          tma_load_2d(w_dst + kValBytes + kMetaBytes, &tm_s, n0, (kb * kStageK) >> args.group_shift,
+                      &full_p[stage], pol_x);
+      }
+      __syncwarp();
+      if (++stage == kStages) stage = 0, phase ^= 1;
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = instr_desc<KIND_F16>(kTileN, BM);
+      int stage = 0, as = 0;
+      uint32_t phase = 0, aphase = 0;
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        mbar_wait_bounded(&full_p[stage], phase);
+        mbar_wait_bounded(&full_a[as], aphase);
+        fence_after_sync();
+        const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          mma_ts_f16(tmem_base + kDCol, tmem_base + as * kACols + k * 8, desc_advance(dx, k * 32), idesc,
+                     (kb > kb_begin || k > 0) ? 1u : 0u);
+        mma_commit(&empty_a[as]);
+        mma_commit(&empty_p[stage]);
+        if (++stage == kStages) stage = 0, phase ^= 1;
+        if (++as == kAStages) as = 0, aphase ^= 1;
+      }
+      mma_commit(tmem_full);
+    }
+  } else {
+    const int qd = warp & 3;  // TMEM quadrant
+    const int nt = qd >> 1, hb = qd & 1;
+    const int c = lane >> 2, r = lane & 3;
+    const uint32_t lut_u32 = smem_u32(lut);
+    const uint32_t msh = 16 * hb + 4 * r;  // this thread's metadata nibble inside each 32-bit word
+    uint32_t sc[4];                        // sc[j]: scale of n = 64 nt + 8c + 4 hb + j, both halves
+#pragma unroll
+    for (int j = 0; j < 4; ++j) sc[j] = 0x3c003c00u;
+    if (!grouped) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int n = n0 + nt * 64 + 8 * c + 4 * hb + j;
+        const uint32_t v = n < args.n ? args.scales[n] : 0;
+        sc[j] = v | (v << 16);
+      }
+    }
+    const uint32_t stage0 = smem_u32(stages) + P::kXBytes;
+    const uint32_t val_off = nt * 512 + lane * 16;
+    const uint32_t meta_off = kValBytes + nt * 256 + c * 16;
+    const uint32_t scale_off = kValBytes + kMetaBytes + (nt * 64 + 8 * c) * 2;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16);
+    int cur_group = -1;
+    int stage = 0, as = 0;
+    uint32_t phase = 0, aphase = 0;
+    for (int kb = kb_begin; kb < kb_end; ++kb) {
+      mbar_wait_bounded(&full_p[stage], phase);
+      const uint32_t base = stage0 + stage * P::kStageBytes;
+      uint32_t words[2][4], meta[2][8];
+#pragma unroll
+      for (int kt = 0; kt < 2; ++kt) {
+        const uint4 w = lds128(base + val_off + kt * 1024);
+        words[kt][0] = w.x >> (8 * hb), words[kt][1] = w.y >> (8 * hb);
+        words[kt][2] = w.z >> (8 * hb), words[kt][3] = w.w >> (8 * hb);
+        const uint4 ma = lds128(base + meta_off + kt * 512);        // j = 0, 1
+        const uint4 mb = lds128(base + meta_off + kt * 512 + 128);  // j = 2, 3
+        meta[kt][0] = ma.x, meta[kt][1] = ma.y, meta[kt][2] = ma.z, meta[kt][3] = ma.w;
+        meta[kt][4] = mb.x, meta[kt][5] = mb.y, meta[kt][6] = mb.z, meta[kt][7] = mb.w;
+      }
+      if (grouped) {
+        const int g = (kb * kStageK) >> args.group_shift;
+        if (g != cur_group) {  // warp-uniform
+          cur_group = g;
+          const uint4 v = lds128(base + scale_off);
+          sc[0] = dup16(v.x, hb), sc[1] = dup16(v.y, hb), sc[2] = dup16(v.z, hb), sc[3] = dup16(v.w, hb);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_p[stage]);
+      mbar_wait_bounded(&empty_a[as], aphase ^ 1);
+      fence_after_sync();
+      const uint32_t t_dst = t_lane + as * kACols;
+#pragma unroll
+      for (int kt = 0; kt < 2; ++kt) {
+#pragma unroll
+        for (int bb = 0; bb < 2; ++bb) {
+          uint32_t lo[2][2], hi[2][2];  // [row c | row c+8][k pair]: groups r (lo) and r + 4 (hi)
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int j = 2 * bb + u;
+            constexpr uint32_t LO = 0x000f000f, HI = 0x00f000f0, EX = 0x64006400;
+            constexpr uint32_t SUB = 0x64086408, MUL = 0x2c002c00, ADD = 0xd480d480;
+            const uint32_t q = words[kt][j];
+            const uint32_t v_lo = mul2<__half>(h2_sub(lop3<kAndOr>(q, LO, EX), SUB), sc[j]);
+            const uint32_t v_hi = mul2<__half>(h2_fma(lop3<kAndOr>(q, HI, EX), MUL, ADD), sc[j]);
+            const uint2 e_lo = lds64(lut_u32 + (((meta[kt][2 * j] >> msh) & 0xf) << 3));
+            const uint2 e_hi = lds64(lut_u32 + (((meta[kt][2 * j + 1] >> msh) & 0xf) << 3));
+            lo[u][0] = __byte_perm(v_lo, 0, e_lo.x), lo[u][1] = __byte_perm(v_lo, 0, e_lo.y);
+            hi[u][0] = __byte_perm(v_hi, 0, e_hi.x), hi[u][1] = __byte_perm(v_hi, 0, e_hi.y);
+          }
+          const uint32_t t = t_dst + ((uint32_t)(16 * bb) << 16) + kt * 16;
+          tmem_st_16x256b(t, lo[0][0], lo[0][1], lo[1][0], lo[1][1]);          // dense k 4r .. 4r+3
+          tmem_st_16x256b(t + 8, hi[0][0], hi[0][1], hi[1][0], hi[1][1]);      // dense k 16+4r ..
+        }
+      }
+      tmem_st_wait();
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full_a[as]);
+      if (++stage == kStages) stage = 0, phase ^= 1;
+      if (++as == kAStages) as = 0, aphase ^= 1;
+    }
+    // epilogue: TMEM lane p of quadrant (nt, hb) is column 8 (p%8) + 4 hb + 2 (p/16) + (p%16)/8
+    {
+      const int n = n0 + nt * 64 + 8 * (lane & 7) + 4 * hb + 2 * (lane >> 4) + ((lane & 15) >> 3);
+      mbar_wait_bounded(tmem_full, 0);
+      fence_after_sync();
+      const uint32_t taddr = t_lane + kDCol;
+#pragma unroll 1
+      for (int cc = 0; cc < BM / 16; ++cc) {
+        if (m0 + cc * 16 >= args.m) break;
+        uint32_t rr[16];
+        tmem_ld16(taddr + cc * 16, rr);
+        tmem_ld_wait();
+        if (n < args.n) {
+          if (args.partial != nullptr) {
+            float* ws = args.partial + ((int64_t)split * args.m) * args.n;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int mm = m0 + cc * 16 + j;
+              if (mm < args.m) ws[(int64_t)mm * args.n + n] = __uint_as_float(rr[j]);
+            }
+          } else {
+            __half* out = reinterpret_cast<__half*>(args.c);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int mm = m0 + cc * 16 + j;
+              if (mm < args.m) out[(int64_t)mm * args.n + n] = __float2half_rn(__uint_as_float(rr[j]));
+            }
+          }
+        }
+      }
+      fence_before_sync();
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    fence_after_sync();
+    tmem_dealloc(tmem_base, P::kTmemCols);
+  }
+}
+
+__global__ void __launch_bounds__(256) splitk_sum24_kernel(__half* __restrict__ out, const float* __restrict__ ws,
+                                                           int64_t total, int splits) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    int s = 0;
+    for (; s + 4 <= splits; s += 4) {
+      const float v0 = ws[(int64_t)s * total + i], v1 = ws[(int64_t)(s + 1) * total + i];
+      const float v2 = ws[(int64_t)(s + 2) * total + i], v3 = ws[(int64_t)(s + 3) * total + i];
+      acc += v0, acc += v1, acc += v2, acc += v3;
+    }
+    for (; s < splits; ++s) acc += ws[(int64_t)s * total + i];
+    out[i] = __float2half_rn(acc);
+  }
+}
+
+template <int BM>
+int launch24(const b200_gptq_marlin_24_gemm_params& p, cudaStream_t st) {
+  using P = Plan24<BM>;
+  CUtensorMap tm_x, tm_w, tm_m, tm_s;
+  int rc = make_tmap_2d(&tm_x, p.a, (uint64_t)p.size_m, (uint64_t)p.size_k, (uint64_t)p.size_k * 2, 2, BM);
+  if (rc != B200_OK) return rc;
+  const uint64_t rows = (uint64_t)p.size_k / 32, cols = (uint64_t)p.size_n * 2;
+  rc = make_tmap_2d_ex(&tm_w, p.b_q_weight, rows, cols, cols * 4, CU_TENSOR_MAP_DATA_TYPE_INT32, 256, 2,
+                       CU_TENSOR_MAP_SWIZZLE_NONE);
+  if (rc != B200_OK) return rc;
+  rc = make_tmap_2d_ex(&tm_m, p.b_meta, rows, cols, cols * 2, CU_TENSOR_MAP_DATA_TYPE_UINT16, 256, 2,
+                       CU_TENSOR_MAP_SWIZZLE_NONE);
+  if (rc != B200_OK) return rc;
+  rc = make_tmap_2d_ex(&tm_s, p.b_scales, (uint64_t)p.num_groups, (uint64_t)p.size_n, (uint64_t)p.size_n * 2,
+                       CU_TENSOR_MAP_DATA_TYPE_UINT16, kTileN, 1, CU_TENSOR_MAP_SWIZZLE_NONE);
+  if (rc != B200_OK) return rc;
+  Args24 a{};
+  a.c = p.c;
+  a.scales = reinterpret_cast<const uint16_t*>(p.b_scales);
+  a.m = p.size_m, a.n = p.size_n, a.k = p.size_k;
+  a.num_groups = p.num_groups;
+  a.group_shift = p.num_groups > 1 ? __builtin_ctz(p.size_k / p.num_groups) : 30;
+  a.num_kb = p.size_k / kStageK;
+  const int m_tiles = (p.size_m + BM - 1) / BM, n_tiles = (p.size_n + kTileN - 1) / kTileN;
+  const int tiles = m_tiles * n_tiles;
+  const int target = (BM <= 32 ? 4 : 2) * kNumSMs;
+  int splits = tiles >= target ? 1 : target / tiles;
+  if (splits > a.num_kb / 4) splits = a.num_kb / 4;
+  const int64_t per = (int64_t)p.size_m * p.size_n * 4;
+  if (p.splitk_ws == nullptr) splits = 1;
+  else if (splits > p.splitk_ws_bytes / per) splits = (int)(p.splitk_ws_bytes / per);
+  if (splits < 1) splits = 1;
+  a.kb_per_split = (a.num_kb + splits - 1) / splits;
+  splits = (a.num_kb + a.kb_per_split - 1) / a.kb_per_split;
+  a.partial = splits > 1 ? reinterpret_cast<float*>(p.splitk_ws) : nullptr;
+  auto kern = marlin24_gemm_kernel<BM>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P::kBytes);
+  kern<<<dim3(m_tiles, n_tiles, splits), kThreads, P::kBytes, st>>>(tm_x, tm_w, tm_m, tm_s, a);
+  rc = check_launch("gptq_marlin_24_gemm");
+  if (rc != B200_OK) return rc;
+  if (splits > 1) {
+    const int64_t total = (int64_t)p.size_m * p.size_n;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    splitk_sum24_kernel<<<blocks, 256, 0, st>>>((__half*)p.c, a.partial, total, splits);
+    rc = check_launch("gptq_marlin_24_gemm split-K sum");
+  }
+  return rc;
+}
+
+}  // namespace
+}  // namespace b200
+
+extern "C" int b200_gptq_marlin_24_gemm(const b200_gptq_marlin_24_gemm_params* pp, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(pp != nullptr, B200_EINVAL, "gptq_marlin_24_gemm: null params");
+  const b200_gptq_marlin_24_gemm_params& p = *pp;
+  // marlin_24_cuda_kernel.cu:1024-1116
+  B200_REQUIRE(p.num_bits == 4 || p.num_bits == 8, B200_EINVAL, "num_bits must be 4 or 8. Got = %d", p.num_bits);
+  B200_REQUIRE(p.num_bits == 4, B200_ENOTSUP,
+               "gptq_marlin_24_gemm: 8-bit 2:4 weights are not implemented yet (4-bit only)");
+  B200_REQUIRE(p.size_m >= 0 && p.size_n > 0 && p.size_k > 0, B200_EINVAL, "gptq_marlin_24_gemm: bad sizes");
+  if (p.size_m == 0) return B200_OK;
+  B200_REQUIRE(p.size_k % 128 == 0, B200_EINVAL, "size_k = %d is not divisible by 128", p.size_k);
+  B200_REQUIRE(p.size_n % 128 == 0, B200_EINVAL, "size_n = %d is not divisible by 128", p.size_n);
+  B200_REQUIRE(p.c && p.a && p.b_q_weight && p.b_meta && p.b_scales, B200_EINVAL,
+               "gptq_marlin_24_gemm: null pointer");
+  B200_REQUIRE(p.num_groups == 1 || p.size_k / p.num_groups == 128, B200_EINVAL, "Unexpected groupsize = %d",
+               p.num_groups > 0 ? p.size_k / p.num_groups : -1);
+  B200_REQUIRE(((uintptr_t)p.a & 15) == 0 && ((uintptr_t)p.b_q_weight & 15) == 0 &&
+                   ((uintptr_t)p.b_meta & 15) == 0 && ((uintptr_t)p.b_scales & 15) == 0,
+               B200_EINVAL, "gptq_marlin_24_gemm: operands must be 16-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (p.size_m <= 16) return launch24<16>(p, st);
+  if (p.size_m <= 32) return launch24<32>(p, st);
+  return launch24<64>(p, st);
 }

@@ -42,6 +42,7 @@ struct MarlinArgs {
   int s_rows;                  // scale rows fetched per stage (0: scales are not staged)
   int kb_per_split, num_kb;
   int w_evict_first;
+  int32_t* locks;  // decode kernel, split-K: arrival counter per n tile (zero on entry, zero on exit)
 };
 
 // NT = 128-row sub-tiles of n per CTA: large-M tiles take 2 so every activation tile fetched from
@@ -392,6 +393,8 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_x);
+    tma_prefetch_desc(&tm_w);
+    if (args.s_rows > 0) tma_prefetch_desc(&tm_s);
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&full_p[s], 1);
       mbar_init(&empty_p[s], kTDequantWarps + 1);
@@ -542,13 +545,15 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
       mbar_wait_bounded(tmem_full, 0);
       fence_after_sync();
       const uint32_t taddr = t_lane + kTmemDCol;
+      const bool split_k = args.partial != nullptr;
 #pragma unroll 1
       for (int c = 0; c < BM / 16; ++c) {
+        if (m0 + c * 16 >= args.m) break;
         uint32_t rr[16];
         tmem_ld16(taddr + c * 16, rr);
         tmem_ld_wait();
         if (n < args.n) {
-          if (args.partial != nullptr) {
+          if (split_k) {
             float* ws = args.partial + ((int64_t)split * args.m) * args.n;
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
@@ -566,6 +571,40 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
         }
       }
       fence_before_sync();
+      if (split_k && args.locks != nullptr) {
+        // the last split to arrive at this n tile sums the partials (fixed order: deterministic)
+        // and hands the counter back as zero -- no second kernel behind the GEMM
+        uint32_t* flag = tmem_slot + 1;
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (warp == 2 && lane == 0) {
+          const int old = atomicAdd(&args.locks[blockIdx.y], 1);
+          *flag = (old == (int)gridDim.z - 1) ? 1u : 0u;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (*flag != 0 && n < args.n) {
+          __threadfence();
+          const int splits = gridDim.z;
+          const int64_t plane = (int64_t)args.m * args.n;
+          T* out = reinterpret_cast<T*>(args.c);
+          const int m_end = min(m0 + BM, args.m);
+          for (int mm = m0; mm < m_end; ++mm) {
+            const float* src = args.partial + (int64_t)mm * args.n + n;
+            float acc = 0.f;
+            int sidx = 0;
+            for (; sidx + 8 <= splits; sidx += 8) {
+              float v[8];
+#pragma unroll
+              for (int u = 0; u < 8; ++u) v[u] = __ldcg(src + (int64_t)(sidx + u) * plane);
+#pragma unroll
+              for (int u = 0; u < 8; ++u) acc += v[u];
+            }
+            for (; sidx < splits; ++sidx) acc += __ldcg(src + (int64_t)sidx * plane);
+            out[(int64_t)mm * args.n + n] = DT<T>::from_f(acc);
+          }
+          if (warp == 2 && lane == 0) args.locks[blockIdx.y] = 0;
+        }
+      }
     }
   }
   __syncthreads();
@@ -746,18 +785,39 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   a.w_evict_first = (m_tiles == 1);
   auto kern = marlin_gemm_tmem_kernel<BITS, BM, T>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P::kBytes);
-  kern<<<dim3(m_tiles, n_tiles, splits), kTThreads, P::kBytes, st>>>(tm_x, tm_w, tm_s, a);
-  rc = check_launch("gptq_marlin_gemm");
-  if (rc != B200_OK) return rc;
-  if (splits > 1) {
+  // tiny M: the last split to arrive reduces in-kernel; otherwise a grid-wide reduce kernel
+  a.locks = (splits > 1 && m_tiles == 1 && p.size_m <= 4) ? p.workspace : nullptr;
+  // (programmatic dependent launch was measured here and lost: early-resident dependents take
+  // TMEM/shared-memory slots from the running grid -- 29 -> 38 us on gate_up)
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(m_tiles, n_tiles, splits);
+  cfg.blockDim = dim3(kTThreads);
+  cfg.dynamicSmemBytes = P::kBytes;
+  cfg.stream = st;
+  cfg.attrs = nullptr;
+  cfg.numAttrs = 0;
+  cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_x, tm_w, tm_s, a);
+  if (le != cudaSuccess) {
+    cudaGetLastError();
+    set_error("gptq_marlin_gemm: launch failed: %s", cudaGetErrorString(le));
+    return B200_ECUDA;
+  }
+  if (splits > 1 && a.locks == nullptr) {
     const int64_t total = (int64_t)p.size_m * p.size_n;
     int blocks = (int)((total / 4 + 255) / 256);
     if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
     if (blocks < 1) blocks = 1;
-    splitk_sum_kernel<T><<<blocks, 256, 0, st>>>((T*)p.c, a.partial, total, splits);
-    rc = check_launch("gptq_marlin_gemm split-K sum");
+    cfg.gridDim = dim3(blocks);
+    cfg.blockDim = dim3(256);
+    cfg.dynamicSmemBytes = 0;
+    le = cudaLaunchKernelEx(&cfg, splitk_sum_kernel<T>, (T*)p.c, (const float*)a.partial, total, splits);
+    if (le != cudaSuccess) {
+      cudaGetLastError();
+      set_error("gptq_marlin_gemm split-K sum: launch failed: %s", cudaGetErrorString(le));
+      return B200_ECUDA;
+    }
   }
-  return rc;
+  return B200_OK;
 }
 
 template <int BITS, typename T, bool ACT>

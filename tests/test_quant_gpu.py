@@ -410,3 +410,63 @@ def test_marlin_gemm_rejects_bad_arguments(ops):
         ops.gptq_marlin_gemm(a, q, s, e, e, torch.zeros(1, dtype=torch.int32, device=DEV), 4, 4, 64, 128, True)
     with pytest.raises(RuntimeError):
         ops.gptq_marlin_gemm(a.float(), q, s.float(), e, e, _ws(64), 4, 4, 64, 128, True)  # dtype
+
+
+# ------------------------------------------------------------------------------------------
+# gptq_marlin_24_gemm (test_marlin_gemm.py:182-229): 2:4 sparse + 4-bit
+# ------------------------------------------------------------------------------------------
+def _marlin24_check(ops, a, mq, meta, ms, w_ref, bits, m, n, k):
+    out = ops.gptq_marlin_24_gemm(a, mq.to(DEV), meta.to(DEV), ms.to(DEV), _ws(n, par=64, thread_n=128),
+                                  bits, m, n, k)
+    ref = torch.matmul(a.float(), w_ref.to(DEV).float())
+    diff = qr.compute_max_diff(out.float(), ref)
+    assert diff < 0.04, diff  # the reference's bar
+    err = (out.float() - ref).abs()
+    tol = 1e-2 * ref.abs() + 2e-3 * ref.abs().max() + 1e-3
+    assert bool((err <= tol).all()), f"max err {err.max()} vs scale {ref.abs().max()}"
+
+
+@pytest.mark.parametrize("group", [-1, 128])
+@pytest.mark.parametrize("mnk", MNK)
+def test_marlin_24_gemm(ops, group, mnk):
+    mf, nf, kf = mnk
+    m, n, k = mf, 512 * nf, 128 * kf
+    torch.manual_seed(0)
+    a = torch.randn(m, k, dtype=torch.half, device=DEV)
+    w = torch.randn(k, n, dtype=torch.half)
+    w_ref, mq, meta, ms = qr.marlin_24_quantize(w, 4, group)
+    _marlin24_check(ops, a, mq, meta, ms, w_ref, 4, m, n, k)
+
+
+@pytest.mark.parametrize("m", [1, 2, 16, 17, 32, 33, 64, 100, 128, 200])
+def test_marlin_24_gemm_m_sweep(ops, m):
+    torch.manual_seed(1)
+    k, n = 1024, 384
+    a = torch.randn(m, k, dtype=torch.half, device=DEV)
+    w_ref, mq, meta, ms = qr.marlin_24_quantize(torch.randn(k, n, dtype=torch.half), 4, 128)
+    _marlin24_check(ops, a, mq, meta, ms, w_ref, 4, m, n, k)
+
+
+@pytest.mark.parametrize("tag,k,n", [("s24_k128_n128_b4_g-1", 128, 128), ("s24_k256_n128_b4_g128", 256, 128)])
+def test_marlin_24_golden_dequant_exact(ops, tag, k, n):
+    """a = identity: the GEMM returns the dequantised 2:4 weight itself, which must equal the
+    reference's w_24_ref bit for bit (fixtures generated from the reference's own Python)."""
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "marlin_24.npz"))
+    mq = torch.from_numpy(g[tag + "_marlin_q"]); meta = torch.from_numpy(g[tag + "_meta"])
+    ms = torch.from_numpy(g[tag + "_marlin_s"]); w_ref = torch.from_numpy(g[tag + "_w_ref"])
+    a = torch.eye(k, dtype=torch.half, device=DEV)
+    out = ops.gptq_marlin_24_gemm(a, mq.to(DEV), meta.to(DEV), ms.to(DEV), _ws(n, par=64, thread_n=128), 4, k, n, k)
+    assert torch.equal(out.cpu(), w_ref)
+
+
+def test_marlin_24_errors(ops):
+    a = torch.zeros(4, 128, dtype=torch.half, device=DEV)
+    q = torch.zeros(4, 256, dtype=torch.int32, device=DEV)
+    meta = torch.zeros(4, 256, dtype=torch.int16, device=DEV)
+    s = torch.ones(1, 128, dtype=torch.half, device=DEV)
+    with pytest.raises(RuntimeError):
+        ops.gptq_marlin_24_gemm(a, q, meta, s, _ws(128, 64, 128), 3, 4, 128, 128)        # num_bits
+    with pytest.raises(RuntimeError):
+        ops.gptq_marlin_24_gemm(a, q, meta, s, _ws(128, 64, 128), 4, 5, 128, 128)        # size_m mismatch
+    with pytest.raises(RuntimeError):
+        ops.gptq_marlin_24_gemm(a.bfloat16(), q, meta, s.bfloat16(), _ws(128, 64, 128), 4, 4, 128, 128)
