@@ -1,0 +1,219 @@
+"""Llama-3-8B W4A16 (gptq_marlin, group 128) decode tokens/s — BASELINE.json metric (i), SURVEY.md §8(d).
+
+A minimal decoder (32 layers, hidden 4096, 32 q / 8 kv heads, D 128, inter 14336, vocab 128256) whose
+hot ops are this repo's kernels through the reference's op surface: gptq_marlin_gemm for the four
+linears, reshape_and_cache + paged_attention_v1/v2 over the block-table KV cache.  RMSNorm, RoPE,
+SiLU*mul, residual adds, the fp16 lm_head and greedy argmax are plain torch ops (SURVEY.md §8(f)
+lists their fusion as the next row).  Scheduler, sampler and tokenizer are excluded (stated).
+
+Tensor parallel: launched under torchrun, rank r owns q heads / kv heads / the
+column shards of qkv and gate_up and the row (K) shards of o and down; the two partial sums per
+layer are all-reduced by NCCL inside the captured CUDA graph (linear.py:792-793 of the reference).
+
+Random-init quantized weights (any int4 pattern is a valid weight), context filled with random KV.
+
+  python benchmarks/decode_bench.py --batches 1,8,64,256 --ctx 1024 --steps 50
+  python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 benchmarks/decode_bench.py
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+HIDDEN, HEADS, KV_HEADS, HEAD, INTER, VOCAB, LAYERS = 4096, 32, 8, 128, 14336, 128256, 32
+BLOCK = 16
+
+
+class QLinear:
+    """One gptq_marlin W4A16 g128 linear shard [k, n] with random packed weights."""
+
+    def __init__(self, ops, k, n, gen):
+        self.ops, self.k, self.n = ops, k, n
+        self.q = torch.randint(-2**31, 2**31 - 1, (k // 16, n * 2), dtype=torch.int32, device="cuda", generator=gen)
+        self.s = (torch.rand(k // 128, n, device="cuda", generator=gen) * 0.004 + 0.0005).half()
+        self.e = torch.empty(0, dtype=torch.int32, device="cuda")
+        self.ws = torch.zeros(max(n // 64, 1) * 16, dtype=torch.int32, device="cuda")
+
+    def bytes(self):
+        return self.q.numel() * 4 + self.s.numel() * 2
+
+    def __call__(self, x):
+        return self.ops.gptq_marlin_gemm(x, self.q, self.s, self.e, self.e, self.ws, 4, x.shape[0], self.n,
+                                         self.k, True)
+
+
+class Layer:
+    def __init__(self, ops, tp, gen, num_blocks):
+        self.h, self.kvh = HEADS // tp, max(KV_HEADS // tp, 1)
+        self.qkv = QLinear(ops, HIDDEN, (self.h + 2 * self.kvh) * HEAD, gen)
+        self.o = QLinear(ops, self.h * HEAD, HIDDEN, gen)
+        self.gate_up = QLinear(ops, HIDDEN, 2 * INTER // tp, gen)
+        self.down = QLinear(ops, INTER // tp, HIDDEN, gen)
+        self.ln1 = torch.ones(HIDDEN, dtype=torch.half, device="cuda")
+        self.ln2 = torch.ones(HIDDEN, dtype=torch.half, device="cuda")
+        s = HEAD ** -0.5
+        self.kc = torch.empty(num_blocks, self.kvh, HEAD // 8, BLOCK, 8, dtype=torch.half, device="cuda").uniform_(-s, s)
+        self.vc = torch.empty(num_blocks, self.kvh, HEAD, BLOCK, dtype=torch.half, device="cuda").uniform_(-s, s)
+
+    def linear_bytes(self):
+        return self.qkv.bytes() + self.o.bytes() + self.gate_up.bytes() + self.down.bytes()
+
+
+def rope(x, cos, sin):  # neox style, x [B, H, D]
+    x1, x2 = x[..., : HEAD // 2], x[..., HEAD // 2:]
+    return torch.cat((x1 * cos - x2 * sin, x2 * cos + x1 * sin), dim=-1)
+
+
+class Decoder:
+    def __init__(self, ops, tp, rank, batch, ctx, lm_head=True):
+        self.ops, self.tp, self.batch, self.ctx = ops, tp, batch, ctx
+        gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
+        blocks_per_seq = (ctx + BLOCK) // BLOCK
+        self.num_blocks = batch * blocks_per_seq
+        self.layers = [Layer(ops, tp, gen, self.num_blocks) for _ in range(LAYERS)]
+        self.norm = torch.ones(HIDDEN, dtype=torch.half, device="cuda")
+        self.lm_head = (torch.randn(VOCAB // tp, HIDDEN, device="cuda", generator=gen) * 0.02).half() if lm_head else None
+        self.embed = (torch.randn(4096, HIDDEN, device="cuda", generator=gen) * 0.02).half()
+        perm = torch.randperm(self.num_blocks, device="cuda", generator=gen).to(torch.int32)
+        self.block_tables = perm.view(batch, blocks_per_seq).contiguous()
+        self.seq_lens = torch.full((batch,), ctx + 1, dtype=torch.int32, device="cuda")
+        last = self.block_tables[:, ctx // BLOCK].to(torch.int64)
+        self.slots = last * BLOCK + ctx % BLOCK
+        ang = (ctx * 500000.0 ** (-torch.arange(0, HEAD, 2, device="cuda").float() / HEAD))
+        self.cos, self.sin = ang.cos().half(), ang.sin().half()
+        self.tokens = torch.randint(0, 4096, (batch,), device="cuda", generator=gen)
+        h = self.layers[0].h
+        self.parts = (ctx + 1 + 511) // 512
+        self.use_v1 = self.parts == 1 or batch * h > 512  # paged_attn.py:118-119 of the reference
+        self.tmp = torch.empty(batch, h, self.parts, HEAD, dtype=torch.half, device="cuda")
+        self.es = torch.empty(batch, h, self.parts, dtype=torch.float32, device="cuda")
+        self.ml = torch.empty_like(self.es)
+
+    def step(self):
+        ops, tp = self.ops, self.tp
+        x = self.embed[self.tokens]
+        res = x
+        for L in self.layers:
+            hn = F.rms_norm(res, (HIDDEN,), L.ln1, 1e-5)
+            qkv = L.qkv(hn)
+            q, k, v = qkv.split([L.h * HEAD, L.kvh * HEAD, L.kvh * HEAD], dim=-1)
+            q = rope(q.view(-1, L.h, HEAD), self.cos, self.sin)
+            k = rope(k.view(-1, L.kvh, HEAD), self.cos, self.sin)
+            v = v.reshape(-1, L.kvh, HEAD)
+            ops.reshape_and_cache(k, v, L.kc, L.vc, self.slots, "auto", 1.0)
+            out = torch.empty_like(q)
+            if self.use_v1:
+                ops.paged_attention_v1(out, q, L.kc, L.vc, L.kvh, HEAD ** -0.5, self.block_tables, self.seq_lens,
+                                       BLOCK, self.ctx + 1, None, "auto", 1.0)
+            else:
+                ops.paged_attention_v2(out, self.es, self.ml, self.tmp, q, L.kc, L.vc, L.kvh, HEAD ** -0.5,
+                                       self.block_tables, self.seq_lens, BLOCK, self.ctx + 1, None, "auto", 1.0)
+            o = L.o(out.view(-1, L.h * HEAD))
+            if tp > 1:
+                dist.all_reduce(o)
+            res = res + o
+            hn = F.rms_norm(res, (HIDDEN,), L.ln2, 1e-5)
+            gu = L.gate_up(hn)
+            act = F.silu(gu[:, : INTER // tp]) * gu[:, INTER // tp:]
+            d = L.down(act)
+            if tp > 1:
+                dist.all_reduce(d)
+            res = res + d
+        hn = F.rms_norm(res, (HIDDEN,), self.norm, 1e-5)
+        if self.lm_head is not None:
+            logits = hn @ self.lm_head.t()
+            self.tokens.copy_(logits.argmax(-1) % 4096)  # greedy on the local vocab shard (no gather: stated)
+        return hn
+
+    def linear_bytes(self):
+        return sum(L.linear_bytes() for L in self.layers)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batches", default="1,8,64,256")
+    ap.add_argument("--ctx", type=int, default=1024)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--no-lm-head", action="store_true")
+    ap.add_argument("--no-graph", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import neural_magic_vllm_b200 as pkg
+    ops = pkg.ops
+    hbm = 6545.6
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            hbm = float(json.load(f)["hbm_gbs"])
+    except Exception:
+        pass
+    for batch in [int(b) for b in args.batches.split(",")]:
+        dec = Decoder(ops, world, rank, batch, args.ctx, lm_head=not args.no_lm_head)
+        with torch.no_grad():
+            for _ in range(2):
+                dec.step()
+            torch.cuda.synchronize()
+            graph = None
+            if not args.no_graph:
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    dec.step()
+            run = graph.replay if graph is not None else dec.step
+            for _ in range(args.warmup):
+                run()
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            st, en = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            st.record()
+            for _ in range(args.steps):
+                run()
+            en.record()
+            torch.cuda.synchronize()
+            ms = st.elapsed_time(en) / args.steps
+        t = torch.tensor([ms], device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        if rank == 0:
+            lin = dec.linear_bytes()
+            kv = 2 * batch * (args.ctx + 1) * dec.layers[0].kvh * HEAD * 2 * LAYERS
+            head = dec.lm_head.numel() * 2 if dec.lm_head is not None else 0
+            byts = lin + kv + head
+            print(json.dumps({
+                "metric": "decode tokens/s/GPU Llama-3-8B W4A16 gptq_marlin g128",
+                "tp": world, "batch": batch, "ctx": args.ctx, "ms_per_step": ms,
+                "tokens_per_s": batch / ms * 1e3, "tokens_per_s_per_gpu": batch / ms * 1e3 / world,
+                "cuda_graph": graph is not None, "lm_head": dec.lm_head is not None,
+                "attention": "paged_attention_v1" if dec.use_v1 else "paged_attention_v2",
+                "hbm_bytes_per_step_per_gpu": byts, "linear_bytes_per_gpu": lin, "kv_bytes_per_gpu": kv,
+                "hbm_GBps": byts / ms / 1e6, "hbm_frac": byts / ms / 1e6 / hbm,
+                "excluded": "scheduler, sampler (greedy argmax on the local vocab shard only), tokenizer",
+                "data": "synthetic: random-init packed int4 weights, random KV"}), flush=True)
+        del dec, graph
+        torch.cuda.empty_cache()
+    # leave without tearing NCCL down: destroy_process_group() after graph-captured collectives
+    # hung at exit on the B200 box (every number above is already printed and flushed)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sys.stdout.flush()
+    os._exit(0)
+
+
+if __name__ == "__main__":
+    main()

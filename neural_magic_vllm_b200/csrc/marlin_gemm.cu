@@ -13,6 +13,8 @@
 //   warps 2..5  epilogue: tcgen05.ld -> fp16/bf16 -> C (or fp32 split-K partials)
 // Decode (small M) is weight streaming: BM = 16..64, split-K fills the 148 SMs; HBM traffic is
 // the packed bytes, read exactly once.
+#include <cstdlib>
+
 #include "marlin_dequant.cuh"
 #include "umma.cuh"
 
@@ -690,6 +692,7 @@ inline int pick_splits(int m, int n, int num_kb, int64_t ws_bytes) {
   const int target = per_sm * kNumSMs;
   if (tiles >= target || tiles == 0) return 1;
   int splits = target / tiles;
+  if (const char* e = getenv("B200_MARLIN_SPLITS")) splits = atoi(e);  // tuning hook (benchmarks only)
   if (splits > num_kb / 4) splits = num_kb / 4;
   const int64_t per = (int64_t)m * n * 4;
   if (ws_bytes >= 0 && per > 0 && splits > ws_bytes / per) splits = (int)(ws_bytes / per);
