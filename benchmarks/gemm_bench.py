@@ -100,6 +100,37 @@ def bench_marlin(ops, ms, iters, dtype=torch.float16):
     return out
 
 
+LLAMA2_7B = {"qkv": (4096, 12288), "o": (4096, 4096), "gate_up": (4096, 22016), "down": (11008, 4096)}
+
+
+def bench_marlin_24(ops, ms, iters):
+    """C5: Llama-2-7B 2:4 sparse + W4A16 g128 (random compressed stream: timing only)."""
+    hbm, tf = peaks()
+    for name, (k, n) in LLAMA2_7B.items():
+        if LAYERS and name not in LAYERS:
+            continue
+        w_bytes = k * n // 4 + k * n // 8 + (k // 128) * n * 2
+        copies = max(2, -(-2 * L2_BYTES // w_bytes))
+        g = torch.Generator(device="cuda").manual_seed(0)
+        qs = [torch.randint(-2**31, 2**31 - 1, (k // 32, n * 2), dtype=torch.int32, device="cuda", generator=g)
+              for _ in range(copies)]
+        mt = [torch.randint(-2**15, 2**15 - 1, (k // 32, n * 2), dtype=torch.int16, device="cuda", generator=g)
+              for _ in range(copies)]
+        ss = [(torch.rand(k // 128, n, device="cuda", generator=g) * 0.02 + 0.001).half() for _ in range(copies)]
+        ws = torch.zeros(n // 128 * 64, dtype=torch.int32, device="cuda")
+        for m in ms:
+            a = torch.randn(m, k, dtype=torch.half, device="cuda")
+            t = time_calls(lambda i: ops.gptq_marlin_24_gemm(a, qs[i], mt[i], ss[i], ws, 4, m, n, k), copies, iters)
+            byts = w_bytes + m * (k + n) * 2
+            fl = 2.0 * m * k * n  # dense-equivalent
+            r = {"op": "gptq_marlin_24_gemm", "layer": name, "m": m, "k": k, "n": n, "us": t * 1e6,
+                 "GBps": byts / t / 1e9, "hbm_frac": byts / t / 1e9 / hbm, "TFLOPs": fl / t / 1e12,
+                 "tensor_frac": fl / t / 1e12 / tf}
+            r["roofline_frac"] = max(r["hbm_frac"], r["tensor_frac"])
+            print(json.dumps(r), flush=True)
+        del qs, mt, ss
+
+
 def bench_scaled_mm(ops, ms, iters, shapes, tag, fp8=True):
     hbm, tf = peaks()
     out = []
@@ -134,7 +165,7 @@ def bench_scaled_mm(ops, ms, iters, shapes, tag, fp8=True):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--op", default="all", choices=["marlin", "scaled_mm", "all"])
+    ap.add_argument("--op", default="all", choices=["marlin", "marlin24", "scaled_mm", "all"])
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--ms", default="1,16,64,256,2048")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches (host overhead included)")
@@ -149,6 +180,8 @@ def main():
     torch.cuda.set_device(0)
     if args.op in ("marlin", "all"):
         bench_marlin(ops, ms, args.iters)
+    if args.op in ("marlin24", "all"):
+        bench_marlin_24(ops, [m for m in ms if m <= 128], args.iters)
     if args.op in ("scaled_mm", "all"):
         bench_scaled_mm(ops, ms, args.iters, LLAMA3_70B_TP8, "70B/TP8")
         bench_scaled_mm(ops, ms, args.iters, LLAMA3_70B_TP2, "70B/TP2")
