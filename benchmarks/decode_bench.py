@@ -2,9 +2,11 @@
 
 A minimal decoder (32 layers, hidden 4096, 32 q / 8 kv heads, D 128, inter 14336, vocab 128256) whose
 hot ops are this repo's kernels through the reference's op surface: gptq_marlin_gemm for the four
-linears, reshape_and_cache + paged_attention_v1/v2 over the block-table KV cache.  RMSNorm, RoPE,
-SiLU*mul, residual adds, the fp16 lm_head and greedy argmax are plain torch ops (SURVEY.md §8(f)
-lists their fusion as the next row).  Scheduler, sampler and tokenizer are excluded (stated).
+linears, reshape_and_cache + paged_attention_v1/v2 over the block-table KV cache, and (default,
+--glue fused) this repo's rms_norm / fused_add_rms_norm / rotary_embedding_and_cache / silu_and_mul
+kernels for everything in between; --glue torch keeps those as plain torch
+ops (the round-1a configuration) for an A/B.  The fp16 lm_head and greedy argmax are torch ops.
+Scheduler, sampler and tokenizer are excluded (stated).
 
 Tensor parallel: launched under torchrun, rank r owns q heads / kv heads / the
 column shards of qkv and gate_up and the row (K) shards of o and down; the two partial sums per
@@ -74,8 +76,9 @@ def rope(x, cos, sin):  # neox style, x [B, H, D]
 
 
 class Decoder:
-    def __init__(self, ops, tp, rank, batch, ctx, lm_head=True):
+    def __init__(self, ops, tp, rank, batch, ctx, lm_head=True, glue="fused"):
         self.ops, self.tp, self.batch, self.ctx = ops, tp, batch, ctx
+        self.step = self.step_fused if glue == "fused" else self.step_torch
         gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
         blocks_per_seq = (ctx + BLOCK) // BLOCK
         self.num_blocks = batch * blocks_per_seq
@@ -90,6 +93,11 @@ class Decoder:
         self.slots = last * BLOCK + ctx % BLOCK
         ang = (ctx * 500000.0 ** (-torch.arange(0, HEAD, 2, device="cuda").float() / HEAD))
         self.cos, self.sin = ang.cos().half(), ang.sin().half()
+        # reference layout of the rotary table: [max_position, rot_dim] = (cos | sin) per position
+        inv = 500000.0 ** (-torch.arange(0, HEAD, 2, device="cuda").float() / HEAD)
+        tab = torch.arange(ctx + 1, device="cuda").float()[:, None] * inv[None]
+        self.cos_sin_cache = torch.cat((tab.cos(), tab.sin()), -1).half()
+        self.positions = torch.full((batch,), ctx, dtype=torch.int64, device="cuda")
         self.tokens = torch.randint(0, 4096, (batch,), device="cuda", generator=gen)
         h = self.layers[0].h
         self.parts = (ctx + 1 + 511) // 512
@@ -98,7 +106,48 @@ class Decoder:
         self.es = torch.empty(batch, h, self.parts, dtype=torch.float32, device="cuda")
         self.ml = torch.empty_like(self.es)
 
-    def step(self):
+    def step_fused(self):
+        """Every op between the embedding gather and the lm_head is one of this repo's kernels."""
+        ops, tp = self.ops, self.tp
+        x = self.embed[self.tokens]
+        res = None
+        for L in self.layers:
+            if res is None:
+                res, hn = x, torch.empty_like(x)
+                ops.rms_norm(hn, x, L.ln1, 1e-5)
+            else:
+                ops.fused_add_rms_norm(x, res, L.ln1, 1e-5)
+                hn = x
+            qkv = L.qkv(hn)
+            q, k, v = qkv.split([L.h * HEAD, L.kvh * HEAD, L.kvh * HEAD], dim=-1)
+            ops.rotary_embedding_and_cache(self.positions, q, k, v, HEAD, self.cos_sin_cache, True, L.kc, L.vc,
+                                           self.slots, "auto", 1.0)
+            q = q.view(-1, L.h, HEAD)
+            out = torch.empty(self.batch, L.h, HEAD, dtype=torch.half, device="cuda")
+            if self.use_v1:
+                ops.paged_attention_v1(out, q, L.kc, L.vc, L.kvh, HEAD ** -0.5, self.block_tables, self.seq_lens,
+                                       BLOCK, self.ctx + 1, None, "auto", 1.0)
+            else:
+                ops.paged_attention_v2(out, self.es, self.ml, self.tmp, q, L.kc, L.vc, L.kvh, HEAD ** -0.5,
+                                       self.block_tables, self.seq_lens, BLOCK, self.ctx + 1, None, "auto", 1.0)
+            o = L.o(out.view(-1, L.h * HEAD))
+            if tp > 1:
+                dist.all_reduce(o)
+            ops.fused_add_rms_norm(o, res, L.ln2, 1e-5)
+            gu = L.gate_up(o)
+            act = torch.empty(self.batch, INTER // tp, dtype=torch.half, device="cuda")
+            ops.silu_and_mul(act, gu)
+            x = L.down(act)
+            if tp > 1:
+                dist.all_reduce(x)
+        ops.fused_add_rms_norm(x, res, self.norm, 1e-5)
+        hn = x
+        if self.lm_head is not None:
+            logits = hn @ self.lm_head.t()
+            self.tokens.copy_(logits.argmax(-1) % 4096)  # greedy on the local vocab shard (no gather: stated)
+        return hn
+
+    def step_torch(self):
         ops, tp = self.ops, self.tp
         x = self.embed[self.tokens]
         res = x
@@ -146,6 +195,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--no-lm-head", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--glue", choices=["fused", "torch"], default="fused")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -162,7 +212,7 @@ def main():
     except Exception:
         pass
     for batch in [int(b) for b in args.batches.split(",")]:
-        dec = Decoder(ops, world, rank, batch, args.ctx, lm_head=not args.no_lm_head)
+        dec = Decoder(ops, world, rank, batch, args.ctx, lm_head=not args.no_lm_head, glue=args.glue)
         with torch.no_grad():
             for _ in range(2):
                 dec.step()
@@ -199,7 +249,7 @@ def main():
                 "tp": world, "batch": batch, "ctx": args.ctx, "ms_per_step": ms,
                 "tokens_per_s": batch / ms * 1e3, "tokens_per_s_per_gpu": batch / ms * 1e3 / world,
                 "cuda_graph": graph is not None, "lm_head": dec.lm_head is not None,
-                "attention": "paged_attention_v1" if dec.use_v1 else "paged_attention_v2",
+                "attention": "paged_attention_v1" if dec.use_v1 else "paged_attention_v2", "glue": args.glue,
                 "hbm_bytes_per_step_per_gpu": byts, "linear_bytes_per_gpu": lin, "kv_bytes_per_gpu": kv,
                 "hbm_GBps": byts / ms / 1e6, "hbm_frac": byts / ms / 1e6 / hbm,
                 "excluded": "scheduler, sampler (greedy argmax on the local vocab shard only), tokenizer",

@@ -250,6 +250,76 @@ typedef struct {
 
 B200_API int b200_gptq_marlin_24_gemm(const b200_gptq_marlin_24_gemm_params* p, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Decode-side glue between the linears and attention.
+ * Rounding follows the reference kernels operator by operator (each scalar_t operator is an
+ * fp32 operation rounded to the element type).
+ * ------------------------------------------------------------------------------------------ */
+
+/* rms_norm (csrc/layernorm_kernels.cu:21-45, 291-310): out = T(x * rsqrt(mean(x^2) + eps)) * weight.
+ * input / out [num_tokens, hidden] contiguous, weight [hidden]. */
+B200_API int b200_rms_norm(void* out, const void* input, const void* weight, float epsilon,
+                           int32_t num_tokens, int32_t hidden, int32_t dtype, void* stream);
+
+/* fused_add_rms_norm (csrc/layernorm_kernels.cu:199-287, 326-352), in place:
+ * residual = input + residual; input = rms_norm(residual) * weight. */
+B200_API int b200_fused_add_rms_norm(void* input, void* residual, const void* weight, float epsilon,
+                                     int32_t num_tokens, int32_t hidden, int32_t dtype, void* stream);
+
+/* rotary_embedding / batched_rotary_embedding (csrc/pos_encoding_kernels.cu:127-203), in place.
+ * query [num_tokens, num_heads*head_size] with row stride query_stride (elements), key likewise;
+ * cos_sin_cache [max_position, rot_dim] = (cos[rot_dim/2], sin[rot_dim/2]) per position;
+ * cos_sin_cache_offsets: NULL (rotary_embedding) or [num_tokens] int64 added to the position
+ * (batched_rotary_embedding). is_neox: rotate halves (NeoX) or interleaved pairs (GPT-J). */
+B200_API int b200_rotary_embedding(const int64_t* positions, void* query, void* key,
+                                   const void* cos_sin_cache, const int64_t* cos_sin_cache_offsets,
+                                   int32_t num_tokens, int32_t rot_dim, int64_t query_stride,
+                                   int64_t key_stride, int32_t num_heads, int32_t num_kv_heads,
+                                   int32_t head_size, int32_t is_neox, int32_t dtype, void* stream);
+
+/* activation ids of b200_act_and_mul / b200_activation */
+typedef enum {
+  B200_ACT_SILU = 0,      /* silu_and_mul        activation_kernels.cu:26-30  */
+  B200_ACT_GELU = 1,      /* gelu_and_mul        :32-40  (erf)                */
+  B200_ACT_GELU_TANH = 2, /* gelu_tanh_and_mul   :42-53                       */
+  B200_ACT_GELU_NEW = 3,  /* gelu_new            :118-123                     */
+  B200_ACT_GELU_FAST = 4, /* gelu_fast           :125-131                     */
+  B200_ACT_GELU_QUICK = 5 /* gelu_quick          :133-137                     */
+} b200_activation_id;
+
+/* {silu,gelu,gelu_tanh}_and_mul (activation_kernels.cu:12-24, 57-89):
+ * input [num_tokens, 2*d] contiguous, out [num_tokens, d] = act(input[:, :d]) * input[:, d:]. */
+B200_API int b200_act_and_mul(void* out, const void* input, int32_t num_tokens, int32_t d, int32_t act,
+                              int32_t dtype, void* stream);
+/* gelu_new / gelu_fast / gelu_quick (activation_kernels.cu:94-157): element-wise, [num_tokens, d]. */
+B200_API int b200_activation(void* out, const void* input, int32_t num_tokens, int32_t d, int32_t act,
+                             int32_t dtype, void* stream);
+
+/* B200 extension (no reference op): rotary_embedding followed by reshape_and_cache
+ * (csrc/pos_encoding_kernels.cu:127-160 + csrc/cache_kernels.cu:152-203, 253-278) in one launch --
+ * the pair the reference issues back to back on every decode step
+ * (model_executor/layers/rotary_embedding.py:forward_cuda, attention/backends/*:forward).
+ * Results are identical to calling the two ops in sequence.  Returns B200_ENOTSUP when rows are
+ * not 16-byte aligned or x != 16/sizeof(cache element); callers then issue the two ops. */
+typedef struct {
+  const int64_t* positions; /* [num_tokens] */
+  void* query;              /* rotated in place */
+  void* key;                /* rotated in place, then cached */
+  const void* value;
+  const void* cos_sin_cache;
+  void* key_cache;   /* [num_blocks, num_kv_heads, head_size/x, block_size, x] */
+  void* value_cache; /* [num_blocks, num_kv_heads, head_size, block_size] */
+  const int64_t* slot_mapping; /* [num_tokens]; < 0: token is rotated but not cached */
+  int32_t num_tokens, num_heads, num_kv_heads, head_size, rot_dim, block_size, x;
+  int64_t query_stride, key_stride, value_stride;
+  float kv_scale;
+  int32_t is_neox;
+  int32_t dtype;    /* b200_dtype of query/key/value */
+  int32_t kv_dtype; /* b200_kv_dtype of the caches */
+} b200_rotary_cache_params;
+
+B200_API int b200_rotary_embedding_and_cache(const b200_rotary_cache_params* p, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

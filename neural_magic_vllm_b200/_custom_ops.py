@@ -23,6 +23,66 @@ def is_custom_op_supported(op_name: str) -> bool:  # :24-26
     return hasattr(getattr(torch.ops, ns), name)
 
 
+# ------------------------------------------------------------------ activation ops (:49-70)
+def silu_and_mul(out: torch.Tensor, x: torch.Tensor) -> None:
+    _C.silu_and_mul(out, x)
+
+
+def gelu_and_mul(out: torch.Tensor, x: torch.Tensor) -> None:
+    _C.gelu_and_mul(out, x)
+
+
+def gelu_tanh_and_mul(out: torch.Tensor, x: torch.Tensor) -> None:
+    _C.gelu_tanh_and_mul(out, x)
+
+
+def gelu_fast(out: torch.Tensor, x: torch.Tensor) -> None:
+    _C.gelu_fast(out, x)
+
+
+def gelu_new(out: torch.Tensor, x: torch.Tensor) -> None:
+    _C.gelu_new(out, x)
+
+
+def gelu_quick(out: torch.Tensor, x: torch.Tensor) -> None:
+    _C.gelu_quick(out, x)
+
+
+# ------------------------------------------------------------------ pos encoding ops (:133-152)
+def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
+                     head_size: int, cos_sin_cache: torch.Tensor, is_neox: bool) -> None:
+    _C.rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox)
+
+
+def batched_rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
+                             head_size: int, cos_sin_cache: torch.Tensor, is_neox: bool,
+                             rot_dim: int, cos_sin_cache_offsets: torch.Tensor) -> None:
+    _C.batched_rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox, rot_dim,
+                                cos_sin_cache_offsets)
+
+
+def rotary_embedding_and_cache(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
+                               value: torch.Tensor, head_size: int, cos_sin_cache: torch.Tensor,
+                               is_neox: bool, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                               slot_mapping: torch.Tensor, kv_cache_dtype: str,
+                               kv_scale: float) -> None:
+    """B200 extension (no reference wrapper): ``rotary_embedding`` followed by
+    ``reshape_and_cache`` in one launch; results identical to the two reference ops in sequence."""
+    _C.rotary_embedding_and_cache(positions, query, key, value, head_size, cos_sin_cache, is_neox,
+                                  key_cache, value_cache, slot_mapping, kv_cache_dtype, kv_scale)
+
+
+# ------------------------------------------------------------------ layer norm ops (:155-163)
+def rms_norm(out: torch.Tensor, input: torch.Tensor, weight: torch.Tensor,
+             epsilon: float) -> None:
+    _C.rms_norm(out, input, weight, epsilon)
+
+
+def fused_add_rms_norm(input: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor,
+                       epsilon: float) -> None:
+    _C.fused_add_rms_norm(input, residual, weight, epsilon)
+
+
 # ------------------------------------------------------------------ attention (:74-129)
 def paged_attention_v1(out, query, key_cache, value_cache, num_kv_heads: int, scale: float,
                        block_tables, seq_lens, block_size: int, max_seq_len: int,

@@ -342,6 +342,7 @@ int64_t get_max_shared_memory_per_block_device_attribute(int64_t device_id) {
 }  // namespace
 
 #include "torch_bindings_quant.inc"
+#include "torch_bindings_glue.inc"
 
 B200_TORCH_LIBRARY(B200_TORCH_NS, ops) {
   ops.def(
@@ -368,6 +369,7 @@ B200_TORCH_LIBRARY(B200_TORCH_NS, ops) {
       "    int blocksparse_head_sliding_step) -> ()");
   ops.impl("paged_attention_v2", c10::DispatchKey::CUDA, &paged_attention_v2);
   b200_register_quant_ops(ops);
+  b200_register_glue_ops(ops);
 }
 
 B200_TORCH_LIBRARY(B200_CAT(B200_TORCH_NS, _cache_ops), cache_ops) {

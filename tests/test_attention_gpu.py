@@ -197,3 +197,53 @@ def test_cuda_graph_capture(ops):
         g.replay()
         s.synchronize()
     torch.testing.assert_close(out.cpu().float(), ref.float(), atol=1e-3, rtol=1e-2)
+
+
+# ------------------------------------------------------------------------------------------
+# BASELINE.json configs[0] (C1): opt-125m on the reference CPU backend -- 12 heads, D 64, fp32,
+# batch 8, block 16, context growing 128 -> 256.  Op-level replay of decode steps, GPU ops against
+# the reference's OWN compiled CPU kernels (oracle/_ref), not just the restatement.
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", ["float", "bf16"])
+def test_c1_opt125m_decode_replay_vs_reference_cpu(ops, dtype):
+    from oracle import ref_cpu
+    if not ref_cpu.available():
+        pytest.skip(f"compiled reference CPU kernels unavailable: {ref_cpu.why_unavailable()}")
+    dt = DTYPES[dtype]
+    heads, d, batch, bs = 12, 64, 8, 16
+    x = 16 // torch.tensor([], dtype=dt).element_size()
+    nb = batch * (256 // bs)
+    g = torch.Generator().manual_seed(0)
+    kc = torch.zeros(nb, heads, d // x, bs, x, dtype=dt)
+    vc = torch.zeros(nb, heads, d, bs, dtype=dt)
+    bt = torch.randperm(nb, generator=g).to(torch.int32).view(batch, 256 // bs)
+    # prefill 128 tokens of context through the CPU reference's cache writer
+    ctx = 128
+    k0 = (torch.rand(batch * ctx, heads, d, generator=g) - 0.5).to(dt)
+    v0 = (torch.rand(batch * ctx, heads, d, generator=g) - 0.5).to(dt)
+    pos = torch.arange(ctx).repeat(batch)
+    seq = torch.arange(batch).repeat_interleave(ctx)
+    slots0 = bt[seq, pos // bs].to(torch.int64) * bs + pos % bs
+    ref_cpu.reshape_and_cache(k0, v0, kc, vc, slots0)
+    kcd, vcd = kc.cuda(), vc.cuda()
+    ops.reshape_and_cache(k0.cuda(), v0.cuda(), torch.zeros_like(kcd), torch.zeros_like(vcd), slots0.cuda(),
+                          "auto", 1.0)  # exercised below on the live caches
+    kcd.zero_(), vcd.zero_()
+    ops.reshape_and_cache(k0.cuda(), v0.cuda(), kcd, vcd, slots0.cuda(), "auto", 1.0)
+    assert torch.equal(kcd.cpu(), kc) and torch.equal(vcd.cpu(), vc)  # cache bytes identical
+    for step in (0, 1, 63, 127):  # decode steps: ctx 128+step, write then attend
+        n = ctx + step
+        q = (torch.rand(batch, heads, d, generator=g) - 0.5).to(dt)
+        k1 = (torch.rand(batch, heads, d, generator=g) - 0.5).to(dt)
+        v1 = (torch.rand(batch, heads, d, generator=g) - 0.5).to(dt)
+        slots = bt[:, n // bs].to(torch.int64) * bs + n % bs
+        ref_cpu.reshape_and_cache(k1, v1, kc, vc, slots)
+        ops.reshape_and_cache(k1.cuda(), v1.cuda(), kcd, vcd, slots.cuda(), "auto", 1.0)
+        sl = torch.full((batch,), n + 1, dtype=torch.int32)
+        ref = torch.empty_like(q)
+        ref_cpu.paged_attention_v1(ref, q, kc, vc, heads, d ** -0.5, bt, sl, bs, n + 1)
+        out = torch.empty_like(q, device="cuda")
+        ops.paged_attention_v1(out, q.cuda(), kcd, vcd, heads, d ** -0.5, bt.cuda(), sl.cuda(), bs, n + 1,
+                               None, "auto", 1.0)
+        torch.testing.assert_close(out.cpu().float(), ref.float(), atol=1e-3, rtol=1e-2)
+    assert torch.equal(kcd.cpu(), kc) and torch.equal(vcd.cpu(), vc)
