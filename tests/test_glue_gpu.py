@@ -5,7 +5,7 @@ test_activation.py and test_cache.py of the reference.
 
 Tolerances: rotary is bit-exact in fp16/bf16 (same rounding sequence, no transcendental);
 RMSNorm / activations differ only through the fp32 summation order / libm ulps, so they must be
-within 1 ulp of the element type with >= 99 % of elements identical; against the reference CPU
+within 2 ulp of the element type with >= 99 % of elements identical; against the reference CPU
 kernels the north_star bound rtol 1e-2 / atol 1e-3 (bf16: 2e-2, its own ulp) applies."""
 import pytest
 import torch
@@ -21,7 +21,9 @@ ULP = {torch.half: 2.0 ** -10, torch.bfloat16: 2.0 ** -7, torch.float: 2.0 ** -2
 
 def _near(out, ref, dtype, exact_frac=0.99):
     out, ref = out.cpu(), ref.cpu()
-    torch.testing.assert_close(out.float(), ref.float(), rtol=ULP[dtype], atol=1e-6)
+    # a 1-ulp (fp32) difference in rstd / libm can flip T(x * rstd) by one T-ulp, and the product
+    # with the weight re-rounds: <= 2 ulp of T, on a handful of elements
+    torch.testing.assert_close(out.float(), ref.float(), rtol=2 * ULP[dtype], atol=1e-6)
     if dtype is not torch.float and out.numel():
         assert (out == ref).float().mean().item() >= exact_frac
 
