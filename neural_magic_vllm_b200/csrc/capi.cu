@@ -1,6 +1,7 @@
 // C-ABI plumbing of libb200vllm: error reporting, enum parsing, device attribute queries.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -25,6 +26,12 @@ int check_launch(const char* what) {
     return B200_ECUDA;
   }
   return B200_OK;
+}
+
+// read per launch (a getenv is noise next to a launch) so that a test can flip it in-process
+bool pdl_enabled() {
+  const char* e = getenv("B200_PDL");
+  return !(e != nullptr && e[0] == '0');
 }
 
 }  // namespace b200

@@ -45,6 +45,34 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------------
+// Decode is a chain of ~10 short kernels per layer inside one CUDA graph.  Kernels launched through
+// launch_pdl() may become resident while their predecessor in the stream is still running; they
+// must execute pdl_wait() before touching anything the predecessor writes (it returns once the
+// predecessor grid has completed and its memory is visible; a no-op for a normal launch).
+// pdl_launch_dependents() lets the NEXT kernel in the stream become resident early.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+bool pdl_enabled();  // capi.cu: env B200_PDL=0 turns the launch attribute off (A/B benchmarking)
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // ---- mbarrier + 1-D bulk async copy (TMA engine, SASS UBLKCP) -------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

@@ -79,6 +79,8 @@ __global__ void __launch_bounds__(1024) rms_norm_kernel(T* out, const T* in,
                                                         const int hidden) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ float red[32];
+  pdl_wait();
+  pdl_launch_dependents();
   T* row = reinterpret_cast<T*>(smem_raw);
   const int64_t base = (int64_t)blockIdx.x * hidden;
   float ss = 0.f;
@@ -140,13 +142,13 @@ int launch_rms(void* out, const void* in, void* residual, const void* weight, fl
   if (vec) {
     int threads = ((hidden / N + 31) / 32) * 32;
     threads = threads > 1024 ? 1024 : threads;
-    rms_norm_kernel<T, FUSED, true><<<tokens, threads, row_bytes, st>>>(
-        (T*)out, (const T*)in, (T*)residual, (const T*)weight, eps, hidden);
+    launch_pdl(rms_norm_kernel<T, FUSED, true>, dim3(tokens), dim3(threads), row_bytes, st, (T*)out,
+               (const T*)in, (T*)residual, (const T*)weight, eps, hidden);
   } else {
     int threads = ((hidden + 31) / 32) * 32;
     threads = threads > 1024 ? 1024 : threads;
-    rms_norm_kernel<T, FUSED, false><<<tokens, threads, 0, st>>>(
-        (T*)out, (const T*)in, (T*)residual, (const T*)weight, eps, hidden);
+    launch_pdl(rms_norm_kernel<T, FUSED, false>, dim3(tokens), dim3(threads), 0, st, (T*)out,
+               (const T*)in, (T*)residual, (const T*)weight, eps, hidden);
   }
   return check_launch(FUSED ? "fused_add_rms_norm" : "rms_norm");
 }
@@ -235,6 +237,8 @@ __global__ void __launch_bounds__(512) rotary_kernel(const int64_t* __restrict__
                                                      const int64_t k_stride, const int num_heads,
                                                      const int num_kv_heads, const int head_size) {
   const int64_t t = blockIdx.x;
+  pdl_wait();
+  pdl_launch_dependents();
   int64_t pos = positions[t];
   if (offsets != nullptr) pos += offsets[t];  // batched_rotary_embedding (:98-125)
   rotary_token<T, NEOX, VEC>(query + t * q_stride, key + t * k_stride, cos_sin_cache + pos * rot_dim,
@@ -254,6 +258,8 @@ __global__ void __launch_bounds__(512)
                         const int block_size, const float kv_scale) {
   constexpr int X = 16 / (int)sizeof(CacheT);
   const int64_t t = blockIdx.x;
+  pdl_wait();
+  pdl_launch_dependents();
   T* kt = key + t * k_stride;
   rotary_token<T, NEOX, true>(query + t * q_stride, kt, cos_sin_cache + positions[t] * rot_dim,
                               rot_dim, num_heads, num_kv_heads, head_size);
@@ -326,9 +332,9 @@ int launch_rotary(const RotArgs& a, cudaStream_t st) {
   int threads = ((items + 31) / 32) * 32;
   threads = threads > 512 ? 512 : (threads < 32 ? 32 : threads);
 #define ROT_LAUNCH(NEOX, VEC)                                                                    \
-  rotary_kernel<T, NEOX, VEC><<<a.tokens, threads, 0, st>>>(                                     \
-      a.positions, (T*)a.query, (T*)a.key, (const T*)a.cache, a.offsets, a.rot_dim, a.q_stride, \
-      a.k_stride, a.num_heads, a.num_kv_heads, a.head_size)
+  launch_pdl(rotary_kernel<T, NEOX, VEC>, dim3(a.tokens), dim3(threads), 0, st, a.positions,      \
+             (T*)a.query, (T*)a.key, (const T*)a.cache, a.offsets, a.rot_dim, a.q_stride,        \
+             a.k_stride, a.num_heads, a.num_kv_heads, a.head_size)
   if (a.neox) {
     if (vec) ROT_LAUNCH(true, true); else ROT_LAUNCH(true, false);
   } else {
@@ -372,6 +378,8 @@ template <typename T, int ACT, bool GATED, bool VEC>
 __global__ void __launch_bounds__(256) act_kernel(T* __restrict__ out, const T* __restrict__ in,
                                                   const int d) {
   const int64_t t = blockIdx.x;
+  pdl_wait();
+  pdl_launch_dependents();
   const T* x = in + t * (GATED ? 2 : 1) * (int64_t)d;
   const T* y = x + d;
   T* o = out + t * (int64_t)d;
@@ -409,9 +417,9 @@ int launch_act(void* out, const void* in, int tokens, int d, cudaStream_t st) {
   chunks = chunks > cap ? cap : chunks;
   dim3 grid(tokens, chunks < 1 ? 1 : chunks);
   if (vec)
-    act_kernel<T, ACT, GATED, true><<<grid, 256, 0, st>>>((T*)out, (const T*)in, d);
+    launch_pdl(act_kernel<T, ACT, GATED, true>, grid, dim3(256), 0, st, (T*)out, (const T*)in, d);
   else
-    act_kernel<T, ACT, GATED, false><<<grid, 256, 0, st>>>((T*)out, (const T*)in, d);
+    launch_pdl(act_kernel<T, ACT, GATED, false>, grid, dim3(256), 0, st, (T*)out, (const T*)in, d);
   return check_launch(GATED ? "act_and_mul" : "activation");
 }
 
@@ -431,9 +439,9 @@ int dispatch_act(void* out, const void* in, int tokens, int d, int act, cudaStre
 
 template <bool GATED>
 int act_entry(void* out, const void* in, int tokens, int d, int act, int dtype, void* stream) {
-  B200_REQUIRE(out && in, B200_EINVAL, "activation: null pointer");
   B200_REQUIRE(tokens >= 0 && d >= 0, B200_EINVAL, "activation: negative size");
   if (tokens == 0 || d == 0) return B200_OK;
+  B200_REQUIRE(out && in, B200_EINVAL, "activation: null pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (dtype) {
     case B200_F16: return dispatch_act<__half, GATED>(out, in, tokens, d, act, st);
@@ -455,11 +463,11 @@ int launch_rotary_cache(const b200_rotary_cache_params* p, cudaStream_t st) {
   int threads = ((items + 31) / 32) * 32;
   threads = threads > 512 ? 512 : (threads < 32 ? 32 : threads);
 #define RC_LAUNCH(NEOX)                                                                           \
-  rotary_cache_kernel<T, CacheT, KV, NEOX><<<p->num_tokens, threads, 0, st>>>(                    \
-      p->positions, (T*)p->query, (T*)p->key, (const T*)p->value, (const T*)p->cos_sin_cache,    \
-      p->rot_dim, p->query_stride, p->key_stride, p->value_stride, p->num_heads, p->num_kv_heads, \
-      p->head_size, (CacheT*)p->key_cache, (CacheT*)p->value_cache, p->slot_mapping,             \
-      p->block_size, p->kv_scale)
+  launch_pdl(rotary_cache_kernel<T, CacheT, KV, NEOX>, dim3(p->num_tokens), dim3(threads), 0, st,  \
+             p->positions, (T*)p->query, (T*)p->key, (const T*)p->value,                         \
+             (const T*)p->cos_sin_cache, p->rot_dim, p->query_stride, p->key_stride,             \
+             p->value_stride, p->num_heads, p->num_kv_heads, p->head_size, (CacheT*)p->key_cache, \
+             (CacheT*)p->value_cache, p->slot_mapping, p->block_size, p->kv_scale)
   if (p->is_neox) RC_LAUNCH(true); else RC_LAUNCH(false);
 #undef RC_LAUNCH
   return check_launch("rotary_embedding_and_cache");
@@ -494,9 +502,9 @@ extern "C" {
 int b200_rms_norm(void* out, const void* input, const void* weight, float epsilon,
                   int32_t num_tokens, int32_t hidden, int32_t dtype, void* stream) {
   using namespace b200;
-  B200_REQUIRE(out && input && weight, B200_EINVAL, "rms_norm: null pointer");
   B200_REQUIRE(num_tokens >= 0 && hidden >= 0, B200_EINVAL, "rms_norm: negative size");
-  if (num_tokens == 0 || hidden == 0) return B200_OK;
+  if (num_tokens == 0 || hidden == 0) return B200_OK;  // empty batch: pointers may be null
+  B200_REQUIRE(out && input && weight, B200_EINVAL, "rms_norm: null pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (dtype) {
     case B200_F16: return launch_rms<__half, false>(out, input, nullptr, weight, epsilon, num_tokens, hidden, st);
@@ -510,9 +518,9 @@ int b200_rms_norm(void* out, const void* input, const void* weight, float epsilo
 int b200_fused_add_rms_norm(void* input, void* residual, const void* weight, float epsilon,
                             int32_t num_tokens, int32_t hidden, int32_t dtype, void* stream) {
   using namespace b200;
-  B200_REQUIRE(input && residual && weight, B200_EINVAL, "fused_add_rms_norm: null pointer");
   B200_REQUIRE(num_tokens >= 0 && hidden >= 0, B200_EINVAL, "fused_add_rms_norm: negative size");
   if (num_tokens == 0 || hidden == 0) return B200_OK;
+  B200_REQUIRE(input && residual && weight, B200_EINVAL, "fused_add_rms_norm: null pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (dtype) {
     case B200_F16: return launch_rms<__half, true>(input, input, residual, weight, epsilon, num_tokens, hidden, st);
@@ -529,12 +537,12 @@ int b200_rotary_embedding(const int64_t* positions, void* query, void* key,
                           int64_t key_stride, int32_t num_heads, int32_t num_kv_heads,
                           int32_t head_size, int32_t is_neox, int32_t dtype, void* stream) {
   using namespace b200;
-  B200_REQUIRE(positions && query && key && cos_sin_cache, B200_EINVAL, "rotary_embedding: null pointer");
   B200_REQUIRE(num_tokens >= 0 && rot_dim >= 0 && rot_dim % 2 == 0 && rot_dim <= head_size &&
                    num_heads >= 0 && num_kv_heads >= 0 && head_size > 0,
                B200_EINVAL, "rotary_embedding: bad shape (tokens=%d rot_dim=%d heads=%d/%d head_size=%d)",
                num_tokens, rot_dim, num_heads, num_kv_heads, head_size);
   if (num_tokens == 0 || rot_dim == 0 || num_heads + num_kv_heads == 0) return B200_OK;
+  B200_REQUIRE(positions && query && key && cos_sin_cache, B200_EINVAL, "rotary_embedding: null pointer");
   RotArgs a{positions, query, key, cos_sin_cache, cos_sin_cache_offsets, num_tokens, rot_dim,
             num_heads, num_kv_heads, head_size, query_stride, key_stride, is_neox != 0};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -550,14 +558,14 @@ int b200_rotary_embedding(const int64_t* positions, void* query, void* key,
 int b200_rotary_embedding_and_cache(const b200_rotary_cache_params* p, void* stream) {
   using namespace b200;
   B200_REQUIRE(p != nullptr, B200_EINVAL, "rotary_embedding_and_cache: null params");
-  B200_REQUIRE(p->positions && p->query && p->key && p->value && p->cos_sin_cache && p->key_cache &&
-                   p->value_cache && p->slot_mapping,
-               B200_EINVAL, "rotary_embedding_and_cache: null pointer");
   B200_REQUIRE(p->num_tokens >= 0 && p->rot_dim > 0 && p->rot_dim % 2 == 0 &&
                    p->rot_dim <= p->head_size && p->num_heads > 0 && p->num_kv_heads > 0 &&
                    p->head_size > 0 && p->block_size > 0,
                B200_EINVAL, "rotary_embedding_and_cache: bad shape");
   if (p->num_tokens == 0) return B200_OK;
+  B200_REQUIRE(p->positions && p->query && p->key && p->value && p->cos_sin_cache && p->key_cache &&
+                   p->value_cache && p->slot_mapping,
+               B200_EINVAL, "rotary_embedding_and_cache: null pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (p->dtype) {
     case B200_F16: return rotary_cache_dtype<__half>(p, st);

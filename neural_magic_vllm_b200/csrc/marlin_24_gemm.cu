@@ -144,9 +144,30 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
     const uint64_t pol_w = l2_policy_evict_first();
     const uint64_t pol_x = l2_policy_evict_last();
     const uint32_t tx_bytes = P::kXBytes + kValBytes + kMetaBytes + (grouped ? kTileN * 2 : 0);
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int kb = kb_begin; kb < kb_end; ++kb) {
+    // programmatic dependent launch: values / metadata / scales of the first ring of stages
+    // stream in before the wait; only the activation tiles depend on the predecessor
+    const int pre = min(kb_end - kb_begin, kStages);
+    if (lane == 0) {
+      for (int i = 0; i < pre; ++i) {
+        const int kb = kb_begin + i;
+        uint8_t* w_dst = stages + i * P::kStageBytes + P::kXBytes;
+        mbar_arrive_expect_tx(&full_p[i], tx_bytes);
+        tma_load_2d(w_dst, &tm_w, n0 * 2, kb * 2, &full_p[i], pol_w);
+        tma_load_2d(w_dst + kValBytes, &tm_m, n0 * 2, kb * 2, &full_p[i], pol_w);
+        if (grouped)
+          tma_load_2d(w_dst + kValBytes + kMetaBytes, &tm_s, n0, (kb * kStageK) >> args.group_shift,
+                      &full_p[i], pol_x);
+      }
+    }
+    pdl_wait();
+    if (lane == 0) {
+      for (int i = 0; i < pre; ++i)
+        tma_load_2d(stages + i * P::kStageBytes, &tm_x, (kb_begin + i) * kStageK, m0, &full_p[i], pol_x);
+    }
+    __syncwarp();
+    int stage = pre == kStages ? 0 : pre;
+    uint32_t phase = pre == kStages ? 1 : 0;
+    for (int kb = kb_begin + pre; kb < kb_end; ++kb) {
       mbar_wait_bounded(&empty_p[stage], phase ^ 1);
       if (lane == 0) {
         uint8_t* x_dst = stages + stage * P::kStageBytes;
@@ -182,6 +203,7 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
         if (++as == kAStages) as = 0, aphase ^= 1;
       }
       mma_commit(tmem_full);
+      pdl_launch_dependents();  // main loop issued: the next kernel may become resident and wait
     }
   } else {
     const int qd = warp & 3;  // TMEM quadrant
@@ -358,7 +380,7 @@ int launch24(const b200_gptq_marlin_24_gemm_params& p, cudaStream_t st) {
   a.partial = splits > 1 ? reinterpret_cast<float*>(p.splitk_ws) : nullptr;
   auto kern = marlin24_gemm_kernel<BM>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P::kBytes);
-  kern<<<dim3(m_tiles, n_tiles, splits), kThreads, P::kBytes, st>>>(tm_x, tm_w, tm_m, tm_s, a);
+  launch_pdl(kern, dim3(m_tiles, n_tiles, splits), dim3(kThreads), P::kBytes, st, tm_x, tm_w, tm_m, tm_s, a);
   rc = check_launch("gptq_marlin_24_gemm");
   if (rc != B200_OK) return rc;
   if (splits > 1) {

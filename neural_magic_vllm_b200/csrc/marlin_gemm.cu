@@ -422,9 +422,31 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
     constexpr int kWordsPerN = 16 * BITS / 32;
     constexpr int kLoadsW = kTileN * kWordsPerN / 256;
     const uint32_t tx_bytes = P::kXBytes + P::kPackedBytes + (uint32_t)args.s_rows * (kTileN * 2);
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int kb = kb_begin; kb < kb_end; ++kb) {
+    // Programmatic dependent launch: this grid may be resident while its predecessor (the kernel
+    // that produces the activations) is still running.  Weights and scales do not depend on it, so
+    // the first ring of stages streams them in right away; only the activation tiles wait.
+    const int pre = min(kb_end - kb_begin, kStages);
+    if (lane == 0) {
+      for (int i = 0; i < pre; ++i) {  // fresh ring: every stage is empty
+        const int kb = kb_begin + i;
+        uint8_t* w_dst = stages + i * P::kStageBytes + P::kXBytes;
+        mbar_arrive_expect_tx(&full_p[i], tx_bytes);
+#pragma unroll
+        for (int l = 0; l < kLoadsW; ++l)
+          tma_load_2d(w_dst + l * 4096, &tm_w, n0 * kWordsPerN + l * 256, kb * 4, &full_p[i], pol_w);
+        if (args.s_rows > 0)
+          tma_load_2d(w_dst + P::kPackedBytes, &tm_s, n0, group_of(args, kb * kStageK), &full_p[i], pol_x);
+      }
+    }
+    pdl_wait();  // the predecessor grid has completed: activations are visible
+    if (lane == 0) {
+      for (int i = 0; i < pre; ++i)
+        tma_load_2d(stages + i * P::kStageBytes, &tm_x, (kb_begin + i) * kStageK, m0, &full_p[i], pol_x);
+    }
+    __syncwarp();
+    int stage = pre == kStages ? 0 : pre;
+    uint32_t phase = pre == kStages ? 1 : 0;
+    for (int kb = kb_begin + pre; kb < kb_end; ++kb) {
       mbar_wait_bounded(&empty_p[stage], phase ^ 1);
       if (lane == 0) {
         uint8_t* x_dst = stages + stage * P::kStageBytes;
@@ -461,6 +483,9 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
         if (++as == kAStages) as = 0, aphase ^= 1;
       }
       mma_commit(tmem_full);
+      // main loop issued: the next kernel in the stream may become resident (its prologue and, for
+      // a GEMM, its first weight stages overlap this grid's epilogue) and wait for our completion
+      pdl_launch_dependents();
     }
   } else {
     const int qd = warp & 3;          // TMEM quadrant = rows 32 qd .. 32 qd + 31
@@ -790,16 +815,24 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P::kBytes);
   // tiny M: the last split to arrive reduces in-kernel; otherwise a grid-wide reduce kernel
   a.locks = (splits > 1 && m_tiles == 1 && p.size_m <= 4) ? p.workspace : nullptr;
-  // (programmatic dependent launch was measured here and lost: early-resident dependents take
-  // TMEM/shared-memory slots from the running grid -- 29 -> 38 us on gate_up)
+  // Programmatic dependent launch: behind a short producer kernel (RMSNorm, SiLU*mul, the attention
+  // reduce) this grid's prologue and first ring of weight stages overlap the producer.  (Back to
+  // back behind ANOTHER GEMM it was measured to lose -- early-resident dependents take TMEM /
+  // shared-memory slots from the running grid, 29 -> 38 us on gate_up -- which the decode chain
+  // never does: the glue kernels in between release their dependents only after their own wait.)
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(m_tiles, n_tiles, splits);
   cfg.blockDim = dim3(kTThreads);
   cfg.dynamicSmemBytes = P::kBytes;
   cfg.stream = st;
+  cudaLaunchAttribute pdl_attr[1];
+  pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  pdl_attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = pdl_attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_x, tm_w, tm_s, a);
   cfg.attrs = nullptr;
   cfg.numAttrs = 0;
-  cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_x, tm_w, tm_s, a);
   if (le != cudaSuccess) {
     cudaGetLastError();
     set_error("gptq_marlin_gemm: launch failed: %s", cudaGetErrorString(le));

@@ -40,6 +40,7 @@ __global__ void __launch_bounds__(kReduceWarps * 32)
   constexpr int MAXP = 4;             // pairs per lane: head_size <= 256
 
   asm volatile("griddepcontrol.wait;" ::: "memory");  // results of the split-KV kernel are visible
+  pdl_launch_dependents();  // the kernel behind the reduce (o_proj GEMM) may take its slots now
 
   float gmax = -FLT_MAX;
   for (int p = lane; p < np; p += 32) gmax = fmaxf(gmax, ml[p]);
@@ -371,7 +372,7 @@ static int run_paged_attention(const b200_paged_attention_params* p, bool v2, cu
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
     cudaError_t le;
     if (p->dtype == B200_F16) {
       le = cudaLaunchKernelEx(&cfg, paged_attn_reduce_kernel<__half>, (__half*)p->out,

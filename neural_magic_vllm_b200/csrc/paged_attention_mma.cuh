@@ -92,6 +92,9 @@ __global__ void __launch_bounds__(kAttnThreads)
   const int BS = FAST ? 16 : a.block_size;
   const int D = FAST ? HMAX : a.head_size;
   const int nks = D >> 4;
+  // programmatic dependent launch: this grid may be resident before the kernel that wrote the
+  // query / the newest KV slot (rotary + cache write) has finished; every CTA waits for it here
+  pdl_wait();
   const int seq_len = a.sl[seq];
   const bool partitioned = a.partition_size > 0;
   const int tok_begin = partitioned ? part * a.partition_size : 0;
@@ -533,7 +536,7 @@ static int launch_one(const AttnArgs& a, dim3 grid, size_t smem, cudaStream_t st
     }
     configured = smem;
   }
-  kern<<<grid, kAttnThreads, smem, stream>>>(a);
+  launch_pdl(kern, grid, dim3(kAttnThreads), smem, stream, a);
   return check_launch("paged_attention");
 }
 

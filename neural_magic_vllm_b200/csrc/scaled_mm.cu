@@ -89,9 +89,20 @@ scaled_mm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
     if (lane == 0) {
       const uint64_t pol_w = args.w_evict_first ? l2_policy_evict_first() : l2_policy_evict_last();
       const uint64_t pol_x = l2_policy_evict_last();
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = kb_begin; kb < kb_end; ++kb) {
+      // programmatic dependent launch: weights do not depend on the predecessor (the activation
+      // quantiser), so the first ring of weight tiles streams in before the wait
+      const int pre = min(kb_end - kb_begin, kStages);
+      for (int i = 0; i < pre; ++i) {
+        mbar_arrive_expect_tx(&full_bar[i], S::kStageBytes);
+        tma_load_2d(tiles + i * S::kStageBytes, &tm_w, (kb_begin + i) * kStageKBytes, n0, &full_bar[i], pol_w);
+      }
+      pdl_wait();
+      for (int i = 0; i < pre; ++i)
+        tma_load_2d(tiles + i * S::kStageBytes + kTileN * kStageKBytes, &tm_x, (kb_begin + i) * kStageKBytes, m0,
+                    &full_bar[i], pol_x);
+      int stage = pre == kStages ? 0 : pre;
+      uint32_t phase = pre == kStages ? 1 : 0;
+      for (int kb = kb_begin + pre; kb < kb_end; ++kb) {
         mbar_wait_bounded(&empty_bar[stage], phase ^ 1);
         uint8_t* w_dst = tiles + stage * S::kStageBytes;
         uint8_t* x_dst = w_dst + kTileN * kStageKBytes;
@@ -120,9 +131,11 @@ scaled_mm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         if (++stage == kStages) stage = 0, phase ^= 1;
       }
       mma_commit(tmem_full);
+      pdl_launch_dependents();  // main loop issued: the next kernel may become resident and wait
     }
   } else {
     // ---- epilogue: warp w owns TMEM lanes [32 * (w % 4), +32) ----
+    pdl_wait();  // the per-token activation scales are the predecessor's output
     const int quarter = warp & 3;
     const int n = n0 + quarter * 32 + lane;
     const int et = threadIdx.x - 64;  // 0..127
@@ -246,7 +259,7 @@ int launch(const b200_scaled_mm_params& p, cudaStream_t st) {
     attr_set = true;
   }
   dim3 grid(m_tiles, n_tiles, splits);
-  kern<<<grid, kThreads, S::kBytes, st>>>(tm_w, tm_x, a);
+  launch_pdl(kern, grid, dim3(kThreads), S::kBytes, st, tm_w, tm_x, a);
   rc = check_launch("scaled_mm");
   if (rc != B200_OK) return rc;
   if (splits > 1) {
