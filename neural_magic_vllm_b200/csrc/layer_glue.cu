@@ -245,8 +245,17 @@ __global__ void __launch_bounds__(512) rotary_kernel(const int64_t* __restrict__
                              rot_dim, num_heads, num_kv_heads, head_size);
 }
 
-// B200 extension: rotary on q/k, then K/V of the same token go to their paged-cache slot
-// (cache_kernels.cu:152-203) without a second launch.  X = elements per 16-byte K-cache group.
+// B200 extension: rotary on q/k and the paged-cache write of the same token's K/V
+// (cache_kernels.cu:152-203) in one pass: the rotated K chunk goes from registers both back to `key`
+// and into its cache slot, so nothing is re-read.  A work item is 16 bytes of one head row:
+// q rotary | k rotary + cache | k tail beyond rot_dim -> cache | v -> cache.
+template <int BYTES>
+__device__ __forceinline__ void store_small(void* dst, const void* src) {
+  if constexpr (BYTES == 16) *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+  else if constexpr (BYTES == 8) *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<const uint2*>(src);
+  else *reinterpret_cast<uint32_t*>(dst) = *reinterpret_cast<const uint32_t*>(src);
+}
+
 template <typename T, typename CacheT, int KV, bool NEOX>
 __global__ void __launch_bounds__(512)
     rotary_cache_kernel(const int64_t* __restrict__ positions, T* __restrict__ query,
@@ -256,52 +265,104 @@ __global__ void __launch_bounds__(512)
                         const int num_kv_heads, const int head_size, CacheT* __restrict__ key_cache,
                         CacheT* __restrict__ value_cache, const int64_t* __restrict__ slot_mapping,
                         const int block_size, const float kv_scale) {
-  constexpr int X = 16 / (int)sizeof(CacheT);
+  constexpr int N = V16<T>::N;
+  constexpr int X = 16 / (int)sizeof(CacheT);  // elements per 16-byte K-cache group (X % N == 0)
   const int64_t t = blockIdx.x;
   pdl_wait();
   pdl_launch_dependents();
+  const int embed = rot_dim / 2;
+  const T* cosp = cos_sin_cache + positions[t] * rot_dim;
+  const T* sinp = cosp + embed;
+  T* qt = query + t * q_stride;
   T* kt = key + t * k_stride;
-  rotary_token<T, NEOX, true>(query + t * q_stride, kt, cos_sin_cache + positions[t] * rot_dim,
-                              rot_dim, num_heads, num_kv_heads, head_size);
-  const int64_t slot = slot_mapping[t];
-  if (slot < 0) return;  // padding token: rotated, not cached (cache_kernels.cu:166-169)
-  __syncthreads();       // the rotated key row (global, written by this CTA) is visible below
-  const int64_t block_idx = slot / block_size, block_off = slot % block_size;
-  const int groups = head_size / X;
   const T* vt = value + t * v_stride;
+  const int64_t slot = slot_mapping[t];
+  const bool cached = slot >= 0;  // padding token: rotated, not cached (cache_kernels.cu:166-169)
+  const int64_t block_idx = cached ? slot / block_size : 0;
+  const int64_t block_off = cached ? slot % block_size : 0;
   CacheT* kdst = key_cache + block_idx * (int64_t)num_kv_heads * head_size * block_size;
-  CacheT* vdst = value_cache + block_idx * (int64_t)num_kv_heads * head_size * block_size;
-  constexpr int SRC = (X * (int)sizeof(T)) / 16;
-  for (int g = threadIdx.x; g < num_kv_heads * groups; g += blockDim.x) {
-    const int head = g / groups, xg = g % groups;
-    union {
-      uint4 v[SRC];
-      T e[X];
-    } kin, vin;
-    const uint4* kp = reinterpret_cast<const uint4*>(kt + head * head_size + xg * X);
-    const uint4* vp = reinterpret_cast<const uint4*>(vt + head * head_size + xg * X);
+  CacheT* vdst = value_cache + block_idx * (int64_t)num_kv_heads * head_size * block_size + block_off;
+  const int groups = head_size / X;
+
+  auto put_k = [&](const V16<T>& v, int head, int d0) {
+    CacheT* kd = kdst + (((int64_t)head * groups + d0 / X) * block_size + block_off) * X + d0 % X;
+    if constexpr (KV == B200_KV_AUTO) {
+      store_small<16>(kd, &v.u);
+    } else {
+      __align__(8) uint8_t b[N];
 #pragma unroll
-    for (int i = 0; i < SRC; ++i) {
-      kin.v[i] = kp[i];  // plain (coherent) load: written above by this kernel
-      vin.v[i] = __ldg(vp + i);
+      for (int j = 0; j < N; ++j) b[j] = fp8_quant<T, KV>(v.e[j], kv_scale);
+      store_small<N>(kd, b);
     }
-    CacheT* kd = kdst + ((int64_t)head * groups + xg) * block_size * X + block_off * X;
-    CacheT* vd = vdst + ((int64_t)head * head_size + xg * X) * block_size + block_off;
-    union {
-      uint4 v;
-      CacheT e[X];
-    } kout;
+  };
+
+  const int rot_per_head = NEOX ? embed / N : embed / (N / 2);
+  const int tail_per_head = (head_size - rot_dim) / N;
+  const int v_per_head = head_size / N;
+  const int n_rot = (num_heads + num_kv_heads) * rot_per_head;
+  const int n_q = num_heads * rot_per_head;
+  const int n_tail = cached ? num_kv_heads * tail_per_head : 0;
+  const int n_v = cached ? num_kv_heads * v_per_head : 0;
+  for (int it = threadIdx.x; it < n_rot + n_tail + n_v; it += blockDim.x) {
+    if (it < n_rot) {
+      const bool is_k = it >= n_q;
+      const int i = is_k ? it - n_q : it;
+      const int h = i / rot_per_head, c = i % rot_per_head;
+      T* arr = (is_k ? kt : qt) + (int64_t)h * head_size;
+      if constexpr (NEOX) {
+        const int ro = c * N;
+        V16<T> x, y, cs, sn;
+        x.load(arr + ro);
+        y.load(arr + embed + ro);
+        cs.load(cosp + ro);
+        sn.load(sinp + ro);
 #pragma unroll
-    for (int j = 0; j < X; ++j) {
-      if constexpr (KV == B200_KV_AUTO) {
-        kout.e[j] = kin.e[j];
-        vd[(int64_t)j * block_size] = vin.e[j];
+        for (int j = 0; j < N; ++j) {
+          float xo, yo;
+          rot_pair<T>(x.f(j), y.f(j), cs.f(j), sn.f(j), xo, yo);
+          x.set(j, xo);
+          y.set(j, yo);
+        }
+        x.store(arr + ro);
+        y.store(arr + embed + ro);
+        if (is_k && cached) {
+          put_k(x, h, ro);
+          put_k(y, h, embed + ro);
+        }
       } else {
-        kout.e[j] = fp8_quant<T, KV>(kin.e[j], kv_scale);
-        vd[(int64_t)j * block_size] = fp8_quant<T, KV>(vin.e[j], kv_scale);
+        constexpr int P = N / 2;
+        const int ro = c * P;
+        V16<T> v;
+        v.load(arr + 2 * ro);
+#pragma unroll
+        for (int j = 0; j < P; ++j) {
+          float xo, yo;
+          rot_pair<T>(v.f(2 * j), v.f(2 * j + 1), DT<T>::to_f(cosp[ro + j]), DT<T>::to_f(sinp[ro + j]),
+                      xo, yo);
+          v.set(2 * j, xo);
+          v.set(2 * j + 1, yo);
+        }
+        v.store(arr + 2 * ro);
+        if (is_k && cached) put_k(v, h, 2 * ro);
+      }
+    } else if (it < n_rot + n_tail) {  // K beyond rot_dim: cached as is
+      const int i = it - n_rot;
+      const int h = i / tail_per_head, d0 = rot_dim + (i % tail_per_head) * N;
+      V16<T> v;
+      v.load(kt + (int64_t)h * head_size + d0);
+      put_k(v, h, d0);
+    } else {  // V: token-strided scatter, consecutive lanes -> consecutive 16-byte chunks of the row
+      const int i = it - n_rot - n_tail;
+      const int h = i / v_per_head, d0 = (i % v_per_head) * N;
+      V16<T> v;
+      v.u = __ldg(reinterpret_cast<const uint4*>(vt + (int64_t)h * head_size + d0));
+      CacheT* vd = vdst + ((int64_t)h * head_size + d0) * block_size;
+#pragma unroll
+      for (int j = 0; j < N; ++j) {
+        if constexpr (KV == B200_KV_AUTO) vd[(int64_t)j * block_size] = v.e[j];
+        else vd[(int64_t)j * block_size] = fp8_quant<T, KV>(v.e[j], kv_scale);
       }
     }
-    *reinterpret_cast<uint4*>(kd) = kout.v;
   }
 }
 
@@ -457,9 +518,8 @@ int launch_rotary_cache(const b200_rotary_cache_params* p, cudaStream_t st) {
   constexpr int N = V16<T>::N;
   constexpr int X = 16 / (int)sizeof(CacheT);
   const int embed = p->rot_dim / 2;
-  const int rot_items = (p->num_heads + p->num_kv_heads) * (p->is_neox ? embed / N : embed / (N / 2));
-  const int cache_items = p->num_kv_heads * (p->head_size / X);
-  int items = rot_items > cache_items ? rot_items : cache_items;
+  const int items = (p->num_heads + p->num_kv_heads) * (p->is_neox ? embed / N : embed / (N / 2)) +
+                    p->num_kv_heads * ((p->head_size - p->rot_dim) / N + p->head_size / N);
   int threads = ((items + 31) / 32) * 32;
   threads = threads > 512 ? 512 : (threads < 32 ? 32 : threads);
 #define RC_LAUNCH(NEOX)                                                                           \
