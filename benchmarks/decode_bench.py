@@ -76,8 +76,9 @@ def rope(x, cos, sin):  # neox style, x [B, H, D]
 
 
 class Decoder:
-    def __init__(self, ops, tp, rank, batch, ctx, lm_head=True, glue="fused"):
+    def __init__(self, ops, tp, rank, batch, ctx, lm_head=True, glue="fused", car=None):
         self.ops, self.tp, self.batch, self.ctx = ops, tp, batch, ctx
+        self.car = car  # one-shot NVLink all-reduce (None: NCCL)
         self.step = self.step_fused if glue == "fused" else self.step_torch
         gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
         blocks_per_seq = (ctx + BLOCK) // BLOCK
@@ -106,6 +107,16 @@ class Decoder:
         self.es = torch.empty(batch, h, self.parts, dtype=torch.float32, device="cuda")
         self.ml = torch.empty_like(self.es)
 
+    def all_reduce(self, t):
+        """Row-parallel partial sums (linear.py:792-793): one-shot NVLink kernel when the message
+        qualifies, NCCL otherwise -- the same split the reference makes (parallel_state.py)."""
+        if self.car is not None:
+            out = self.car.custom_all_reduce(t)
+            if out is not None:
+                return out
+        dist.all_reduce(t)
+        return t
+
     def step_fused(self):
         """Every op between the embedding gather and the lm_head is one of this repo's kernels."""
         ops, tp = self.ops, self.tp
@@ -132,14 +143,14 @@ class Decoder:
                                        self.block_tables, self.seq_lens, BLOCK, self.ctx + 1, None, "auto", 1.0)
             o = L.o(out.view(-1, L.h * HEAD))
             if tp > 1:
-                dist.all_reduce(o)
+                o = self.all_reduce(o)
             ops.fused_add_rms_norm(o, res, L.ln2, 1e-5)
             gu = L.gate_up(o)
             act = torch.empty(self.batch, INTER // tp, dtype=torch.half, device="cuda")
             ops.silu_and_mul(act, gu)
             x = L.down(act)
             if tp > 1:
-                dist.all_reduce(x)
+                x = self.all_reduce(x)
         ops.fused_add_rms_norm(x, res, self.norm, 1e-5)
         hn = x
         if self.lm_head is not None:
@@ -196,6 +207,8 @@ def main():
     ap.add_argument("--no-lm-head", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--glue", choices=["fused", "torch"], default="fused")
+    ap.add_argument("--ar", choices=["one_shot", "nccl"], default="one_shot",
+                    help="TP all-reduce: this repo's one-shot NVLink kernel (NCCL above its max_size) or NCCL only")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -211,8 +224,14 @@ def main():
             hbm = float(json.load(f)["hbm_gbs"])
     except Exception:
         pass
+    car = None
+    if world > 1 and args.ar == "one_shot":
+        from neural_magic_vllm_b200.custom_all_reduce import CustomAllreduce
+        car = CustomAllreduce(None, local)
+        if car.disabled:
+            car = None
     for batch in [int(b) for b in args.batches.split(",")]:
-        dec = Decoder(ops, world, rank, batch, args.ctx, lm_head=not args.no_lm_head, glue=args.glue)
+        dec = Decoder(ops, world, rank, batch, args.ctx, lm_head=not args.no_lm_head, glue=args.glue, car=car)
         with torch.no_grad():
             for _ in range(2):
                 dec.step()
@@ -250,6 +269,7 @@ def main():
                 "tokens_per_s": batch / ms * 1e3, "tokens_per_s_per_gpu": batch / ms * 1e3 / world,
                 "cuda_graph": graph is not None, "lm_head": dec.lm_head is not None,
                 "attention": "paged_attention_v1" if dec.use_v1 else "paged_attention_v2", "glue": args.glue,
+                "all_reduce": ("one_shot_nvlink" if car is not None else "nccl") if world > 1 else None,
                 "hbm_bytes_per_step_per_gpu": byts, "linear_bytes_per_gpu": lin, "kv_bytes_per_gpu": kv,
                 "hbm_GBps": byts / ms / 1e6, "hbm_frac": byts / ms / 1e6 / hbm,
                 "excluded": "scheduler, sampler (greedy argmax on the local vocab shard only), tokenizer",

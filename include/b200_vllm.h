@@ -320,6 +320,28 @@ typedef struct {
 
 B200_API int b200_rotary_embedding_and_cache(const b200_rotary_cache_params* p, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * One-shot all-reduce over NVLink peer memory for the latency-bound
+ * decode all-reduces of the row-parallel linears.  Replaces the one-shot path of
+ * csrc/custom_all_reduce.cuh:179-253 / custom_all_reduce.cu:50-148 (ops _C_custom_ar::*,
+ * csrc/torch_bindings.cpp:262-294; Python: distributed/device_communicators/custom_all_reduce.py).
+ *
+ * Every rank allocates one buffer of b200_ar_state_bytes() + 2 * max_bytes with b200_ar_alloc
+ * (zeroed; returns its 64-byte CUDA IPC handle), exchanges the handles out of band, opens the
+ * peers' with b200_ar_open, and passes the world_size base pointers (its own at index rank) to
+ * every b200_all_reduce call.  Sum in fp32 in rank order: all ranks produce identical bits.
+ * Sizes: numel * element size must be a multiple of 16 and <= max_bytes (else B200_ENOTSUP: the
+ * caller falls back to NCCL, as the reference does).  World sizes 2, 4, 6, 8.  Graph-capturable.
+ * ------------------------------------------------------------------------------------------ */
+B200_API int64_t b200_ar_state_bytes(void);
+B200_API int b200_ar_alloc(int64_t max_bytes, void** ptr, unsigned char* ipc_handle /* [64] */);
+B200_API int b200_ar_open(const unsigned char* ipc_handle /* [64] */, void** ptr);
+B200_API int b200_ar_close(void* ptr);
+B200_API int b200_ar_free(void* ptr);
+B200_API int b200_all_reduce(void* const* bases, int32_t rank, int32_t world, const void* input,
+                             void* output, int64_t numel, int32_t dtype, int64_t max_bytes,
+                             void* stream);
+
 #ifdef __cplusplus
 }
 #endif

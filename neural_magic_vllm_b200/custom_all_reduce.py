@@ -1,0 +1,128 @@
+"""One-shot all-reduce over NVLink peer memory -- host side.
+
+Mirror of the reference's ``CustomAllreduce``
+(``vllm/distributed/device_communicators/custom_all_reduce.py:38-272``): same constructor shape,
+``should_custom_ar`` / ``custom_all_reduce`` / ``close`` with the same meaning (``custom_all_reduce``
+returns the reduced tensor, or ``None`` when the tensor does not qualify and the caller must use
+NCCL -- ``parallel_state.py`` of the reference does exactly that).
+
+What differs, by design: there is no buffer registration (``register_buffer`` /
+``register_graph_buffers``): the kernel copies its input into a per-rank IPC staging buffer itself,
+so the same call works eagerly and under CUDA-graph capture, and the epoch that separates
+consecutive calls lives on the device.  IPC handles are exchanged once, through
+``torch.distributed.all_gather_object`` on the given group.
+
+Calls ``libb200vllm.so`` through its C ABI (``include/b200_vllm.h``: ``b200_ar_*``,
+``b200_all_reduce``); there is no fallback inside this class.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Union
+
+import torch
+import torch.distributed as dist
+
+from . import c_abi
+
+_DTYPE = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2}
+
+
+def _lib():
+    lib = c_abi()
+    lib.b200_last_error.restype = ctypes.c_char_p
+    lib.b200_ar_alloc.argtypes = [ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p), ctypes.c_char_p]
+    lib.b200_ar_open.argtypes = [ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p)]
+    lib.b200_ar_close.argtypes = [ctypes.c_void_p]
+    lib.b200_ar_free.argtypes = [ctypes.c_void_p]
+    lib.b200_all_reduce.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int32, ctypes.c_int32,
+                                    ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32,
+                                    ctypes.c_int64, ctypes.c_void_p]
+    return lib
+
+
+class CustomAllreduce:
+    _SUPPORTED_WORLD_SIZES = [2, 4, 6, 8]
+
+    def __init__(self, group: Optional[dist.ProcessGroup] = None,
+                 device: Union[int, str, torch.device, None] = None,
+                 max_size: int = 2 * 1024 * 1024) -> None:
+        # default max_size = the flag-in-data ("LL") range, where the kernel beats NCCL on B200
+        # (profiles/r1c_all_reduce.md); larger max_size also enables the staged one-shot kernel
+        self.disabled = True
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world_size = dist.get_world_size(group)
+        if self.world_size == 1:
+            return  # nothing to reduce (custom_all_reduce.py:66-68)
+        if self.world_size not in self._SUPPORTED_WORLD_SIZES:
+            return  # the caller keeps NCCL (custom_all_reduce.py:70-77)
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        elif isinstance(device, int):
+            device = torch.device("cuda", device)
+        elif isinstance(device, str):
+            device = torch.device(device)
+        self.device = device
+        self.max_size = int(max_size)
+        self._lib = _lib()
+        self._own = ctypes.c_void_p()
+        handle = ctypes.create_string_buffer(64)
+        with torch.cuda.device(device):
+            self._check(self._lib.b200_ar_alloc(self.max_size, ctypes.byref(self._own), handle))
+            handles: List[Optional[bytes]] = [None] * self.world_size
+            dist.all_gather_object(handles, handle.raw, group=group)
+            self._bases = (ctypes.c_void_p * self.world_size)()
+            self._opened: List[ctypes.c_void_p] = []
+            for r, h in enumerate(handles):
+                if r == self.rank:
+                    self._bases[r] = self._own.value
+                else:
+                    p = ctypes.c_void_p()
+                    self._check(self._lib.b200_ar_open(h, ctypes.byref(p)))
+                    self._opened.append(p)
+                    self._bases[r] = p.value
+        dist.barrier(group=group)  # every rank has mapped every buffer before the first call
+        self.disabled = False
+
+    def _check(self, rc: int) -> None:
+        if rc != 0:
+            raise RuntimeError(self._lib.b200_last_error().decode())
+
+    def should_custom_ar(self, inp: torch.Tensor) -> bool:
+        """custom_all_reduce.cu:37-48 of the reference: 16-byte multiple, within max_size,
+        (weakly) contiguous, a supported dtype."""
+        if self.disabled:
+            return False
+        nbytes = inp.numel() * inp.element_size()
+        return (inp.is_cuda and inp.dtype in _DTYPE and nbytes % 16 == 0 and nbytes <= self.max_size
+                and inp.is_contiguous() and inp.data_ptr() % 16 == 0)
+
+    def all_reduce(self, inp: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if out is None:
+            out = torch.empty_like(inp)
+        stream = torch.cuda.current_stream(inp.device).cuda_stream
+        self._check(self._lib.b200_all_reduce(self._bases, self.rank, self.world_size, inp.data_ptr(),
+                                              out.data_ptr(), inp.numel(), _DTYPE[inp.dtype],
+                                              self.max_size, stream))
+        return out
+
+    def custom_all_reduce(self, input: torch.Tensor) -> Optional[torch.Tensor]:
+        """The reduced tensor, or None when the caller must fall back to NCCL."""
+        if self.disabled or not self.should_custom_ar(input):
+            return None
+        return self.all_reduce(input)
+
+    def close(self) -> None:
+        if not self.disabled:
+            self.disabled = True
+            torch.cuda.synchronize(self.device)
+            for p in self._opened:
+                self._lib.b200_ar_close(p)
+            self._lib.b200_ar_free(self._own)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
