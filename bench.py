@@ -294,13 +294,21 @@ def main():
     e2e_value = nbytes * world / (e2e_ms / args.steps * 1e-3) / 1e9
     peak, peak_kind = measured_peak_hbm()
     per_gpu = nbytes / (ms_step * 1e-3) / 1e9
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
+    # capture of this workload (profiles/traffic.json names the source file); null when there is none
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get("paged_attention_v2_" + ("fp8" if fp8 else "fp16"), {}).get("bytes")
+    except Exception:
+        traffic = None
     line = {
         "metric": metric, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
         "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f16 (fp32 softmax/accumulate)" + (", fp8-e4m3 KV" if fp8 else ""),
         "data": "synthetic", "config": config,
         "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s",
-                     "frac": per_gpu / peak, "traffic": None, "peak_kind": f"of {peak_kind}",
+                     "frac": per_gpu / peak, "traffic": traffic, "peak_kind": f"of {peak_kind}",
                      "frac_of_8TBs_spec": per_gpu / 8000.0,
                      "kernel": "paged_attn_mma_kernel (+ reduce kernel: duration is the whole op)",
                      "algorithmic_bytes_per_launch": nbytes},

@@ -384,7 +384,8 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
   uint64_t* tmem_full = empty_a + kAStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp-uniform by construction: tell the compiler, so TMEM / barrier addresses live in uniform registers
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * BM;
   const int n0 = blockIdx.y * kTileN;
   const int split = blockIdx.z;
