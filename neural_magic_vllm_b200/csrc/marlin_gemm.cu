@@ -436,7 +436,7 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
         for (int l = 0; l < kLoadsW; ++l)
           tma_load_2d(w_dst + l * 4096, &tm_w, n0 * kWordsPerN + l * 256, kb * 4, &full_p[i], pol_w);
         if (args.s_rows > 0)
-          tma_load_2d(w_dst + P::kPackedBytes, &tm_s, n0, group_of(args, kb * kStageK), &full_p[i], pol_x);
+          tma_load_2d(w_dst + P::kPackedBytes, &tm_s, n0, ((kb * kStageK) >> args.group_shift), &full_p[i], pol_x);
       }
     }
     pdl_wait();  // the predecessor grid has completed: activations are visible
@@ -459,7 +459,7 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
         for (int l = 0; l < kLoadsW; ++l)
           tma_load_2d(w_dst + l * 4096, &tm_w, n0 * kWordsPerN + l * 256, kb * 4, &full_p[stage], pol_w);
         if (args.s_rows > 0)
-          tma_load_2d(s_dst, &tm_s, n0, group_of(args, kb * kStageK), &full_p[stage], pol_x);
+          tma_load_2d(s_dst, &tm_s, n0, ((kb * kStageK) >> args.group_shift), &full_p[stage], pol_x);
       }
       __syncwarp();
       if (++stage == kStages) stage = 0, phase ^= 1;
@@ -508,14 +508,24 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
     }
     // one group per 64-k stage (group_size >= 64; smaller groups take the shared-memory kernel)
     int cur_group = -1;
-    int stage = 0, as = 0;
-    uint32_t phase = 0, aphase = 0;
     const uint32_t lane_src = smem_u32(stages) + P::kXBytes + chunk_off<BITS>(0, nt) + lane * (BITS * 4) +
                               (qd & 1) * (BITS * 2);
     const uint32_t scale_src = smem_u32(stages) + P::kXBytes + P::kPackedBytes + (nt * 64 + 8 * a_row) * 2 +
                                (qd & 1) * 8;
     const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16);
-    for (int kb = kb_begin; kb < kb_end; ++kb) {
+    // The k loop is unrolled over one full trip of the stage ring, so the stage index, the TMEM
+    // A-ring slot and its phase are compile-time constants (kStages is a multiple of kAStages: every
+    // outer iteration starts with the A ring at slot 0, phase 0) -- no ring bookkeeping, constant
+    // shared-memory / TMEM offsets.
+    static_assert(kStages % kAStages == 0, "the unrolled dequant loop needs whole A-ring wraps");
+    uint32_t phase = 0;
+    for (int kb0 = kb_begin; kb0 < kb_end; kb0 += kStages, phase ^= 1) {
+#pragma unroll
+     for (int u = 0; u < kStages; ++u) {
+      const int kb = kb0 + u;
+      if (kb >= kb_end) break;
+      const int stage = u, as = u % kAStages;
+      const uint32_t aphase = (u / kAStages) & 1;
       mbar_wait_bounded(&full_p[stage], phase);
       const uint32_t w_src = lane_src + stage * P::kStageBytes;
       uint32_t words[4][BITS == 4 ? 2 : 4];
@@ -530,7 +540,7 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
         }
       }
       if (grouped) {
-        const int g = group_of(args, kb * kStageK);
+        const int g = ((kb * kStageK) >> args.group_shift);
         if (g != cur_group) {  // warp-uniform
           cur_group = g;
           const uint2 v = lds64(scale_src + stage * P::kStageBytes);
@@ -565,8 +575,7 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
       fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(&full_a[as]);
-      if (++stage == kStages) stage = 0, phase ^= 1;
-      if (++as == kAStages) as = 0, aphase ^= 1;
+     }
     }
     {
       const int n = n0 + qd * 32 + lane;
@@ -860,7 +869,9 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
 template <int BITS, typename T, bool ACT>
 int dispatch_bm(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t lda, cudaStream_t st) {
   // decode kernel: ungrouped, or groups that never change inside a 64-k stage
-  const bool one_group_per_stage = p.num_groups == 1 || (p.size_k / p.num_groups) % kStageK == 0;
+  // (and power-of-two group sizes, so the group index is a shift: every GPTQ group size is)
+  const int gsz = p.num_groups > 1 ? p.size_k / p.num_groups : 0;
+  const bool one_group_per_stage = p.num_groups == 1 || (gsz % kStageK == 0 && (gsz & (gsz - 1)) == 0);
   if (!ACT && one_group_per_stage) {
     switch (pick_bm(p.size_m)) {
       case 16: return launch_tmem<BITS, 16, T>(p, st);
