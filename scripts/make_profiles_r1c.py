@@ -74,7 +74,7 @@ def copies():
         s = os.path.join(G, src)
         if os.path.exists(s):
             shutil.copy(s, os.path.join(P, dst))
-    for rep, title, dst in (("f2/glue_add_rms.ncu-rep", "r1c: ncu --set full, fused_add_rms_norm fp16, 16384 tokens x 4096", "r1c_glue_add_rms_ncu.md"),
+    for rep, title, dst in (("f2/glue_add_rms.ncu-rep", "r1c: ncu --set full, rms_norm fp16 (the FUSED=0 instantiation was the one captured), 16384 tokens x 4096", "r1c_glue_add_rms_ncu.md"),
                             ("f2/glue_silu.ncu-rep", "r1c: ncu --set full, silu_and_mul fp16, 16384 tokens x 2x14336", "r1c_glue_silu_ncu.md"),
                             ("f2/glue_rotary_cache.ncu-rep", "r1c: ncu --set full, rotary_embedding_and_cache fp16, 16384 tokens", "r1c_glue_rotary_cache_ncu.md"),
                             ("f2/marlin_m16_gateup.ncu-rep", "r1c: ncu --set full, gptq_marlin_gemm W4A16 g128 decode kernel with PDL producer, gate_up M=16", "r1c_marlin_decode_ncu.md")):
