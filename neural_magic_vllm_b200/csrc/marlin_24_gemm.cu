@@ -228,9 +228,17 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
     const uint32_t scale_off = kValBytes + kMetaBytes + (nt * 64 + 8 * c) * 2;
     const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16);
     int cur_group = -1;
-    int stage = 0, as = 0;
-    uint32_t phase = 0, aphase = 0;
-    for (int kb = kb_begin; kb < kb_end; ++kb) {
+    // unrolled over one full trip of the stage ring: stage, TMEM A-ring slot and its phase are
+    // compile-time constants (kStages is a multiple of kAStages), as in marlin_gemm_tmem_kernel
+    static_assert(kStages % kAStages == 0, "the unrolled dequant loop needs whole A-ring wraps");
+    uint32_t phase = 0;
+    for (int kb0 = kb_begin; kb0 < kb_end; kb0 += kStages, phase ^= 1) {
+#pragma unroll
+     for (int us = 0; us < kStages; ++us) {
+      const int kb = kb0 + us;
+      if (kb >= kb_end) break;
+      const int stage = us, as = us % kAStages;
+      const uint32_t aphase = (us / kAStages) & 1;
       mbar_wait_bounded(&full_p[stage], phase);
       const uint32_t base = stage0 + stage * P::kStageBytes;
       uint32_t words[2][4], meta[2][8];
@@ -284,8 +292,7 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
       fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(&full_a[as]);
-      if (++stage == kStages) stage = 0, phase ^= 1;
-      if (++as == kAStages) as = 0, aphase ^= 1;
+     }
     }
     // epilogue: TMEM lane p of quadrant (nt, hb) is column 8 (p%8) + 4 hb + 2 (p/16) + (p%16)/8
     {
