@@ -4,7 +4,7 @@
 
 Correctness: (a) every rank holds identical bits; (b) the result equals the fp32 sum of the ranks'
 inputs in rank order, rounded once (reconstructed from an all_gather) -- bit-exact; (c) within
-rtol 1e-2 / atol 1e-3 of NCCL's all_reduce; eagerly and from a replayed CUDA graph with varying
+rtol 1e-2 / atol 8 fp16-ulp-at-2.0 of NCCL's all_reduce (NCCL rounds partial sums per hop); eagerly and from a replayed CUDA graph with varying
 sizes back to back (the epoch / double-buffer protocol).  Then latency per call from a CUDA graph of
 64 calls, one-shot vs NCCL."""
 from __future__ import annotations
@@ -37,7 +37,8 @@ def main():
             for it in range(3):
                 x = torch.randn(n, device="cuda", generator=g).to(dtype)
                 out = car.custom_all_reduce(x)
-                assert out is not None
+                if out is None:  # above the world-size policy limit: still exercise the kernel itself
+                    out = car.all_reduce(x)
                 gathered = [torch.empty_like(x) for _ in range(world)]
                 dist.all_gather(gathered, x)
                 acc = torch.zeros(n, device="cuda", dtype=torch.float32)
@@ -49,7 +50,10 @@ def main():
                 dist.all_gather(outs, out)
                 same = all(torch.equal(o, outs[0]) for o in outs)
                 bit = torch.equal(out, exact)
-                close = torch.allclose(out.float(), ref.float(), rtol=1e-2, atol=1e-3 if dtype is not torch.bfloat16 else 2e-2)
+                # NCCL rounds its partial sums to the element type at every hop (world > 2), ours
+                # rounds once: where the sum cancels, NCCL is off by an ulp of the PARTIAL magnitude
+                atol = {torch.half: 1.6e-2, torch.bfloat16: 1.3e-1, torch.float: 1e-4}[dtype]
+                close = torch.allclose(out.float(), ref.float(), rtol=1e-2, atol=atol)
                 if not (same and bit and close):
                     ok = False
                     if rank == 0:
@@ -62,20 +66,50 @@ def main():
     s = torch.cuda.Stream()
     with torch.cuda.stream(s):
         for x in xs:
-            car.custom_all_reduce(x)
+            car.all_reduce(x)
         s.synchronize()
         gph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(gph, stream=s):
-            outs = [car.custom_all_reduce(x) for x in xs]
+            outs = [car.all_reduce(x) for x in xs]
         for _ in range(20):
             gph.replay()
         s.synchronize()
     for x, o in zip(xs, outs):
         ref = x.clone(); dist.all_reduce(ref)
-        if not torch.allclose(o.float(), ref.float(), rtol=1e-2, atol=1e-3):
+        if not torch.allclose(o.float(), ref.float(), rtol=1e-2, atol=1.6e-2):
             ok = False
             if rank == 0:
                 print("GRAPH MISMATCH", x.numel(), flush=True)
+    # fused all-reduce + residual add + RMSNorm == all_reduce then fused_add_rms_norm (our own ops)
+    import neural_magic_vllm_b200 as pkg
+    for dtype in (torch.half, torch.bfloat16):
+        for tokens, hidden in ((1, 4096), (8, 4096), (64, 4096), (100, 5120), (256, 4096), (3, 8192)):
+            for it in range(2):
+                x = torch.randn(tokens, hidden, device="cuda", generator=g).to(dtype)
+                res = torch.empty(tokens, hidden, device="cuda", dtype=dtype)
+                w = torch.empty(hidden, device="cuda", dtype=dtype)
+                if rank == 0:
+                    res.copy_(torch.randn(tokens, hidden, device="cuda", generator=g).to(dtype))
+                    w.copy_((torch.randn(hidden, device="cuda", generator=g) * 0.1 + 1).to(dtype))
+                dist.broadcast(res, 0); dist.broadcast(w, 0)  # residual / weight are replicated under TP
+                ref_x = car.all_reduce(x); ref_r = res.clone()
+                pkg.ops.fused_add_rms_norm(ref_x, ref_r, w, 1e-5)
+                fx, fr = x.clone(), res.clone()
+                done = car.all_reduce_add_rms_norm(fx, fr, w, 1e-5)
+                if not done and x.numel() * x.element_size() > car.one_shot_limit:
+                    continue  # above this world size's one-shot policy limit: the two-op path is the product path
+                if not done:
+                    ok = False
+                    if rank == 0:
+                        print(f"FUSED NOT TAKEN {dtype} {tokens}x{hidden}", flush=True)
+                    continue
+                ulp = 2.0 ** -10 if dtype is torch.half else 2.0 ** -7
+                good = torch.equal(fr, ref_r) and torch.allclose(fx.float(), ref_x.float(), rtol=2 * ulp, atol=1e-5)
+                if not good:
+                    ok = False
+                    if rank == 0:
+                        print(f"FUSED MISMATCH {dtype} {tokens}x{hidden} it={it} res_equal={torch.equal(fr, ref_r)} "
+                              f"maxdiff={(fx.float() - ref_x.float()).abs().max().item()}", flush=True)
     flag = torch.tensor([1 if ok else 0], device="cuda"); dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     ok = bool(flag.item())
 
@@ -84,7 +118,7 @@ def main():
     for n in (4096, 8 * 4096, 64 * 4096, 256 * 4096, 1024 * 4096):
         x = torch.randn(n, device="cuda", generator=g).half()
         res = {}
-        for name, fn in (("one_shot", lambda: car.custom_all_reduce(x)), ("nccl", lambda: dist.all_reduce(x))):
+        for name, fn in (("one_shot", lambda: car.all_reduce(x)), ("nccl", lambda: dist.all_reduce(x))):
             with torch.cuda.stream(s):
                 for _ in range(3):
                     fn()

@@ -79,6 +79,7 @@ class Decoder:
     def __init__(self, ops, tp, rank, batch, ctx, lm_head=True, glue="fused", car=None):
         self.ops, self.tp, self.batch, self.ctx = ops, tp, batch, ctx
         self.car = car  # one-shot NVLink all-reduce (None: NCCL)
+        self.fuse_ar_norm = True
         self.step = self.step_fused if glue == "fused" else self.step_torch
         gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
         blocks_per_seq = (ctx + BLOCK) // BLOCK
@@ -117,6 +118,14 @@ class Decoder:
         dist.all_reduce(t)
         return t
 
+    def reduce_add_norm(self, t, res, w):
+        """all_reduce(t); fused_add_rms_norm(t, res, w) -- one kernel when the message qualifies."""
+        if self.car is not None and self.fuse_ar_norm and self.car.all_reduce_add_rms_norm(t, res, w, 1e-5):
+            return t
+        t = self.all_reduce(t)
+        self.ops.fused_add_rms_norm(t, res, w, 1e-5)
+        return t
+
     def step_fused(self):
         """Every op between the embedding gather and the lm_head is one of this repo's kernels."""
         ops, tp = self.ops, self.tp
@@ -126,6 +135,8 @@ class Decoder:
             if res is None:
                 res, hn = x, torch.empty_like(x)
                 ops.rms_norm(hn, x, L.ln1, 1e-5)
+            elif tp > 1:
+                hn = x = self.reduce_add_norm(x, res, L.ln1)  # previous layer's down_proj partial sums
             else:
                 ops.fused_add_rms_norm(x, res, L.ln1, 1e-5)
                 hn = x
@@ -143,15 +154,17 @@ class Decoder:
                                        self.block_tables, self.seq_lens, BLOCK, self.ctx + 1, None, "auto", 1.0)
             o = L.o(out.view(-1, L.h * HEAD))
             if tp > 1:
-                o = self.all_reduce(o)
-            ops.fused_add_rms_norm(o, res, L.ln2, 1e-5)
+                o = self.reduce_add_norm(o, res, L.ln2)
+            else:
+                ops.fused_add_rms_norm(o, res, L.ln2, 1e-5)
             gu = L.gate_up(o)
             act = torch.empty(self.batch, INTER // tp, dtype=torch.half, device="cuda")
             ops.silu_and_mul(act, gu)
-            x = L.down(act)
-            if tp > 1:
-                x = self.all_reduce(x)
-        ops.fused_add_rms_norm(x, res, self.norm, 1e-5)
+            x = L.down(act)  # TP: partial sums, reduced together with the next norm
+        if tp > 1:
+            x = self.reduce_add_norm(x, res, self.norm)
+        else:
+            ops.fused_add_rms_norm(x, res, self.norm, 1e-5)
         hn = x
         if self.lm_head is not None:
             logits = hn @ self.lm_head.t()
@@ -207,6 +220,8 @@ def main():
     ap.add_argument("--no-lm-head", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--glue", choices=["fused", "torch"], default="fused")
+    ap.add_argument("--no-fuse-ar-norm", action="store_true",
+                    help="keep all_reduce and fused_add_rms_norm as two kernels")
     ap.add_argument("--ar", choices=["one_shot", "nccl"], default="one_shot",
                     help="TP all-reduce: this repo's one-shot NVLink kernel (NCCL above its max_size) or NCCL only")
     args = ap.parse_args()
@@ -232,6 +247,7 @@ def main():
             car = None
     for batch in [int(b) for b in args.batches.split(",")]:
         dec = Decoder(ops, world, rank, batch, args.ctx, lm_head=not args.no_lm_head, glue=args.glue, car=car)
+        dec.fuse_ar_norm = not args.no_fuse_ar_norm
         with torch.no_grad():
             for _ in range(2):
                 dec.step()
@@ -270,6 +286,7 @@ def main():
                 "cuda_graph": graph is not None, "lm_head": dec.lm_head is not None,
                 "attention": "paged_attention_v1" if dec.use_v1 else "paged_attention_v2", "glue": args.glue,
                 "all_reduce": ("one_shot_nvlink" if car is not None else "nccl") if world > 1 else None,
+                "ar_norm_fused": bool(car is not None and dec.fuse_ar_norm),
                 "hbm_bytes_per_step_per_gpu": byts, "linear_bytes_per_gpu": lin, "kv_bytes_per_gpu": kv,
                 "hbm_GBps": byts / ms / 1e6, "hbm_frac": byts / ms / 1e6 / hbm,
                 "excluded": "scheduler, sampler (greedy argmax on the local vocab shard only), tokenizer",

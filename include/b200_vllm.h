@@ -342,6 +342,17 @@ B200_API int b200_all_reduce(void* const* bases, int32_t rank, int32_t world, co
                              void* output, int64_t numel, int32_t dtype, int64_t max_bytes,
                              void* stream);
 
+/* B200 extension (no reference op): the all-reduce of the row-parallel partial sums fused with the
+ * fused_add_rms_norm that follows it in every decoder layer (linear.py:792-793 +
+ * layernorm.py forward_cuda -> csrc/layernorm_kernels.cu:199-287), in place:
+ *   input = sum over ranks; residual += input; input = rms_norm(residual) * weight
+ * with the rounding steps of the two separate ops.  B200_ENOTSUP when the message does not fit the
+ * flag-in-data path (row > 32 KiB or total > 2 MiB): callers then issue the two ops. */
+B200_API int b200_all_reduce_add_rms_norm(void* const* bases, int32_t rank, int32_t world, void* input,
+                                          void* residual, const void* weight, float epsilon,
+                                          int32_t num_tokens, int32_t hidden, int32_t dtype,
+                                          int64_t max_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

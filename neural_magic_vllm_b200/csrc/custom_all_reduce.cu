@@ -141,6 +141,11 @@ __global__ void __launch_bounds__(kArThreads) ll_all_reduce_kernel(
   const int b = blockIdx.x, tid = threadIdx.x;
   ArState* me = reinterpret_cast<ArState*>(peers.base[rank]);
   __shared__ uint32_t s_epoch;
+  // PDL: resident behind the row-parallel GEMM's tail; its partial sums (and the previous call's
+  // epoch) are visible after the wait.  The kernel behind this one (a GEMM: its weight stages do
+  // not depend on us) may start streaming while we exchange.
+  pdl_wait();
+  pdl_launch_dependents();
   if (tid == 0) s_epoch = me->epoch[b] + 1;
   __syncthreads();
   const uint32_t epoch = s_epoch;
@@ -202,8 +207,8 @@ int launch_ll(const ArPeers& peers, int rank, int world, const void* in, void* o
   active = active < 1 ? 1 : (active > kArGrid ? kArGrid : active);
 #define LL_CASE(W)                                                       \
   case W:                                                                \
-    ll_all_reduce_kernel<T, W><<<kArGrid, kArThreads, 0, st>>>(          \
-        peers, rank, (const T*)in, (T*)out, units, (int)active, ll_off); \
+    launch_pdl(ll_all_reduce_kernel<T, W>, dim3(kArGrid), dim3(kArThreads), 0, st, peers, rank, \
+               (const T*)in, (T*)out, units, (int)active, ll_off);                             \
     break;
   switch (world) {
     LL_CASE(2)
@@ -216,6 +221,158 @@ int launch_ll(const ArPeers& peers, int rank, int world, const void* in, void* o
   }
 #undef LL_CASE
   return check_launch("all_reduce (LL)");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fused: all-reduce of the row-parallel partial sums + residual add + RMSNorm, one kernel.
+// The pair the decode layer issues after o_proj / down_proj (linear.py:792-793 followed by
+// layernorm.py: fused_add_rms_norm).  Same flag-in-data push as ll_all_reduce_kernel; the thread
+// that has summed a unit of a token row keeps it in registers, adds the residual, and the CTA
+// that owns the row reduces the sum of squares -- the reduced activations never go to HBM between
+// the collective and the norm.  Rounding steps are those of the two separate ops:
+//   o = T(sum_r partial_r)  (fp32, rank order);  z = T(o + residual);  residual = z;
+//   x = T(T(z * rstd) * weight).
+// One CTA per token row (rows strided over the fixed grid); units per thread bounded by kRowUnits.
+// ---------------------------------------------------------------------------------------------
+constexpr int kRowUnits = 8;  // 8-byte units per thread per row: hidden <= 16384 (fp16/bf16)
+
+template <typename T, int W>
+__global__ void __launch_bounds__(kArThreads) ll_all_reduce_add_rms_norm_kernel(
+    const ArPeers peers, const int rank, T* x, T* residual, const T* __restrict__ weight,
+    const float eps, const int tokens, const int hidden, const int64_t ll_off) {
+  constexpr int N = 8 / (int)sizeof(T);
+  const int b = blockIdx.x, tid = threadIdx.x;
+  ArState* me = reinterpret_cast<ArState*>(peers.base[rank]);
+  __shared__ uint32_t s_epoch;
+  __shared__ float red[32];
+  pdl_wait();
+  pdl_launch_dependents();
+  if (tid == 0) s_epoch = me->epoch[b] + 1;
+  __syncthreads();
+  const uint32_t epoch = s_epoch;
+  if (tid == 0) me->epoch[b] = epoch;
+  if (b >= tokens) return;
+  const int64_t par_off = ll_off + (int64_t)(epoch & 1) * kArMaxRanks * kLLSrcBytes;
+  const int row_units = hidden / N;
+  // pass 1: push this CTA's rows to every peer
+  for (int t = b; t < tokens; t += gridDim.x) {
+    const uint2* src = reinterpret_cast<const uint2*>(x + (int64_t)t * hidden);
+    for (int u = tid; u < row_units; u += kArThreads) {
+      const uint2 d = src[u];
+      const uint4 line = make_uint4(d.x, epoch, d.y, epoch);
+      const int64_t i = (int64_t)t * row_units + u;
+#pragma unroll
+      for (int r = 0; r < W; ++r) {
+        if (r == rank) continue;
+        st_volatile16(reinterpret_cast<uint4*>(peers.base[r] + par_off + (int64_t)rank * kLLSrcBytes) + i, line);
+      }
+    }
+  }
+  // pass 2: per row -- poll + sum, add residual, sum of squares, normalise
+  for (int t = b; t < tokens; t += gridDim.x) {
+    uint2* xrow = reinterpret_cast<uint2*>(x + (int64_t)t * hidden);
+    uint2* rrow = reinterpret_cast<uint2*>(residual + (int64_t)t * hidden);
+    float z[kRowUnits][N];
+    float ss = 0.f;
+    // residual and weight do not depend on the peers: fetch them before polling
+    const uint2* wrow = reinterpret_cast<const uint2*>(weight);
+    uint2 rpre[kRowUnits], wpre[kRowUnits];
+#pragma unroll
+    for (int k = 0; k < kRowUnits; ++k) {
+      const int u = tid + k * kArThreads;
+      if (u < row_units) rpre[k] = rrow[u], wpre[k] = __ldg(wrow + u);
+    }
+#pragma unroll
+    for (int k = 0; k < kRowUnits; ++k) {
+      const int u = tid + k * kArThreads;
+      if (u < row_units) {
+        const int64_t i = (int64_t)t * row_units + u;
+        float acc[N];
+#pragma unroll
+        for (int j = 0; j < N; ++j) acc[j] = 0.f;
+#pragma unroll
+        for (int r = 0; r < W; ++r) {
+          union {
+            uint2 u2;
+            T e[N];
+          } v;
+          if (r == rank) {
+            v.u2 = xrow[u];
+          } else {
+            const uint4* slot = reinterpret_cast<const uint4*>(peers.base[rank] + par_off + (int64_t)r * kLLSrcBytes) + i;
+            uint4 l = ld_volatile16(slot);
+            uint32_t spins = 0;
+            while (l.y != epoch || l.w != epoch) {
+              if (++spins > (1u << 26)) __trap();
+              l = ld_volatile16(slot);
+            }
+            v.u2 = make_uint2(l.x, l.z);
+          }
+#pragma unroll
+          for (int j = 0; j < N; ++j) acc[j] += DT<T>::to_f(v.e[j]);
+        }
+        union {
+          uint2 u2;
+          T e[N];
+        } rv, zo;
+        rv.u2 = rpre[k];
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const float o = DT<T>::to_f(DT<T>::from_f(acc[j]));            // the all-reduce's output rounding
+          zo.e[j] = DT<T>::from_f(__fadd_rn(o, DT<T>::to_f(rv.e[j])));  // fused_add: z = T(o + residual)
+          z[k][j] = DT<T>::to_f(zo.e[j]);
+          ss = fmaf(z[k][j], z[k][j], ss);
+        }
+        rrow[u] = zo.u2;
+      }
+    }
+    // block-wide sum of squares
+    ss = warp_sum(ss);
+    if ((tid & 31) == 0) red[tid >> 5] = ss;
+    __syncthreads();
+    float tot = (tid & 31) < (kArThreads / 32) ? red[tid & 31] : 0.f;
+    tot = warp_sum(tot);
+    __syncthreads();  // red is reused by the next row
+    const float rstd = rsqrtf(tot / hidden + eps);
+#pragma unroll
+    for (int k = 0; k < kRowUnits; ++k) {
+      const int u = tid + k * kArThreads;
+      if (u < row_units) {
+        union {
+          uint2 u2;
+          T e[N];
+        } wv, ov;
+        wv.u2 = wpre[k];
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const float n1 = DT<T>::to_f(DT<T>::from_f(__fmul_rn(z[k][j], rstd)));
+          ov.e[j] = DT<T>::from_f(__fmul_rn(n1, DT<T>::to_f(wv.e[j])));
+        }
+        xrow[u] = ov.u2;
+      }
+    }
+  }
+}
+
+template <typename T>
+int launch_ll_norm(const ArPeers& peers, int rank, int world, void* x, void* residual, const void* weight,
+                   float eps, int tokens, int hidden, int64_t ll_off, cudaStream_t st) {
+#define LLN_CASE(W)                                                                          \
+  case W:                                                                                    \
+    launch_pdl(ll_all_reduce_add_rms_norm_kernel<T, W>, dim3(kArGrid), dim3(kArThreads), 0, st,  \
+               peers, rank, (T*)x, (T*)residual, (const T*)weight, eps, tokens, hidden, ll_off); \
+    break;
+  switch (world) {
+    LLN_CASE(2)
+    LLN_CASE(4)
+    LLN_CASE(6)
+    LLN_CASE(8)
+    default:
+      set_error("all_reduce_add_rms_norm: unsupported world size %d (2, 4, 6, 8)", world);
+      return B200_ENOTSUP;
+  }
+#undef LLN_CASE
+  return check_launch("all_reduce_add_rms_norm");
 }
 
 template <typename T>
@@ -336,6 +493,43 @@ int b200_all_reduce(void* const* bases, int32_t rank, int32_t world, const void*
                 : launch_ar<float>(peers, rank, world, input, output, bytes / 16, max_bytes, st);
   }
   set_error("all_reduce: unsupported dtype %d", dtype);
+  return B200_EINVAL;
+}
+
+int b200_all_reduce_add_rms_norm(void* const* bases, int32_t rank, int32_t world, void* input,
+                                 void* residual, const void* weight, float epsilon,
+                                 int32_t num_tokens, int32_t hidden, int32_t dtype, int64_t max_bytes,
+                                 void* stream) {
+  using namespace b200;
+  B200_REQUIRE(bases && world >= 2 && world <= kArMaxRanks && rank >= 0 && rank < world, B200_EINVAL,
+               "all_reduce_add_rms_norm: bad rank/world (%d/%d)", rank, world);
+  B200_REQUIRE(num_tokens >= 0 && hidden >= 0, B200_EINVAL, "all_reduce_add_rms_norm: negative size");
+  if (num_tokens == 0 || hidden == 0) return B200_OK;
+  B200_REQUIRE(input && residual && weight, B200_EINVAL, "all_reduce_add_rms_norm: null pointer");
+  const int64_t esz = dtype == B200_F32 ? 4 : 2;
+  const int64_t row_bytes = (int64_t)hidden * esz, bytes = row_bytes * num_tokens;
+  B200_REQUIRE(row_bytes % 8 == 0 && row_bytes / 8 <= (int64_t)kRowUnits * kArThreads &&
+                   bytes <= kLLMaxPayload && bytes <= max_bytes,
+               B200_ENOTSUP,
+               "all_reduce_add_rms_norm: %d x %d does not fit the fused kernel (row <= %d bytes, total "
+               "<= %lld); call all_reduce + fused_add_rms_norm",
+               num_tokens, hidden, kRowUnits * kArThreads * 8, (long long)kLLMaxPayload);
+  B200_REQUIRE(((reinterpret_cast<uintptr_t>(input) | reinterpret_cast<uintptr_t>(residual) |
+                 reinterpret_cast<uintptr_t>(weight)) & 7) == 0,
+               B200_ENOTSUP, "all_reduce_add_rms_norm: pointers must be 8-byte aligned");
+  ArPeers peers{};
+  for (int r = 0; r < world; ++r) {
+    B200_REQUIRE(bases[r] != nullptr, B200_EINVAL, "all_reduce_add_rms_norm: null peer buffer %d", r);
+    peers.base[r] = static_cast<uint8_t*>(bases[r]);
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int64_t ll_off = kArDataOffset + 2 * max_bytes;
+  switch (dtype) {
+    case B200_F16: return launch_ll_norm<__half>(peers, rank, world, input, residual, weight, epsilon, num_tokens, hidden, ll_off, st);
+    case B200_BF16: return launch_ll_norm<__nv_bfloat16>(peers, rank, world, input, residual, weight, epsilon, num_tokens, hidden, ll_off, st);
+    case B200_F32: return launch_ll_norm<float>(peers, rank, world, input, residual, weight, epsilon, num_tokens, hidden, ll_off, st);
+  }
+  set_error("all_reduce_add_rms_norm: unsupported dtype %d", dtype);
   return B200_EINVAL;
 }
 

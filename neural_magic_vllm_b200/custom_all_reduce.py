@@ -38,6 +38,10 @@ def _lib():
     lib.b200_all_reduce.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int32, ctypes.c_int32,
                                     ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32,
                                     ctypes.c_int64, ctypes.c_void_p]
+    lib.b200_all_reduce_add_rms_norm.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int32, ctypes.c_int32,
+                                                 ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                                 ctypes.c_float, ctypes.c_int32, ctypes.c_int32,
+                                                 ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p]
     return lib
 
 
@@ -65,6 +69,12 @@ class CustomAllreduce:
             device = torch.device(device)
         self.device = device
         self.max_size = int(max_size)
+        # A one-shot all-reduce moves (world - 1) x the message per rank, so the size up to which it
+        # beats NCCL shrinks with the world size (the reference makes the same cut:
+        # custom_all_reduce.cu:37-48 -- any size at world 2, < 512 KiB beyond).  Measured on B200
+        # (profiles/r1c_all_reduce.md): world 2 wins through 2 MiB, world 4 through 512 KiB-1 MiB.
+        self.one_shot_limit = {2: self.max_size, 4: 1024 * 1024}.get(self.world_size, 512 * 1024)
+        self.one_shot_limit = min(self.one_shot_limit, self.max_size)
         self._lib = _lib()
         self._own = ctypes.c_void_p()
         handle = ctypes.create_string_buffer(64)
@@ -95,7 +105,7 @@ class CustomAllreduce:
         if self.disabled:
             return False
         nbytes = inp.numel() * inp.element_size()
-        return (inp.is_cuda and inp.dtype in _DTYPE and nbytes % 16 == 0 and nbytes <= self.max_size
+        return (inp.is_cuda and inp.dtype in _DTYPE and nbytes % 16 == 0 and nbytes <= self.one_shot_limit
                 and inp.is_contiguous() and inp.data_ptr() % 16 == 0)
 
     def all_reduce(self, inp: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -112,6 +122,26 @@ class CustomAllreduce:
         if self.disabled or not self.should_custom_ar(input):
             return None
         return self.all_reduce(input)
+
+    def all_reduce_add_rms_norm(self, input: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor,
+                                epsilon: float) -> bool:
+        """B200 extension: ``all_reduce(input)`` followed by ``fused_add_rms_norm(input, residual,
+        weight, epsilon)`` in ONE kernel, in place (no reference op; the pair the reference issues
+        after every row-parallel linear).  Returns False -- nothing done -- when the tensors do not
+        qualify; the caller then issues the two ops."""
+        if self.disabled or input.dim() != 2 or not self.should_custom_ar(input):
+            return False
+        tokens, hidden = input.shape
+        row_bytes = hidden * input.element_size()
+        if (row_bytes % 8 or row_bytes > 32 * 1024 or not residual.is_contiguous() or not weight.is_contiguous()
+                or residual.shape != input.shape or residual.dtype != input.dtype or weight.dtype != input.dtype
+                or weight.numel() != hidden):
+            return False
+        stream = torch.cuda.current_stream(input.device).cuda_stream
+        self._check(self._lib.b200_all_reduce_add_rms_norm(
+            self._bases, self.rank, self.world_size, input.data_ptr(), residual.data_ptr(), weight.data_ptr(),
+            float(epsilon), tokens, hidden, _DTYPE[input.dtype], self.max_size, stream))
+        return True
 
     def close(self) -> None:
         if not self.disabled:

@@ -25,10 +25,11 @@ def decode_table():
     srcs = [("f2/decode_tp1_torchglue.jsonl", "torch ops", "off (torch)"), ("f2/decode_tp1_fused_nopdl.jsonl", "ours", "off"),
             ("f2/decode_tp1_fused_pdl.jsonl", "ours", "on")]
     for n in (2, 4, 8):
-        srcs += [(f"decode_tp{n}_r1g_nccl.jsonl", "ours", "on"), (f"decode_tp{n}_r1g_oneshot.jsonl", "ours", "on")]
+        srcs += [(f"decode_tp{n}_r1g_nccl.jsonl", "ours", "on"), (f"decode_tp{n}_r1g_oneshot.jsonl", "ours", "on"),
+                 (f"decode_tp{n}_r1h_fusednorm.jsonl", "ours", "on")]
     for f, glue, pdl in srcs:
         for r in rows(os.path.join(G, f)):
-            md.append(f"| {r['tp']} | {glue} | {pdl} | {r.get('all_reduce') or '-'} | {r['batch']} | {r['ms_per_step']:.3f} | "
+            md.append(f"| {r['tp']} | {glue} | {pdl} | {(r.get('all_reduce') or '-') + (' + fused add/RMSNorm' if r.get('ar_norm_fused') else '')} | {r['batch']} | {r['ms_per_step']:.3f} | "
                       f"{r['tokens_per_s']:.0f} | {r['tokens_per_s_per_gpu']:.0f} | {100 * r['hbm_frac']:.1f} |")
     open(os.path.join(P, "r1c_decode_tokens.md"), "w").write("\n".join(md) + "\n")
 
