@@ -133,6 +133,10 @@ class CustomAllreduce:
             return False
         tokens, hidden = input.shape
         row_bytes = hidden * input.element_size()
+        # one CTA per row over a fixed 72-CTA grid: past ~2 rows per CTA the two-kernel path wins
+        # (measured at TP2, batch 256: profiles/r1c_decode_tokens.md)
+        if tokens > 144:
+            return False
         if (row_bytes % 8 or row_bytes > 32 * 1024 or not residual.is_contiguous() or not weight.is_contiguous()
                 or residual.shape != input.shape or residual.dtype != input.dtype or weight.dtype != input.dtype
                 or weight.numel() != hidden):
