@@ -20,7 +20,9 @@ def rows(path):
 def decode_table():
     md = ["# r1c: Llama-3-8B W4A16 (gptq_marlin g128) decode tokens/s, ctx 1024, CUDA-graph replay (benchmarks/decode_bench.py)",
           "", "Sampler/scheduler/tokenizer excluded; lm_head fp16 torch matmul + argmax. `glue` = who runs RMSNorm / RoPE+cache write / SiLU*mul;",
-          "`PDL` = programmatic dependent launch across the chain; `all_reduce` = TP partial-sum reduction.", "",
+          "`PDL` = programmatic dependent launch across the chain; `all_reduce` = TP partial-sum reduction (messages above the",
+          "world-size one-shot limit -- 2 MiB / 1 MiB / 512 KiB at world 2 / 4 / 8, i.e. batch 256 at TP4 -- go through NCCL in every configuration;",
+          "the fused add/RMSNorm kernel is taken up to 144 rows).", "",
           "| TP | glue | PDL | all_reduce | batch | ms/step | tokens/s (job) | tokens/s/GPU | % HBM peak (weights+KV+lm_head) |", "|---|---|---|---|---|---|---|---|---|"]
     srcs = [("f2/decode_tp1_torchglue.jsonl", "torch ops", "off (torch)"), ("f2/decode_tp1_fused_nopdl.jsonl", "ours", "off"),
             ("f2/decode_tp1_fused_pdl.jsonl", "ours", "on")]
