@@ -96,7 +96,8 @@ def main():
                 pkg.ops.fused_add_rms_norm(ref_x, ref_r, w, 1e-5)
                 fx, fr = x.clone(), res.clone()
                 done = car.all_reduce_add_rms_norm(fx, fr, w, 1e-5)
-                if not done and (x.numel() * x.element_size() > car.one_shot_limit or tokens > 144):
+                if not done and (x.numel() * x.element_size() > car.one_shot_limit or tokens > 144
+                                 or (world > 4 and tokens < 32)):
                     continue  # above this world size's one-shot policy limit: the two-op path is the product path
                 if not done:
                     ok = False

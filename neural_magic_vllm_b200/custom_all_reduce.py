@@ -137,6 +137,11 @@ class CustomAllreduce:
         # (measured at TP2, batch 256: profiles/r1c_decode_tokens.md)
         if tokens > 144:
             return False
+        # at world 6/8 a lone row (one CTA pushing to 7 peers) loses to the two-kernel path, which
+        # spreads a small message over more CTAs; from a few dozen rows the fused kernel wins again
+        # (TP8: batch 1/8 551/4082 vs 519/3906 tokens/s unfused vs fused, batch 64 21653 vs 22329)
+        if self.world_size > 4 and tokens < 32:
+            return False
         if (row_bytes % 8 or row_bytes > 32 * 1024 or not residual.is_contiguous() or not weight.is_contiguous()
                 or residual.shape != input.shape or residual.dtype != input.dtype or weight.dtype != input.dtype
                 or weight.numel() != hidden):
