@@ -10,7 +10,9 @@ Scheduler, sampler and tokenizer are excluded (stated).
 
 Tensor parallel: launched under torchrun, rank r owns q heads / kv heads / the
 column shards of qkv and gate_up and the row (K) shards of o and down; the two partial sums per
-layer are all-reduced by NCCL inside the captured CUDA graph (linear.py:792-793 of the reference).
+layer (linear.py:792-793 of the reference) are reduced inside the captured CUDA graph by this repo's
+one-shot NVLink all-reduce -- fused with the add + RMSNorm behind it where the message qualifies --
+and by NCCL above its size limit (--ar nccl: NCCL only; --no-fuse-ar-norm: two kernels).
 
 Random-init quantized weights (any int4 pattern is a valid weight), context filled with random KV.
 
