@@ -314,7 +314,7 @@ int b200_convert_fp8(void* dst, const void* src, int64_t numel, float scale, int
                "convert_fp8: Unsupported data type: kv dtype enum %d", kv_dtype);
   const int threads = 256;
   int64_t blocks64 = (numel + threads - 1) / threads;
-  const int blocks = (int)(blocks64 > kNumSMs * 16 ? kNumSMs * 16 : blocks64);
+  const int blocks = (int)(blocks64 > num_sms() * 16 ? num_sms() * 16 : blocks64);
 #define CV(T, KV)                                                                              \
   if (to_fp8)                                                                                  \
     convert_fp8_kernel<T, KV, true><<<blocks, threads, 0, stream>>>(dst, src, numel, scale);   \

@@ -34,6 +34,33 @@ bool pdl_enabled() {
   return !(e != nullptr && e[0] == '0');
 }
 
+int num_sms() {
+  static int cached[kMaxDevices] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    cudaGetLastError();
+    return 148;
+  }
+  if (dev >= 0 && dev < kMaxDevices && cached[dev] > 0) return cached[dev];
+  int v = 0;
+  if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) {
+    cudaGetLastError();
+    v = 148;
+  }
+  if (dev >= 0 && dev < kMaxDevices) cached[dev] = v;
+  return v;
+}
+
+int env_int_once(const char* name, int* cache, int unset) {
+  // cache[0]: 0 = not read yet; cache[1]: the value (`unset` when the variable is absent)
+  if (cache[0] == 0) {
+    const char* e = getenv(name);
+    cache[1] = e != nullptr ? atoi(e) : unset;
+    cache[0] = 1;
+  }
+  return cache[1];
+}
+
 }  // namespace b200
 
 extern "C" {

@@ -27,7 +27,25 @@ int check_launch(const char* what);    // returns B200_OK / B200_ECUDA after a k
     }                                    \
   } while (0)
 
-constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
+constexpr int kMaxDevices = 64;
+// SM count of the CURRENT device, queried once per device (148 on B200: 2 dies x 74 SMs)
+int num_sms();  // capi.cu
+// integer tuning knob from the environment, read once per process (benchmark sweeps only)
+int env_int_once(const char* name, int* cache, int unset);  // capi.cu
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per (function, device): remember, per device, the
+// largest size already configured for this kernel so the attribute call leaves the launch path.
+// `configured` is a zero-initialised static owned by the call site (one per kernel instantiation).
+template <typename K>
+inline cudaError_t ensure_dyn_smem(K kern, size_t bytes, size_t (&configured)[kMaxDevices]) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev >= 0 && dev < kMaxDevices && bytes <= configured[dev]) return cudaSuccess;
+  e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e == cudaSuccess && dev >= 0 && dev < kMaxDevices) configured[dev] = bytes;
+  return e;
+}
 
 // ---- small device utilities ---------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {

@@ -474,7 +474,7 @@ int launch_act(void* out, const void* in, int tokens, int d, cudaStream_t st) {
   const int per_cta = 256 * (vec ? N : 1);
   int chunks = (d + per_cta - 1) / per_cta;
   // enough CTAs to cover the SMs at small batch; one pass per CTA at large batch
-  const int cap = tokens >= 4 * kNumSMs ? 1 : (4 * kNumSMs + tokens - 1) / tokens;
+  const int cap = tokens >= 4 * num_sms() ? 1 : (4 * num_sms() + tokens - 1) / tokens;
   chunks = chunks > cap ? cap : chunks;
   dim3 grid(tokens, chunks < 1 ? 1 : chunks);
   if (vec)

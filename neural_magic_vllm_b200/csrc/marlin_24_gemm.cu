@@ -375,7 +375,7 @@ int launch24(const b200_gptq_marlin_24_gemm_params& p, cudaStream_t st) {
   a.num_kb = p.size_k / kStageK;
   const int m_tiles = (p.size_m + BM - 1) / BM, n_tiles = (p.size_n + kTileN - 1) / kTileN;
   const int tiles = m_tiles * n_tiles;
-  const int target = (BM <= 32 ? 4 : 2) * kNumSMs;
+  const int target = (BM <= 32 ? 4 : 2) * num_sms();
   int splits = tiles >= target ? 1 : target / tiles;
   if (splits > a.num_kb / 4) splits = a.num_kb / 4;
   const int64_t per = (int64_t)p.size_m * p.size_n * 4;
@@ -386,14 +386,19 @@ int launch24(const b200_gptq_marlin_24_gemm_params& p, cudaStream_t st) {
   splits = (a.num_kb + a.kb_per_split - 1) / a.kb_per_split;
   a.partial = splits > 1 ? reinterpret_cast<float*>(p.splitk_ws) : nullptr;
   auto kern = marlin24_gemm_kernel<BM>;
-  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P::kBytes);
+  static size_t smem_configured[kMaxDevices] = {};
+  if (ensure_dyn_smem(kern, P::kBytes, smem_configured) != cudaSuccess) {
+    cudaGetLastError();
+    set_error("gptq_marlin_24_gemm: cannot reserve %d B of shared memory", (int)P::kBytes);
+    return B200_ECUDA;
+  }
   launch_pdl(kern, dim3(m_tiles, n_tiles, splits), dim3(kThreads), P::kBytes, st, tm_x, tm_w, tm_m, tm_s, a);
   rc = check_launch("gptq_marlin_24_gemm");
   if (rc != B200_OK) return rc;
   if (splits > 1) {
     const int64_t total = (int64_t)p.size_m * p.size_n;
     int blocks = (int)((total + 255) / 256);
-    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    if (blocks > num_sms() * 8) blocks = num_sms() * 8;
     splitk_sum24_kernel<<<blocks, 256, 0, st>>>((__half*)p.c, a.partial, total, splits);
     rc = check_launch("gptq_marlin_24_gemm split-K sum");
   }

@@ -724,10 +724,14 @@ inline int pick_splits(int m, int n, int num_kb, int64_t ws_bytes) {
   // the large tiles.  Split K until one resident wave covers the grid (never past it: a second,
   // partial wave costs more than idle SM slots).
   const int per_sm = bm <= 32 ? 4 : bm <= 64 ? 2 : 1;
-  const int target = per_sm * kNumSMs;
+  const int target = per_sm * num_sms();
   if (tiles >= target || tiles == 0) return 1;
   int splits = target / tiles;
-  if (const char* e = getenv("B200_MARLIN_SPLITS")) splits = atoi(e);  // tuning hook (benchmarks only)
+  {  // tuning hook (benchmarks only), read once per process
+    static int knob[2] = {0, 0};
+    const int v = env_int_once("B200_MARLIN_SPLITS", knob, 0);
+    if (v > 0) splits = v;
+  }
   if (splits > num_kb / 4) splits = num_kb / 4;
   const int64_t per = (int64_t)m * n * 4;
   if (ws_bytes >= 0 && per > 0 && splits > ws_bytes / per) splits = (int)(ws_bytes / per);
@@ -761,14 +765,19 @@ int launch(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t ld
   const int m_tiles = (p.size_m + BM - 1) / BM, n_tiles = (p.size_n + P::kCtaN - 1) / P::kCtaN;
   a.w_evict_first = (m_tiles == 1);
   auto kern = marlin_gemm_kernel<BITS, BM, NT, T, ACT>;
-  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P::kBytes);
+  static size_t smem_configured[kMaxDevices] = {};
+  if (ensure_dyn_smem(kern, P::kBytes, smem_configured) != cudaSuccess) {
+    cudaGetLastError();
+    set_error("gptq_marlin_gemm: cannot reserve %d B of shared memory", (int)P::kBytes);
+    return B200_ECUDA;
+  }
   kern<<<dim3(m_tiles, n_tiles, splits), kThreads, P::kBytes, st>>>(tm_x, tm_w, tm_s, a);
   rc = check_launch("gptq_marlin_gemm");
   if (rc != B200_OK) return rc;
   if (splits > 1) {
     const int64_t total = (int64_t)p.size_m * p.size_n;
     int blocks = (int)((total / 4 + 255) / 256);
-    if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
+    if (blocks > num_sms() * 4) blocks = num_sms() * 4;
     if (blocks < 1) blocks = 1;
     splitk_sum_kernel<T><<<blocks, 256, 0, st>>>((T*)p.c, a.partial, total, splits);
     rc = check_launch("gptq_marlin_gemm split-K sum");
@@ -822,7 +831,12 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   const int m_tiles = (p.size_m + BM - 1) / BM, n_tiles = (p.size_n + kTileN - 1) / kTileN;
   a.w_evict_first = (m_tiles == 1);
   auto kern = marlin_gemm_tmem_kernel<BITS, BM, T>;
-  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P::kBytes);
+  static size_t smem_configured[kMaxDevices] = {};
+  if (ensure_dyn_smem(kern, P::kBytes, smem_configured) != cudaSuccess) {
+    cudaGetLastError();
+    set_error("gptq_marlin_gemm: cannot reserve %d B of shared memory", (int)P::kBytes);
+    return B200_ECUDA;
+  }
   // tiny M: the last split to arrive reduces in-kernel; otherwise a grid-wide reduce kernel
   a.locks = (splits > 1 && m_tiles == 1 && p.size_m <= 4) ? p.workspace : nullptr;
   // Programmatic dependent launch: behind a short producer kernel (RMSNorm, SiLU*mul, the attention
@@ -851,7 +865,7 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   if (splits > 1 && a.locks == nullptr) {
     const int64_t total = (int64_t)p.size_m * p.size_n;
     int blocks = (int)((total / 4 + 255) / 256);
-    if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
+    if (blocks > num_sms() * 4) blocks = num_sms() * 4;
     if (blocks < 1) blocks = 1;
     cfg.gridDim = dim3(blocks);
     cfg.blockDim = dim3(256);

@@ -328,8 +328,9 @@ static int run_paged_attention(const b200_paged_attention_params* p, bool v2, cu
     int stages = (12 * 1024) / a.stage_bytes;
     if (stages < 2) stages = 2;
     if (stages > kAttnMaxStages) stages = kAttnMaxStages;
-    if (const char* ev = getenv("B200_ATTN_STAGES")) {  // tuning knob (bench sweeps)
-      const int v = atoi(ev);
+    {  // tuning knob (bench sweeps), read once per process
+      static int knob[2] = {0, 0};
+      const int v = env_int_once("B200_ATTN_STAGES", knob, 0);
       if (v >= 2 && v <= kAttnMaxStages) stages = v;
     }
     while (stages * a.stage_bytes < merge_bytes) ++stages;

@@ -525,16 +525,12 @@ __global__ void __launch_bounds__(kAttnThreads)
 template <typename T, int KV, int NT, int HMAX, bool FAST>
 static int launch_one(const AttnArgs& a, dim3 grid, size_t smem, cudaStream_t stream) {
   auto kern = paged_attn_mma_kernel<T, KV, NT, HMAX, FAST>;
-  static size_t configured = 0;  // per instantiation; grows monotonically
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) {
-      cudaGetLastError();
-      set_error("paged_attention: cannot reserve %zu B of shared memory: %s", smem,
-                cudaGetErrorString(e));
-      return B200_ECUDA;
-    }
-    configured = smem;
+  static size_t configured[kMaxDevices] = {};  // per instantiation and device; grows monotonically
+  cudaError_t e = ensure_dyn_smem(kern, smem, configured);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    set_error("paged_attention: cannot reserve %zu B of shared memory: %s", smem, cudaGetErrorString(e));
+    return B200_ECUDA;
   }
   launch_pdl(kern, grid, dim3(kAttnThreads), smem, stream, a);
   return check_launch("paged_attention");

@@ -159,7 +159,7 @@ template <typename T>
 int launch_fp8(uint8_t* out, const void* in, float* scale, int64_t n, bool dynamic, cudaStream_t st) {
   if (n == 0) return B200_OK;
   int64_t want = (n + 512 * 8 - 1) / (512 * 8);
-  int grid = (int)(want < 1 ? 1 : (want > kNumSMs * 4 ? kNumSMs * 4 : want));
+  int grid = (int)(want < 1 ? 1 : (want > num_sms() * 4 ? num_sms() * 4 : want));
   if (dynamic) fp8_absmax_kernel<T><<<grid, 512, 0, st>>>(scale, (const T*)in, n);
   fp8_quant_kernel<T><<<grid, 512, 0, st>>>(out, (const T*)in, scale, n);
   return check_launch("scaled_fp8_quant");

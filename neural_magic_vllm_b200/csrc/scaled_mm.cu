@@ -240,8 +240,8 @@ int launch(const b200_scaled_mm_params& p, cudaStream_t st) {
   const int tiles = m_tiles * n_tiles;
   // split-K only to fill the machine for weight streaming; each split keeps >= 4 k-blocks
   int splits = 1;
-  if (p.workspace != nullptr && tiles < kNumSMs) {
-    splits = (2 * kNumSMs + tiles - 1) / tiles / 1;
+  if (p.workspace != nullptr && tiles < num_sms()) {
+    splits = (2 * num_sms() + tiles - 1) / tiles / 1;
     if (splits > a.num_kb / 4) splits = a.num_kb / 4;
     const int64_t per_split = (int64_t)p.m * p.n * 4;
     if (per_split > 0 && splits > p.workspace_bytes / per_split) splits = (int)(p.workspace_bytes / per_split);
@@ -253,10 +253,11 @@ int launch(const b200_scaled_mm_params& p, cudaStream_t st) {
   a.partial = splits > 1 ? p.workspace : nullptr;
   a.w_evict_first = (m_tiles == 1);
   auto kern = scaled_mm_kernel<KIND, BM, OutT>;
-  static bool attr_set = false;  // per template instantiation
-  if (!attr_set) {
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes);
-    attr_set = true;
+  static size_t smem_configured[kMaxDevices] = {};  // per template instantiation, per device
+  if (ensure_dyn_smem(kern, S::kBytes, smem_configured) != cudaSuccess) {
+    cudaGetLastError();
+    set_error("scaled_mm: cannot reserve %d B of shared memory", (int)S::kBytes);
+    return B200_ECUDA;
   }
   dim3 grid(m_tiles, n_tiles, splits);
   launch_pdl(kern, grid, dim3(kThreads), S::kBytes, st, tm_w, tm_x, a);
@@ -265,7 +266,7 @@ int launch(const b200_scaled_mm_params& p, cudaStream_t st) {
   if (splits > 1) {
     const int64_t total = (int64_t)p.m * p.n;
     int blocks = (int)((total + 255) / 256);
-    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    if (blocks > num_sms() * 8) blocks = num_sms() * 8;
     splitk_reduce_kernel<KIND == KIND_I8, OutT><<<blocks, 256, 0, st>>>(
         (OutT*)p.out, (const uint32_t*)p.workspace, p.a_scales, p.b_scales, (const OutT*)p.bias, p.m,
         p.n, p.ldc, splits, a.a_scales_per_token, a.b_scales_per_channel);
@@ -296,8 +297,8 @@ int64_t b200_scaled_mm_workspace_bytes(int32_t m, int32_t n, int32_t k) {
   // enough for the split-K partials of the weight-streaming regime; 0 when the grid is full
   const int bm = m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : m <= 128 ? 128 : 256;
   const int tiles = ((m + bm - 1) / bm) * ((n + 127) / 128);
-  if (tiles >= b200::kNumSMs || tiles == 0) return 0;
-  int splits = (2 * b200::kNumSMs + tiles - 1) / tiles;
+  if (tiles >= b200::num_sms() || tiles == 0) return 0;
+  int splits = (2 * b200::num_sms() + tiles - 1) / tiles;
   const int num_kb = (k + 127) / 128;
   if (splits > num_kb / 4) splits = num_kb / 4;
   if (splits <= 1) return 0;

@@ -307,13 +307,11 @@ void convert_fp8(Tensor& dst_cache, Tensor& src_cache, double scale, const std::
   const at::cuda::OptionalCUDAGuard guard(sd);
   B200_TCHECK(src_cache.is_contiguous() && dst_cache.is_contiguous(), "caches must be contiguous");
   B200_TCHECK(src_cache.numel() == dst_cache.numel(), "src and dst sizes differ");
-  int kv;
-  if (kv_cache_dtype == "auto") {
-    kv = B200_KV_FP8_E4M3;  // cache_kernels.cu:359-371: "auto" converts with the e4m3 routines
-  } else {
-    kv = kv_dtype_of(kv_cache_dtype);
-    B200_TCHECK(kv != B200_KV_AUTO, "Unsupported data type: ", kv_cache_dtype);
-  }
+  // cache_kernels.cu:372-388: only "fp8" / "fp8_e4m3" convert.  "fp8_e5m2" (and anything else) is a
+  // host-side TORCH_CHECK(false) there; "auto" reaches `assert(false)` in device code
+  // (quant_utils.cuh:513-523, kAuto) -- an error either way, raised here on the host.
+  B200_TCHECK(kv_cache_dtype == "fp8" || kv_cache_dtype == "fp8_e4m3", "Unsupported data type: ", kv_cache_dtype);
+  const int kv = B200_KV_FP8_E4M3;
   const bool to_fp8 = dst_cache.scalar_type() == at::ScalarType::Byte;
   const Tensor& wide = to_fp8 ? src_cache : dst_cache;
   B200_TCHECK((to_fp8 ? src_cache : dst_cache).scalar_type() != at::ScalarType::Byte &&

@@ -15,10 +15,29 @@ namespace b200 {
 namespace umma {
 
 // ---- bounded mbarrier wait: a protocol bug traps instead of hanging the GPU ----------------------
+// The bound is WALL TIME (globaltimer), not a spin count: under programmatic dependent launch a
+// GEMM CTA can be resident -- its MMA / dequant warps already waiting here -- while its predecessor
+// (e.g. a cross-GPU all-reduce polling a peer that is seconds late: first graph replay, a stalled
+// host) is still running.  kMbarTimeoutNs is longer than any skew the all-reduce itself tolerates.
+constexpr uint64_t kMbarTimeoutNs = 120ull * 1000ull * 1000ull * 1000ull;
+__device__ __forceinline__ uint64_t global_timer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
+  // try_wait itself suspends the thread for a HW-defined interval; the clock is read only once
+  // every 4096 failed probes
   uint32_t spins = 0;
+  uint64_t t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 22)) __trap();
+    if ((++spins & 0xfffu) == 0) {
+      const uint64_t t = global_timer_ns();
+      if (t0 == 0)
+        t0 = t;
+      else if (t - t0 > kMbarTimeoutNs)
+        __trap();
+    }
   }
 }
 

@@ -23,6 +23,14 @@ def get_pack_factor(num_bits: int) -> int:  # quant_utils.py:9-11
     return 32 // num_bits
 
 
+def _wrap_i32(x: torch.Tensor) -> torch.Tensor:
+    """int64 holding a uint32 bit pattern -> the int32 with the same 32 bits (what the reference's
+    numpy ``astype(np.int32)`` does).  Every function below is plain torch and runs on whatever
+    device its input lives on, so full-size shapes can be quantised on the GPU by the tests."""
+    x = x & 0xFFFFFFFF
+    return torch.where(x >= 2 ** 31, x - 2 ** 32, x).to(torch.int32)
+
+
 # ------------------------------------------------------------------------------------------
 # quantize_weights (quant_utils.py:41-110): symmetric per-group quantisation, zero point 2^(b-1)
 # ------------------------------------------------------------------------------------------
@@ -46,12 +54,12 @@ def quantize_weights(w: torch.Tensor, num_bits: int, group_size: int, act_order:
             return t.reshape(group_size, -1, size_n).permute(1, 0, 2).reshape(size_k, size_n).contiguous()
         q, w_ref = back(q), back(w_ref)
     s = s.reshape(-1, size_n).contiguous()
-    g_idx = torch.empty(0, dtype=torch.int32)
-    rand_perm = torch.empty(0, dtype=torch.int64)
+    g_idx = torch.empty(0, dtype=torch.int32, device=w.device)
+    rand_perm = torch.empty(0, dtype=torch.int64, device=w.device)
     if act_order:  # permute_rows (quant_utils.py:14-38)
         assert group_size < size_k
-        g_idx = (torch.arange(size_k) // group_size).to(torch.int32)
-        rand_perm = torch.randperm(size_k, generator=generator)
+        g_idx = (torch.arange(size_k, device=w.device) // group_size).to(torch.int32)
+        rand_perm = torch.randperm(size_k, generator=generator).to(w.device)
         g_idx = g_idx[rand_perm].contiguous()
         q = q[rand_perm].contiguous()
         w_ref = w_ref[rand_perm].contiguous()
@@ -66,23 +74,23 @@ def sort_weights(q_w: torch.Tensor, g_idx: torch.Tensor):  # quant_utils.py:113-
 def gptq_pack(q_w: torch.Tensor, num_bits: int, size_k: int, size_n: int) -> torch.Tensor:
     """[K, N] ints -> [K/pack, N] int32, packed along K (quant_utils.py:129-152)."""
     pack = get_pack_factor(num_bits)
-    q = q_w.numpy().astype(np.uint32)
-    res = np.zeros((size_k // pack, size_n), dtype=np.uint32)
+    q = q_w.to(torch.int64)
+    res = torch.zeros((size_k // pack, size_n), dtype=torch.int64, device=q_w.device)
     for i in range(pack):
         res |= q[i::pack, :] << (num_bits * i)
-    return torch.from_numpy(res.astype(np.int32))
+    return _wrap_i32(res)
 
 
 def gptq_unpack(packed: torch.Tensor, num_bits: int) -> torch.Tensor:
     """inverse of gptq_pack: [K/pack, N] int32 -> [K, N] int32."""
     pack = get_pack_factor(num_bits)
-    p = packed.numpy().astype(np.uint32)
+    p = packed.to(torch.int64) & 0xFFFFFFFF
     k = p.shape[0] * pack
-    out = np.zeros((k, p.shape[1]), dtype=np.int32)
+    out = torch.zeros((k, p.shape[1]), dtype=torch.int32, device=packed.device)
     mask = (1 << num_bits) - 1
     for i in range(pack):
-        out[i::pack, :] = (p >> (num_bits * i)) & mask
-    return torch.from_numpy(out)
+        out[i::pack, :] = ((p >> (num_bits * i)) & mask).to(torch.int32)
+    return out
 
 
 # ------------------------------------------------------------------------------------------
@@ -109,17 +117,17 @@ def get_perms(num_bits: int):
 def marlin_permute_weights(q_w, size_k, size_n, perm, tile=MARLIN_TILE):  # marlin_utils.py:25-37
     q_w = q_w.reshape(size_k // tile, tile, size_n // tile, tile).permute(0, 2, 1, 3)
     q_w = q_w.reshape(size_k // tile, size_n * tile)
-    return q_w.reshape(-1, perm.numel())[:, perm].reshape(q_w.shape)
+    return q_w.reshape(-1, perm.numel())[:, perm.to(q_w.device)].reshape(q_w.shape)
 
 
 def marlin_weights(q_w, size_k, size_n, num_bits, perm):  # marlin_utils.py:40-58
     q_w = marlin_permute_weights(q_w, size_k, size_n, perm)
     pack = get_pack_factor(num_bits)
-    q = q_w.numpy().astype(np.uint32)
-    packed = np.zeros((q.shape[0], q.shape[1] // pack), dtype=np.uint32)
+    q = q_w.to(torch.int64)
+    packed = torch.zeros((q.shape[0], q.shape[1] // pack), dtype=torch.int64, device=q_w.device)
     for i in range(pack):
         packed |= q[:, i::pack] << (num_bits * i)
-    return torch.from_numpy(packed.astype(np.int32))
+    return _wrap_i32(packed)
 
 
 def marlin_permute_scales(s, size_k, size_n, group_size, scale_perm, scale_perm_single):
@@ -136,7 +144,7 @@ def marlin_quantize(w, num_bits, group_size, act_order, generator=None):  # marl
     if group_size == -1:
         group_size = size_k
     w_ref, q_w, s, g_idx, rand_perm = quantize_weights(w, num_bits, group_size, act_order, generator)
-    sort_indices = torch.empty(0, dtype=torch.int32)
+    sort_indices = torch.empty(0, dtype=torch.int32, device=w.device)
     if act_order:
         q_w, g_idx, sort_indices = sort_weights(q_w, g_idx)
     perm, sp, sps = get_perms(num_bits)
@@ -149,15 +157,15 @@ def marlin_unpack(marlin_q_w: torch.Tensor, size_k: int, size_n: int, num_bits: 
     """inverse of marlin_weights: Marlin tiles [K/16, N*16/pack] int32 -> [K, N] ints."""
     perm, _, _ = get_perms(num_bits)
     pack = get_pack_factor(num_bits)
-    p = marlin_q_w.numpy().astype(np.uint32)
-    q = np.zeros((p.shape[0], p.shape[1] * pack), dtype=np.int32)
+    p = marlin_q_w.to(torch.int64) & 0xFFFFFFFF
+    q = torch.zeros((p.shape[0], p.shape[1] * pack), dtype=torch.int32, device=marlin_q_w.device)
     mask = (1 << num_bits) - 1
     for i in range(pack):
-        q[:, i::pack] = (p >> (num_bits * i)) & mask
-    q = torch.from_numpy(q).reshape(-1, perm.numel())
+        q[:, i::pack] = ((p >> (num_bits * i)) & mask).to(torch.int32)
+    q = q.reshape(-1, perm.numel())
     inv = torch.empty_like(perm)
     inv[perm] = torch.arange(perm.numel())
-    q = q[:, inv].reshape(size_k // 16, size_n * 16)
+    q = q[:, inv.to(q.device)].reshape(size_k // 16, size_n * 16)
     q = q.reshape(size_k // 16, size_n // 16, 16, 16).permute(0, 2, 1, 3).reshape(size_k, size_n)
     return q.contiguous()
 
@@ -206,10 +214,10 @@ def inject_24(w: torch.Tensor):  # marlin_utils.py:110-116 (sparsity runs along 
     return (mask * w).contiguous(), mask.contiguous()
 
 
-def _meta_scatter_offsets(m: int, meta_ncols: int) -> torch.Tensor:
+def _meta_scatter_offsets(m: int, meta_ncols: int, device=None) -> torch.Tensor:
     """int16-metadata reordering of the CUTLASS sparse GEMM (format_24.py:22-49)."""
-    r = torch.arange(m)[:, None].repeat(1, meta_ncols)
-    c = torch.arange(meta_ncols).repeat(m, 1)
+    r = torch.arange(m, device=device)[:, None].repeat(1, meta_ncols)
+    c = torch.arange(meta_ncols, device=device).repeat(m, 1)
     gx, gy = 64, 32
     r = r // gx * gx + (r % 2) * 2 + (r % 8) // 4 + ((r % gy) % 4) // 2 * 32 + ((r % gx) // 8) * 4
     tr = ((r % 2 == 0) & (c % 2 == 1)).to(torch.int8)
@@ -235,7 +243,7 @@ def compress_24(dense: torch.Tensor):
     meta4 = (idx0 | (idx1 << 2)).reshape(-1, k // 16, 4).to(torch.int16)
     meta = meta4[:, :, 0] | (meta4[:, :, 1] << 4) | (meta4[:, :, 2] << 8) | (meta4[:, :, 3] << 12)
     out = meta.new_empty(m * (k // 16))
-    out.scatter_(0, _meta_scatter_offsets(m, k // 16), meta.reshape(-1))
+    out.scatter_(0, _meta_scatter_offsets(m, k // 16, dense.device), meta.reshape(-1))
     return sparse, out.reshape(m, k // 16)
 
 
@@ -243,11 +251,11 @@ def decompress_24(sparse: torch.Tensor, meta_reordered: torch.Tensor) -> torch.T
     """inverse of compress_24 (sparse_semi_structured_to_dense_cutlass, format_24.py:180-275)."""
     m, kh = sparse.shape
     ncols = meta_reordered.shape[1]
-    meta = torch.gather(meta_reordered.reshape(-1), 0, _meta_scatter_offsets(m, ncols)).reshape(m, ncols)
+    meta = torch.gather(meta_reordered.reshape(-1), 0, _meta_scatter_offsets(m, ncols, sparse.device)).reshape(m, ncols)
     meta = meta.to(torch.int32) & 0xFFFF
     idx = torch.stack([(meta >> (2 * i)) & 3 for i in range(8)], dim=-1).reshape(-1)  # [m*kh]
-    base = (torch.arange(m * kh // 2) * 4).reshape(-1, 1).repeat(1, 2).reshape(-1)
-    dense = torch.zeros(m * 2 * kh, dtype=sparse.dtype)
+    base = (torch.arange(m * kh // 2, device=sparse.device) * 4).reshape(-1, 1).repeat(1, 2).reshape(-1)
+    dense = torch.zeros(m * 2 * kh, dtype=sparse.dtype, device=sparse.device)
     dense.scatter_(0, (idx.long() + base), sparse.reshape(-1))
     return dense.reshape(m, 2 * kh)
 

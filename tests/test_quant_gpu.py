@@ -170,6 +170,61 @@ def test_dequant_golden(ops):
         assert torch.equal(out.cpu(), torch.from_numpy(g[key + "_w_ref"])), key
 
 
+def _identity_gemm(ops, mq, ms, k, n, bits, dtype, rows_per_call):
+    """gptq_marlin_gemm with a = slices of I_K: the GEMM's OWN dequant path (scale fetch, register
+    order, tcgen05.st lane map / stmatrix swizzle, MMA operand layout) writes out the dequantised
+    weight.  One non-zero product per output, fp32 accumulate, one rounding of an exactly
+    representable value: the result must equal w_ref bit for bit."""
+    eye = torch.eye(k, dtype=dtype, device=DEV)
+    e = torch.empty(0, dtype=torch.int32, device=DEV)
+    out = torch.empty(k, n, dtype=dtype, device=DEV)
+    for r0 in range(0, k, rows_per_call):
+        a = eye[r0:r0 + rows_per_call].contiguous()
+        out[r0:r0 + rows_per_call] = ops.gptq_marlin_gemm(a, mq, ms, e, e, _ws(n), bits, a.shape[0], n, k, True)
+    return out
+
+
+@pytest.mark.parametrize("rows_per_call", [1, 16, 32, 64, 128, 256])
+def test_marlin_gemm_identity_golden_exact(ops, rows_per_call):
+    """rows_per_call <= 64 runs marlin_gemm_tmem_kernel (BM 16/32/64; group sizes >= 64), 128 / 256
+    the shared-memory kernel (BM 128/256, NT 2); group 32 always takes the shared-memory kernel."""
+    g = np.load(os.path.join(GOLD, "marlin_dense.npz"))
+    n_checked = 0
+    for key in sorted({k[:-len("_marlin_q")] for k in g.files if k.endswith("_marlin_q")}):
+        if key.endswith("_a1"):
+            continue
+        parts = key.split("_")
+        k, n, bits = int(parts[1][1:]), int(parts[2][1:]), int(parts[3][1:])
+        mq = torch.from_numpy(g[key + "_marlin_q"]).to(DEV)
+        ms = torch.from_numpy(g[key + "_marlin_s"]).to(DEV)
+        out = _identity_gemm(ops, mq, ms, k, n, bits, torch.half, min(rows_per_call, k))
+        assert torch.equal(out.cpu(), torch.from_numpy(g[key + "_w_ref"])), key
+        n_checked += 1
+    assert n_checked >= 5
+
+
+@pytest.mark.parametrize("rows_per_call", [8, 64, 256])
+@pytest.mark.parametrize("bits", [4, 8])
+@pytest.mark.parametrize("group", [-1, 32, 64, 128])
+@pytest.mark.parametrize("dtype", [torch.half, torch.bfloat16])
+def test_marlin_gemm_identity_exact(ops, rows_per_call, bits, group, dtype):
+    """same, on a shape with several n tiles, a ragged last n tile (192 = 128 + 64), several k
+    stages and groups, both dtypes -- long enough (k = 512) that the stage ring wraps."""
+    torch.manual_seed(5)
+    k, n = 512, 192
+    w = torch.randn(k, n, dtype=torch.half, device=DEV)
+    gs = k if group == -1 else group
+    _, q_w, s, _, _ = qr.quantize_weights(w, bits, gs, False)
+    s = s.to(dtype)
+    zp = 1 << (bits - 1)
+    w_ref = ((q_w - zp).float().view(k // gs, gs, n) * s.float()[:, None, :]).view(k, n).to(dtype)
+    perm, sp, sps = qr.get_perms(bits)
+    mq = qr.marlin_weights(q_w, k, n, bits, perm)
+    ms = qr.marlin_permute_scales(s, k, n, gs, sp, sps)
+    out = _identity_gemm(ops, mq, ms, k, n, bits, dtype, rows_per_call)
+    assert torch.equal(out.view(torch.int16), w_ref.view(torch.int16))
+
+
 # ------------------------------------------------------------------------------------------
 # cutlass_scaled_mm (test_cutlass.py:52-321)
 # ------------------------------------------------------------------------------------------
