@@ -1,19 +1,35 @@
 #!/usr/bin/env python
-"""Headline benchmark: paged_attention_v2 at the Llama-3-8B decode shape (BASELINE.json configs[1]).
+"""Headline benchmark: Llama-3-8B W4A16 (gptq_marlin g128) decode tokens/s at TP = N (BASELINE.json
+configs[2], metric (i)), with the configs[1] paged_attention_v2 microbench (metric (ii), fp16 and
+fp8-e4m3 KV) nested in the same JSON line.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--kv fp16|fp8] [--impl b200|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
 
-One "step" = one pass of the hot path over one batch: a `paged_attention_v2` call (split-KV
-kernel + reduce) on 64 sequences x 4096 context, 32 query / 8 kv heads, head 128, block 16.
-Prints ONE JSON line (contract in DESIGN.md section 6):
-  value    whole-job algorithmic HBM GB/s, inputs resident in HBM, device-timed (CUDA events)
-  e2e      same metric through the public op surface with HOST step inputs: per step
-           H2D(query, block_tables, seq_lens from pinned memory) + op + D2H(out)
-  roofline achieved GB/s of the op vs the measured HBM copy peak (MEASURED_PEAKS.json)
-  cpu_baseline  the reference's own CPU kernel (oracle/_ref, csrc/cpu/attention.cpp) on host cores
-`--impl reference` times only the reference CPU kernel on the same config.
-N>1 (torchrun): every rank runs the same per-GPU workload on its own batch (the path shards by
-sequence / head with no collective): "scaling": "weak".
+One "step" = one decode step of the whole model over one batch (headline: 64 sequences at context
+1024): embedding gather, 32 x [RMSNorm, qkv gptq_marlin_gemm, rotary + reshape_and_cache,
+paged_attention, o gptq_marlin_gemm, (all-reduce +) add + RMSNorm, gate_up gptq_marlin_gemm,
+SiLU*mul, down gptq_marlin_gemm, (all-reduce +) add + RMSNorm], fp16 lm_head, greedy sampling --
+replayed from one CUDA graph, as the reference replays decode (worker/model_runner.py).
+N > 1 is tensor parallel: rank r owns q/kv heads and the column shards of
+qkv / gate_up and the K shards of o / down; the two row-parallel partial sums per layer
+(linear.py:792-793) go through this repo's one-shot NVLink all-reduce (fused with add + RMSNorm
+where the message qualifies) or NCCL above its size limit.  "scaling": "strong".
+
+ONE JSON line (contract in DESIGN.md section 6):
+  value      whole-job tokens/s at batch 64, inputs resident in HBM, device-timed (CUDA events)
+  e2e        same, through the graph with HOST step inputs: per step H2D(tokens, positions,
+             slot_mapping, block_tables, seq_lens from pinned memory) + step + D2H(sampled ids)
+  roofline   (weight + KV + lm_head bytes per GPU) / step time vs the measured HBM copy peak,
+             plus the dominant kernel (gate_up gptq_marlin_gemm) timed alone, live
+  batches    tokens/s at batch 1 and 256 as well
+  attention  configs[1]: paged_attention_v2 64 x 4096, fp16 and fp8 KV, GB/s + roofline each
+  checks     output checked against the oracle once, outside the timed regions; at N > 1 the
+             all-reduce bit-identity check and a TP-N vs TP-1 hidden-state comparison
+  cpu_baseline  the reference's CPU path for the same step on the host cores (N = 1 only)
+`--impl reference` times only that CPU path (compiled csrc/cpu attention + cache ops, torch
+dequant-matmul linears) on a bounded sample of the same step.
 """
 from __future__ import annotations
 
@@ -28,28 +44,28 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+HEADLINE_BATCH, EXTRA_BATCHES, DECODE_CTX = 64, (1, 256), 1024
+# configs[1] attention microbench
 NUM_SEQS, NUM_HEADS, NUM_KV_HEADS, HEAD, BLOCK, CTX = 64, 32, 8, 128, 16, 4096
 PARTITION = 512
+METRIC = "decode tokens/s Llama-3-8B W4A16 gptq_marlin g128 (whole job at TP=n_gpus; /n_gpus = per GPU)"
 
 
-def algorithmic_bytes(kv_bytes_per_elem: int) -> int:
+def attention_bytes(kv_bytes_per_elem: int) -> int:
     """KV read once + q + out + block_tables + seq_lens."""
     kv = 2 * NUM_SEQS * CTX * NUM_KV_HEADS * HEAD * kv_bytes_per_elem
     q = NUM_SEQS * NUM_HEADS * HEAD * 2
-    out = q
-    bt = NUM_SEQS * (CTX // BLOCK) * 4
-    sl = NUM_SEQS * 4
-    return kv + q + out + bt + sl
+    return kv + 2 * q + NUM_SEQS * (CTX // BLOCK) * 4 + NUM_SEQS * 4
 
 
 def measured_peak_hbm():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         try:
-            return float(json.load(open(p))["hbm_gbs"]), "measured"
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
         except Exception:
             pass
-    return 6650.0, "fallback"
+    return 6650.0, "fallback (B200_PROFILING.md)"
 
 
 class ClockSampler:
@@ -78,7 +94,7 @@ class ClockSampler:
         except subprocess.TimeoutExpired:
             self.proc.kill()
             out, _ = self.proc.communicate()
-        sm, mx, reasons = [], [], set()
+        sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in out.strip().splitlines():
             f = [x.strip() for x in line.split(",")]
@@ -87,53 +103,307 @@ class ClockSampler:
             try:
                 sm.append(float(f[1]))
                 mx.append(float(f[2]))
+                pw.append(float(f[3]))
             except ValueError:
                 continue
             for n, v in zip(names, f[4:8]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
-        return {"sm_mhz": statistics.median(sm) if sm else None,
+        # "under load" = samples drawing well above idle power
+        load = [s for s, p in zip(sm, pw) if p > 300.0] or sm
+        return {"sm_mhz": statistics.median(load) if load else None,
                 "sm_max_mhz": max(mx) if mx else None, "samples": len(sm),
-                "reasons": sorted(reasons)}
+                "samples_under_load": len(load), "reasons": sorted(reasons)}
 
 
-def cpu_reference_run(steps: int, warmup: int, seqs: int):
-    """Times the reference's CPU paged_attention_v2 (csrc/cpu/attention.cpp:739) on bf16
-    (the CPU backend has no fp16: cpu_types_x86.hpp:16-18) for `seqs` sequences of the C2 shape.
-    Returns (GB/s algorithmic, seconds per call, cores, sample description)."""
-    import torch
-    from oracle import ref_cpu
-    if not ref_cpu.available():
-        return None, None, 0, ref_cpu.why_unavailable()
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
+def cpu_reference(steps: int, warmup: int):
+    """The CPU arm (oracle/cpu_decode_ref.py): bounded sample of the headline step."""
+    from oracle import cpu_decode_ref
+    return cpu_decode_ref.run(batch=HEADLINE_BATCH, ctx=DECODE_CTX, sample_layers=2,
+                              steps=max(1, min(steps, 3)), warmup=max(1, min(warmup, 1)))
+
+
+class CountingOps:
+    """Proxy over the op surface that counts kernel launches of THIS repo's ops during one eager
+    step (lower bound: a split-K GEMM with its reduce kernel is counted once)."""
+    LAUNCHES = {"paged_attention_v2": 2}
+
+    def __init__(self, ops):
+        self._ops, self.count = ops, 0
+
+    def __getattr__(self, name):
+        fn = getattr(self._ops, name)
+
+        def wrapped(*a, **k):
+            self.count += self.LAUNCHES.get(name, 1)
+            return fn(*a, **k)
+        return wrapped
+
+
+def graph_step(dec, torch):
+    """Warm the step eagerly, then capture it into one CUDA graph; -> (graph, replay)."""
+    with torch.no_grad():
+        for _ in range(2):
+            dec.step()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            dec.step()
+    return g
+
+
+def time_steps(run, steps, warmup, barrier, torch):
+    """W untimed + exactly K timed calls of `run`, CUDA events on the launching stream, barrier +
+    synchronize on both sides.  -> ms per step on this rank."""
+    for _ in range(warmup):
+        run()
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(steps):
+        run()
+    ev1.record()
+    barrier()
+    return ev0.elapsed_time(ev1) / steps
+
+
+def decode_bytes(dec, batch, ctx):
+    """Algorithmic HBM bytes of one decode step on ONE GPU: every packed
+    weight + scale of the rank's shards once, the rank's KV heads of every sequence once, the
+    rank's lm_head shard once.  Activations (batch x 4096 fp16 per op) are not counted."""
+    lin = dec.linear_bytes()
+    kv = 2 * batch * (ctx + 1) * dec.layers[0].kvh * HEAD * 2 * len(dec.layers)
+    head = dec.lm_head.numel() * 2 if dec.lm_head is not None else 0
+    return lin, kv, head
+
+
+def run_decode(ops, torch, dist, world, rank, car, batch, steps, warmup, barrier, e2e: bool):
+    """One batch size: build the TP shard of the decoder, capture, time.  -> dict."""
+    from benchmarks.decode_bench import Decoder
+    dec = Decoder(ops, world, rank, batch, DECODE_CTX, lm_head=True, glue="fused", car=car)
+    counter = CountingOps(ops)
+    dec.ops = counter
+    for L in dec.layers:
+        for lin in (L.qkv, L.o, L.gate_up, L.down):
+            lin.ops = counter
+    with torch.no_grad():
+        dec.step()
+    launches = counter.count
+    dec.ops = ops
+    for L in dec.layers:
+        for lin in (L.qkv, L.o, L.gate_up, L.down):
+            lin.ops = ops
+    g = graph_step(dec, torch)
+    ms = time_steps(g.replay, steps, warmup, barrier, torch)
+    lin, kv, head = decode_bytes(dec, batch, DECODE_CTX)
+    res = {"batch": batch, "ms_per_step": ms, "launches_per_step": launches,
+           "bytes_per_gpu": lin + kv + head, "linear_bytes_per_gpu": lin, "kv_bytes_per_gpu": kv,
+           "lm_head_bytes_per_gpu": head,
+           "attention_op": "paged_attention_v1" if dec.use_v1 else "paged_attention_v2"}
+    if e2e:
+        # host-resident step inputs (what the reference's model_runner prepares every step:
+        # worker/model_runner.py _prepare_model_input) in pinned memory; sampled ids back to host
+        host = {k: getattr(dec, k).cpu().pin_memory()
+                for k in ("tokens", "positions", "slots", "block_tables", "seq_lens")}
+        next_h = torch.empty(batch, dtype=torch.int64).pin_memory()
+        h2d = sum(t.numel() * t.element_size() for t in host.values())
+        d2h = next_h.numel() * 8
+        stream = torch.cuda.current_stream()
+
+        def e2e_step():
+            for k, t in host.items():
+                getattr(dec, k).copy_(t, non_blocking=True)
+            g.replay()
+            next_h.copy_(dec.next_tokens, non_blocking=True)
+            stream.synchronize()
+
+        for _ in range(3):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            e2e_step()
+        barrier()
+        res.update({"e2e_ms_per_step": (time.perf_counter() - t0) / steps * 1e3,
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h})
+    res["_dec"], res["_graph"] = dec, g
+    return res
+
+
+def run_attention(ops, torch, dev, fp8: bool, steps, warmup, barrier, peak):
+    """configs[1]: paged_attention_v2, 64 seqs x ctx 4096, 32 q / 8 kv heads, D 128, block 16, a
+    random permutation of 16384 distinct blocks (KV working set 1 GiB / 512 MiB > 126 MB L2).
+    The output of 2 sequences is checked against the oracle once, outside the timed region."""
+    from oracle import attention_ref as ar
+    kv_str, esz = ("fp8", 1) if fp8 else ("auto", 2)
+    x = 16 // esz
     s = HEAD ** -0.5
-    nb = seqs * (CTX // BLOCK)
-    g = torch.Generator().manual_seed(0)
-    q = torch.empty(seqs, NUM_HEADS, HEAD, dtype=torch.bfloat16).uniform_(-s, s, generator=g)
-    kc = torch.empty(nb, NUM_KV_HEADS, HEAD // 8, BLOCK, 8, dtype=torch.bfloat16).uniform_(-s, s, generator=g)
-    vc = torch.empty(nb, NUM_KV_HEADS, HEAD, BLOCK, dtype=torch.bfloat16).uniform_(-s, s, generator=g)
-    bt = torch.randperm(nb, generator=g).to(torch.int32).view(seqs, CTX // BLOCK)
-    sl = torch.full((seqs,), CTX, dtype=torch.int32)
+    g = torch.Generator(device=dev).manual_seed(0)
+    nb = NUM_SEQS * CTX // BLOCK
+    q = torch.empty(NUM_SEQS, NUM_HEADS, HEAD, dtype=torch.float16, device=dev).uniform_(-s, s, generator=g)
+    kc = torch.empty(nb, NUM_KV_HEADS, HEAD // x, BLOCK, x, dtype=torch.float16, device=dev).uniform_(-s, s, generator=g)
+    vc = torch.empty(nb, NUM_KV_HEADS, HEAD, BLOCK, dtype=torch.float16, device=dev).uniform_(-s, s, generator=g)
+    if fp8:
+        kc8 = torch.empty(kc.shape, dtype=torch.uint8, device=dev)
+        vc8 = torch.empty(vc.shape, dtype=torch.uint8, device=dev)
+        ops.convert_fp8(kc8, kc, 1.0, "fp8")
+        ops.convert_fp8(vc8, vc, 1.0, "fp8")
+        kc, vc = kc8, vc8
+    bt = torch.randperm(nb, device=dev, generator=g).to(torch.int32).view(NUM_SEQS, CTX // BLOCK).contiguous()
+    sl = torch.full((NUM_SEQS,), CTX, dtype=torch.int32, device=dev)
     parts = CTX // PARTITION
     out = torch.empty_like(q)
-    es = torch.empty(seqs, NUM_HEADS, parts)
+    es = torch.empty(NUM_SEQS, NUM_HEADS, parts, dtype=torch.float32, device=dev)
     ml = torch.empty_like(es)
-    tmp = torch.empty(seqs, NUM_HEADS, parts, HEAD, dtype=torch.bfloat16)
+    tmp = torch.empty(NUM_SEQS, NUM_HEADS, parts, HEAD, dtype=torch.float16, device=dev)
 
-    def call():
-        ref_cpu.paged_attention_v2(out, es, ml, tmp, q, kc, vc, NUM_KV_HEADS, s, bt, sl, BLOCK, CTX)
+    def step():
+        ops.paged_attention_v2(out, es, ml, tmp, q, kc, vc, NUM_KV_HEADS, s, bt, sl, BLOCK, CTX,
+                               None, kv_str, 1.0)
 
-    for _ in range(max(warmup, 1)):
-        call()
+    ms = time_steps(step, steps, warmup, barrier, torch)
+    # oracle check (2 sequences; their blocks compacted into a small CPU cache)
+    sample = [0, NUM_SEQS - 1]
+    blocks = bt[sample].reshape(-1).long()
+    bt_s = torch.arange(len(sample) * (CTX // BLOCK), dtype=torch.int32).view(len(sample), -1)
+    ref = ar.paged_attention_ref(q[sample].cpu(), kc[blocks].cpu(), vc[blocks].cpu(), bt_s, sl[sample].cpu(),
+                                 s, None, kv_str, 1.0)
+    atol = 1e-2 if fp8 else 1e-3
+    torch.testing.assert_close(out[sample].cpu().float(), ref.float(), atol=atol, rtol=1e-2)
+    # end to end through the op with host step inputs
+    q_h, bt_h, sl_h = q.cpu().pin_memory(), bt.cpu().pin_memory(), sl.cpu().pin_memory()
+    out_h = torch.empty(out.shape, dtype=out.dtype).pin_memory()
+    stream = torch.cuda.current_stream()
+
+    def e2e_step():
+        q.copy_(q_h, non_blocking=True)
+        bt.copy_(bt_h, non_blocking=True)
+        sl.copy_(sl_h, non_blocking=True)
+        step()
+        out_h.copy_(out, non_blocking=True)
+        stream.synchronize()
+
+    for _ in range(3):
+        e2e_step()
     t0 = time.perf_counter()
     for _ in range(steps):
-        call()
-    dt = (time.perf_counter() - t0) / steps
-    nbytes = algorithmic_bytes(2) * seqs / NUM_SEQS
-    return nbytes / dt / 1e9, dt, cores, (
-        f"reference csrc/cpu paged_attention_v2, bf16 KV, {seqs} seqs x ctx {CTX} "
-        f"({nbytes / 2**20:.0f} MiB/call), {steps} calls")
+        e2e_step()
+    e2e_ms = (time.perf_counter() - t0) / steps * 1e3
+    nbytes = attention_bytes(esz)
+    gbs = nbytes / (ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get("paged_attention_v2_" + ("fp8" if fp8 else "fp16"), {}).get("bytes")
+    except Exception:
+        pass
+    return {"metric": "paged_attention_v2 algorithmic HBM GB/s (Llama-3-8B shape, batch 64, ctx 4096)",
+            "kv_cache": "fp8_e4m3" if fp8 else "fp16", "value": gbs, "unit": "GB/s", "ms_per_step": ms,
+            "steps": steps, "oracle_check": f"ok (2 sequences, rtol 1e-2 atol {atol})",
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                         "frac_of_8TBs_spec": gbs / 8000.0, "traffic": traffic,
+                         "algorithmic_bytes_per_launch": nbytes,
+                         "kernel": "paged_attn_mma_kernel (+ reduce kernel: duration is the whole op)"},
+            "e2e": {"value": nbytes / (e2e_ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": q_h.numel() * 2 + bt_h.numel() * 4 + sl_h.numel() * 4,
+                    "d2h_bytes_per_step": out_h.numel() * 2}}
+
+
+def time_dominant_kernel(dec, batch, torch, steps, peak):
+    """The kernel with the largest share of the headline step: the gate_up gptq_marlin_gemm
+    (marlin_gemm_tmem_kernel at M <= 64).  Timed alone with CUDA events, rotating over the 32
+    layers' weights (32 x 59 MB > L2) so that every launch streams its weights from HBM."""
+    x = torch.randn(batch, 4096, dtype=torch.half, device="cuda")
+    lins = [L.gate_up for L in dec.layers]
+    with torch.no_grad():
+        for lin in lins:
+            lin(x)
+        torch.cuda.synchronize()
+        reps = max(1, steps // 8)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for _ in range(reps):
+            for lin in lins:
+                lin(x)
+        ev1.record()
+        torch.cuda.synchronize()
+    us = ev0.elapsed_time(ev1) * 1e3 / (reps * len(lins))
+    lin = lins[0]
+    nbytes = lin.bytes() + batch * (lin.k + lin.n) * 2
+    gbs = nbytes / us / 1e3
+    return {"kernel": "gptq_marlin_gemm gate_up (marlin_gemm_tmem_kernel + split-K sum where split)",
+            "shape_mkn": [batch, lin.k, lin.n], "us_per_launch": us, "launches_timed": reps * len(lins),
+            "algorithmic_bytes_per_launch": nbytes, "achieved": gbs, "peak": peak, "unit": "GB/s",
+            "frac": gbs / peak, "share_of_step": None}
+
+
+def check_all_reduce(car, torch, dist, world, rank):
+    """One-shot all-reduce: bit-identical on every rank and equal to the fp32 sum of the ranks'
+    inputs rounded once (benchmarks/ar_check.py holds the full matrix of sizes / dtypes)."""
+    g = torch.Generator(device="cuda").manual_seed(100 + rank)
+    n_ok = 0
+    for n in (4096, 64 * 4096, 8):
+        for dtype in (torch.half, torch.bfloat16):
+            x = torch.randn(n, device="cuda", generator=g).to(dtype)
+            out = car.all_reduce(x)
+            gathered = [torch.empty_like(x) for _ in range(world)]
+            dist.all_gather(gathered, x)
+            acc = torch.zeros(n, device="cuda", dtype=torch.float32)
+            for t in gathered:
+                acc += t.float()
+            assert torch.equal(out, acc.to(dtype)), f"one-shot all-reduce mismatch n={n} {dtype}"
+            outs = [torch.empty_like(out) for _ in range(world)]
+            dist.all_gather(outs, out)
+            assert all(torch.equal(o, outs[0]) for o in outs), "ranks disagree"
+            n_ok += 1
+    return f"ok ({n_ok} size x dtype cases bit-exact vs the fp32 sum, identical on all ranks)"
+
+
+def check_tp_vs_tp1(ops, torch, world, rank, car):
+    """TP-N hidden state (2 layers, batch 64, through the fused all-reduce + add + RMSNorm) against
+    the same 2 layers at TP-1 computed locally from the same full weights."""
+    from benchmarks.decode_bench import Decoder
+    with torch.no_grad():
+        d_tp = Decoder(ops, world, rank, 64, 128, lm_head=False, car=car, num_layers=2)
+        h_tp = d_tp.step().float().clone()
+        del d_tp
+        d_1 = Decoder(ops, 1, 0, 64, 128, lm_head=False, car=None, num_layers=2)
+        h_1 = d_1.step().float().clone()
+        del d_1
+    torch.cuda.synchronize()
+    err = float((h_tp - h_1).abs().max() / h_1.abs().max())
+    assert err < 2e-2, f"TP-{world} hidden state differs from TP-1: rel-to-max error {err}"
+    return {"max_err_rel_to_max": err, "layers": 2, "batch": 64, "bound": 2e-2}
+
+
+def check_vs_reference_cuda(dec, batch, torch):
+    """gate_up gptq_marlin_gemm against the reference's OWN CUDA kernel (oracle/_ref/_C_refcuda.so,
+    recompiled for sm_100) on identical inputs; also times that kernel the same way as ours."""
+    try:
+        from oracle import ref_cuda
+        if not ref_cuda.available():
+            return {"unavailable": ref_cuda.why_unavailable()}
+    except Exception as e:  # the checker is optional on the bench path
+        return {"unavailable": repr(e)}
+    lins = [L.gate_up for L in dec.layers]
+    x = torch.randn(batch, 4096, dtype=torch.half, device="cuda")
+    with torch.no_grad():
+        ours = lins[0](x)
+        ws = torch.zeros(lins[0].n // 64 * 16, dtype=torch.int32, device="cuda")
+
+        def ref_call(lin):
+            return torch.ops._C_refcuda.gptq_marlin_gemm(x, lin.q, lin.s, lin.e, lin.e, ws, 4, batch, lin.n, lin.k, True)
+        ref = ref_call(lins[0])
+        torch.testing.assert_close(ours.float(), ref.float(), rtol=1e-2, atol=2e-3)
+        torch.cuda.synchronize()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for lin in lins:
+            ref_call(lin)
+        ev1.record()
+        torch.cuda.synchronize()
+    return {"gate_up_vs_reference_cuda": "ok (rtol 1e-2 atol 2e-3)",
+            "reference_cuda_us_per_launch": ev0.elapsed_time(ev1) * 1e3 / len(lins)}
 
 
 def main():
@@ -142,40 +412,40 @@ def main():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--kv", default="fp16", choices=["fp16", "fp8"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-attention", action="store_true")
+    ap.add_argument("--no-extra-batches", action="store_true")
+    ap.add_argument("--ar", choices=["one_shot", "nccl"], default="one_shot")
     ap.add_argument("--profile", action="store_true",
-                    help="ncu mode: warm-up + timed steps only (no e2e / clock soak / CPU baseline)")
+                    help="ncu mode: headline batch only, warm-up + timed steps, nothing else")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
-    config = {"workload": "paged_attention_v2 Llama-3-8B shape (configs[1])", "num_seqs": NUM_SEQS,
-              "ctx": CTX, "q_heads": NUM_HEADS, "kv_heads": NUM_KV_HEADS, "head_size": HEAD,
-              "block_size": BLOCK, "kv_cache": args.kv, "distinct_blocks": NUM_SEQS * CTX // BLOCK,
-              "l2": "inputs larger than L2 (KV working set 1 GiB fp16 / 512 MiB fp8 vs 126 MB L2)",
-              "parallelism": f"replica x{world} (independent batches, no collective)"}
-    metric = "paged_attention_v2 algorithmic HBM GB/s (Llama-3-8B shape, batch 64, ctx 4096)"
+    config = {"workload": "Llama-3-8B W4A16 gptq_marlin g128 decode step (configs[2]): 32 layers, hidden 4096, "
+                          "32 q / 8 kv heads, D 128, inter 14336, vocab 128256, fp16 lm_head, greedy sampling",
+              "batch": HEADLINE_BATCH, "ctx": DECODE_CTX, "block_size": BLOCK, "cuda_graph": True,
+              "parallelism": f"tp{world}" if world > 1 else "single GPU",
+              "l2": "inputs larger than L2 (weights + KV read per step: GBs vs 126 MB L2)",
+              "excluded": "scheduler, tokenizer"}
 
     if args.impl == "reference":
         if rank != 0:
             return
-        seqs = 16  # bounded sample: 256 MiB of bf16 KV per call
-        steps = max(1, min(args.steps, 20))
-        gbs, dt, cores, sample = cpu_reference_run(steps, min(args.warmup, 2), seqs)
-        if gbs is None:
-            print(json.dumps({"impl": "reference", "unavailable": sample}))
+        r = cpu_reference(args.steps, args.warmup)
+        if "unavailable" in r:
+            print(json.dumps({"impl": "reference", "unavailable": r["unavailable"]}))
             return
-        config["kv_cache"] = "bf16 (reference CPU backend has no fp16/fp8)"
+        config["parallelism"] = f"host CPU, {r['cores']} threads"
         print(json.dumps({
-            "impl": "reference", "metric": metric, "value": gbs, "unit": "GB/s", "n_gpus": args.gpus,
-            "steps": steps, "warmup": min(args.warmup, 2), "ms_per_step": dt * 1e3 * NUM_SEQS / seqs,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
-            "data": "synthetic", "config": config,
-            "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "reference",
-                             "sample": sample},
-            "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "impl": "reference", "metric": METRIC, "value": r["tokens_per_s"], "unit": "tokens/s",
+            "n_gpus": args.gpus, "steps": max(1, min(args.steps, 3)), "warmup": 1,
+            "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": r["matmul_dtype"] + " (bf16 KV)", "data": "synthetic", "config": config,
+            "cpu_baseline": {"value": r["tokens_per_s"], "unit": "tokens/s", "cores": r["cores"],
+                             "kind": "port", "sample": r["sample"]},
+            "e2e": {"value": r["tokens_per_s"], "unit": "tokens/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0},
             "gpu_launches": 0}))
         return
 
@@ -188,144 +458,123 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     import neural_magic_vllm_b200 as pkg
     ops = pkg.ops
-
-    fp8 = args.kv == "fp8"
-    kv_str = "fp8" if fp8 else "auto"
-    esz = 1 if fp8 else 2
-    x = 16 // esz
-    s = HEAD ** -0.5
-    torch.manual_seed(rank)
-    nb = NUM_SEQS * CTX // BLOCK
-    q = torch.empty(NUM_SEQS, NUM_HEADS, HEAD, dtype=torch.float16, device=dev).uniform_(-s, s)
-    kc = torch.empty(nb, NUM_KV_HEADS, HEAD // x, BLOCK, x, dtype=torch.float16, device=dev).uniform_(-s, s)
-    vc = torch.empty(nb, NUM_KV_HEADS, HEAD, BLOCK, dtype=torch.float16, device=dev).uniform_(-s, s)
-    if fp8:
-        kc8 = torch.empty(kc.shape, dtype=torch.uint8, device=dev)
-        vc8 = torch.empty(vc.shape, dtype=torch.uint8, device=dev)
-        ops.convert_fp8(kc8, kc, 1.0, "fp8")
-        ops.convert_fp8(vc8, vc, 1.0, "fp8")
-        kc, vc = kc8, vc8
-    bt = torch.randperm(nb, device=dev).to(torch.int32).view(NUM_SEQS, CTX // BLOCK).contiguous()
-    sl = torch.full((NUM_SEQS,), CTX, dtype=torch.int32, device=dev)
-    parts = CTX // PARTITION
-    out = torch.empty_like(q)
-    es = torch.empty(NUM_SEQS, NUM_HEADS, parts, dtype=torch.float32, device=dev)
-    ml = torch.empty_like(es)
-    tmp = torch.empty(NUM_SEQS, NUM_HEADS, parts, HEAD, dtype=torch.float16, device=dev)
-
-    def step():
-        ops.paged_attention_v2(out, es, ml, tmp, q, kc, vc, NUM_KV_HEADS, s, bt, sl, BLOCK, CTX,
-                               None, kv_str, 1.0)
+    warmup = max(args.warmup, 3)
+    peak, peak_kind = measured_peak_hbm()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(warmup):
-        step()
-    barrier()
+    car = None
+    checks = {}
+    if world > 1 and args.ar == "one_shot":
+        from neural_magic_vllm_b200.custom_all_reduce import CustomAllreduce
+        car = CustomAllreduce(None, local_rank)
+        if car.disabled:
+            car = None
+    if world > 1 and not args.profile:
+        if car is not None:
+            checks["ar_check"] = check_all_reduce(car, torch, dist, world, rank)
+        checks["tp_vs_tp1"] = check_tp_vs_tp1(ops, torch, world, rank, car)
+        barrier()
+
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    # the op is ~0.2 ms: repeat the timed block so the clock sampler sees the GPU under load
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    ev0.record()
-    for _ in range(args.steps):
-        step()
-    ev1.record()
-    barrier()
-    ms_total = ev0.elapsed_time(ev1)
-
+    head = run_decode(ops, torch, dist, world, rank, car, HEADLINE_BATCH, args.steps, warmup, barrier,
+                      e2e=not args.profile)
     if args.profile:
         if rank == 0:
             sampler.stop()
-            print(json.dumps({"profile_mode": True, "ms_per_step": ms_total / args.steps}))
+            print(json.dumps({"profile_mode": True, "ms_per_step": head["ms_per_step"]}))
         return
-
-    # ---- end to end: host step inputs -> device, op, result -> host ----
-    q_h = q.cpu().pin_memory()
-    bt_h = bt.cpu().pin_memory()
-    sl_h = sl.cpu().pin_memory()
-    out_h = torch.empty(out.shape, dtype=out.dtype).pin_memory()
-    h2d = q_h.numel() * 2 + bt_h.numel() * 4 + sl_h.numel() * 4
-    d2h = out_h.numel() * 2
-
-    def e2e_step():
-        q.copy_(q_h, non_blocking=True)
-        bt.copy_(bt_h, non_blocking=True)
-        sl.copy_(sl_h, non_blocking=True)
-        step()
-        out_h.copy_(out, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-
-    for _ in range(3):
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    # the timed regions are tens of milliseconds: keep the same kernel running for ~1.5 s so that
-    # the 100 ms nvidia-smi sampler sees the clocks under this load
+    dec = head.pop("_dec")
+    graph = head.pop("_graph")
+    dom = time_dominant_kernel(dec, HEADLINE_BATCH, torch, args.steps, peak)
+    if rank == 0:
+        checks.update(check_vs_reference_cuda(dec, HEADLINE_BATCH, torch))
+    # keep the headline graph replaying ~1.5 s so the 100 ms nvidia-smi sampler sees it under load
     t_soak = time.perf_counter()
     while time.perf_counter() - t_soak < 1.5:
-        for _ in range(50):
-            step()
+        for _ in range(20):
+            graph.replay()
         torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
     if clocks is not None:
-        clocks["window"] = "timed region + e2e region + 1.5 s continuation of the same op"
+        clocks["window"] = "timed region + e2e region + 1.5 s continuation of the headline step"
+    del dec, graph
+    torch.cuda.empty_cache()
 
-    t = torch.tensor([ms_total, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    extra = []
+    if not args.no_extra_batches:
+        for b in EXTRA_BATCHES:
+            r = run_decode(ops, torch, dist, world, rank, car, b, min(args.steps, 50), warmup, barrier, e2e=False)
+            r.pop("_dec"), r.pop("_graph")
+            extra.append(r)
+            torch.cuda.empty_cache()
+
+    attention = []
+    if not args.no_attention and rank == 0:
+        for fp8 in (False, True):
+            attention.append(run_attention(ops, torch, dev, fp8, min(args.steps, 100), warmup,
+                                           torch.cuda.synchronize, peak))
+            torch.cuda.empty_cache()
+    barrier()
+
+    keys = ["ms_per_step", "e2e_ms_per_step"]
+    t = torch.tensor([head[k] for k in keys] + [r["ms_per_step"] for r in extra], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, e2e_ms = float(t[0]), float(t[1])
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
-
-    nbytes = algorithmic_bytes(esz)
-    ms_step = ms_total / args.steps
-    value = nbytes * world / (ms_step * 1e-3) / 1e9
-    e2e_value = nbytes * world / (e2e_ms / args.steps * 1e-3) / 1e9
-    peak, peak_kind = measured_peak_hbm()
-    per_gpu = nbytes / (ms_step * 1e-3) / 1e9
-    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
-    # capture of this workload (profiles/traffic.json names the source file); null when there is none
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get("paged_attention_v2_" + ("fp8" if fp8 else "fp16"), {}).get("bytes")
-    except Exception:
-        traffic = None
-    line = {
-        "metric": metric, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
-        "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f16 (fp32 softmax/accumulate)" + (", fp8-e4m3 KV" if fp8 else ""),
-        "data": "synthetic", "config": config,
-        "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s",
-                     "frac": per_gpu / peak, "traffic": traffic, "peak_kind": f"of {peak_kind}",
-                     "frac_of_8TBs_spec": per_gpu / 8000.0,
-                     "kernel": "paged_attn_mma_kernel (+ reduce kernel: duration is the whole op)",
-                     "algorithmic_bytes_per_launch": nbytes},
-        "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / args.steps},
-        "gpu_launches": 2 * args.steps,
-        "tokens_attended_per_s": NUM_SEQS * CTX * world / (ms_step * 1e-3),
-        "clocks": clocks,
-    }
-    if not args.no_cpu_baseline and world >= 1:
-        gbs, dt, cores, sample = cpu_reference_run(3, 1, 8)
-        line["cpu_baseline"] = ({"value": gbs, "unit": "GB/s", "cores": cores, "kind": "reference",
-                                 "sample": sample} if gbs is not None else
-                                {"value": None, "unit": "GB/s", "cores": 0, "kind": "reference",
-                                 "sample": f"unavailable: {sample}"})
-    print(json.dumps(line))
+    vals = t.tolist()
+    head["ms_per_step"], head["e2e_ms_per_step"] = vals[0], vals[1]
+    for r, v in zip(extra, vals[2:]):
+        r["ms_per_step"] = v
+    if rank == 0:
+        ms = head["ms_per_step"]
+        per_gpu_gbs = head["bytes_per_gpu"] / (ms * 1e-3) / 1e9
+        dom["share_of_step"] = dom["us_per_launch"] * 32 / (ms * 1e3)
+        line = {
+            "metric": METRIC, "value": HEADLINE_BATCH / (ms * 1e-3), "unit": "tokens/s", "n_gpus": world,
+            "steps": args.steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "w4a16: int4 weights, f16 activations, fp32 accumulate",
+            "data": "synthetic: random-init packed int4 weights + scales, random KV, random token ids",
+            "config": config,
+            "tokens_per_s_per_gpu": HEADLINE_BATCH / (ms * 1e-3) / world,
+            "roofline": {"bound": "hbm", "achieved": per_gpu_gbs, "peak": peak, "unit": "GB/s",
+                         "frac": per_gpu_gbs / peak, "traffic": None, "peak_kind": peak_kind,
+                         "what": "whole decode step on one GPU: (packed weights + scales + KV + lm_head shard bytes) / step time",
+                         "algorithmic_bytes_per_step_per_gpu": head["bytes_per_gpu"],
+                         "linear_bytes": head["linear_bytes_per_gpu"], "kv_bytes": head["kv_bytes_per_gpu"],
+                         "lm_head_bytes": head["lm_head_bytes_per_gpu"], "dominant_kernel": dom},
+            "e2e": {"value": HEADLINE_BATCH / (head["e2e_ms_per_step"] * 1e-3), "unit": "tokens/s",
+                    "h2d_bytes_per_step": head["h2d_bytes_per_step"], "d2h_bytes_per_step": head["d2h_bytes_per_step"],
+                    "ms_per_step": head["e2e_ms_per_step"]},
+            "gpu_launches": head["launches_per_step"] * args.steps,
+            "launches_per_step": head["launches_per_step"],
+            "all_reduce": (("one_shot_nvlink (fused with add+RMSNorm where eligible), NCCL above its limit"
+                            if car is not None else "nccl") if world > 1 else None),
+            "batches": [{"batch": r["batch"], "tokens_per_s": r["batch"] / (r["ms_per_step"] * 1e-3),
+                         "ms_per_step": r["ms_per_step"],
+                         "hbm_frac": r["bytes_per_gpu"] / (r["ms_per_step"] * 1e-3) / 1e9 / peak,
+                         "attention_op": r["attention_op"]} for r in extra],
+            "attention": attention, "checks": checks, "clocks": clocks,
+        }
+        if not args.no_cpu_baseline and world == 1:
+            r = cpu_reference(2, 1)
+            line["cpu_baseline"] = ({"value": r["tokens_per_s"], "unit": "tokens/s", "cores": r["cores"],
+                                     "kind": "port", "sample": r["sample"]} if "unavailable" not in r else
+                                    {"value": None, "unit": "tokens/s", "cores": 0, "kind": "port",
+                                     "sample": "unavailable: " + str(r["unavailable"])})
+        print(json.dumps(line), flush=True)
     if world > 1:
+        # orderly teardown: graphs that hold captured collectives go first, then the IPC buffers
+        # (after every rank has stopped using its peers'), then NCCL
+        torch.cuda.synchronize()
+        dist.barrier()
+        if car is not None:
+            car.close()
+        dist.barrier()
         dist.destroy_process_group()
 
 

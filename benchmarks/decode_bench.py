@@ -38,12 +38,38 @@ BLOCK = 16
 
 
 class QLinear:
-    """One gptq_marlin W4A16 g128 linear shard [k, n] with random packed weights."""
+    """One gptq_marlin W4A16 g128 linear shard with random packed weights.
 
-    def __init__(self, ops, k, n, gen):
-        self.ops, self.k, self.n = ops, k, n
-        self.q = torch.randint(-2**31, 2**31 - 1, (k // 16, n * 2), dtype=torch.int32, device="cuda", generator=gen)
-        self.s = (torch.rand(k // 128, n, device="cuda", generator=gen) * 0.004 + 0.0005).half()
+    The FULL layer [k, n] is drawn from `gen` (seeded identically on every rank) in the Marlin
+    layout and then sharded the way the reference shards it (linear.py:277-333, 490-560, 700-760):
+    column-parallel layers keep, for every logical sub-matrix in `col_parts` (q|k|v, gate|up), the
+    rank's slice of its columns; row-parallel layers keep the rank's K rows (and its scale groups).
+    A Marlin tile is 16 k x 64 n (gptq_marlin_repack.cu:32-256), so column slices at multiples of 64
+    and row slices at multiples of 16 are slices of the packed tensor too: [k/16, 2n] int32 and
+    [k/128, n] scales (scale permutation works inside 64-column chunks, gptq_marlin.py:28-57).
+    TP-N therefore computes the same function as TP-1 up to summation order."""
+
+    def __init__(self, ops, k, n, gen, tp=1, rank=0, shard="none", col_parts=None):
+        self.ops = ops
+        q = torch.randint(-2**31, 2**31 - 1, (k // 16, n * 2), dtype=torch.int32, device="cuda", generator=gen)
+        s = (torch.rand(k // 128, n, device="cuda", generator=gen) * 0.004 + 0.0005).half()
+        if tp > 1 and shard == "col":
+            qs, ss, off = [], [], 0
+            for w in (col_parts or [n]):
+                lo = off + rank * (w // tp)
+                assert (w // tp) % 64 == 0
+                qs.append(q[:, 2 * lo: 2 * (lo + w // tp)])
+                ss.append(s[:, lo: lo + w // tp])
+                off += w
+            q, s = torch.cat(qs, 1).contiguous(), torch.cat(ss, 1).contiguous()
+        elif tp > 1 and shard == "row":
+            kk = k // tp
+            assert kk % 128 == 0
+            q = q[rank * kk // 16: (rank + 1) * kk // 16].contiguous()
+            s = s[rank * kk // 128: (rank + 1) * kk // 128].contiguous()
+        self.q, self.s = q, s
+        self.k, self.n = q.shape[0] * 16, q.shape[1] // 2
+        n = self.n
         self.e = torch.empty(0, dtype=torch.int32, device="cuda")
         self.ws = torch.zeros(max(n // 64, 1) * 16, dtype=torch.int32, device="cuda")
 
@@ -56,17 +82,26 @@ class QLinear:
 
 
 class Layer:
-    def __init__(self, ops, tp, gen, num_blocks):
-        self.h, self.kvh = HEADS // tp, max(KV_HEADS // tp, 1)
-        self.qkv = QLinear(ops, HIDDEN, (self.h + 2 * self.kvh) * HEAD, gen)
-        self.o = QLinear(ops, self.h * HEAD, HIDDEN, gen)
-        self.gate_up = QLinear(ops, HIDDEN, 2 * INTER // tp, gen)
-        self.down = QLinear(ops, INTER // tp, HIDDEN, gen)
-        self.ln1 = torch.ones(HIDDEN, dtype=torch.half, device="cuda")
-        self.ln2 = torch.ones(HIDDEN, dtype=torch.half, device="cuda")
+    def __init__(self, ops, tp, rank, gen, num_blocks):
+        assert KV_HEADS % tp == 0, "kv heads are the sharding unit (8 / tp)"
+        self.h, self.kvh = HEADS // tp, KV_HEADS // tp
+        self.qkv = QLinear(ops, HIDDEN, (HEADS + 2 * KV_HEADS) * HEAD, gen, tp, rank, "col",
+                           [HEADS * HEAD, KV_HEADS * HEAD, KV_HEADS * HEAD])
+        self.o = QLinear(ops, HEADS * HEAD, HIDDEN, gen, tp, rank, "row")
+        self.gate_up = QLinear(ops, HIDDEN, 2 * INTER, gen, tp, rank, "col", [INTER, INTER])
+        self.down = QLinear(ops, INTER, HIDDEN, gen, tp, rank, "row")
+        self.ln1 = (torch.rand(HIDDEN, device="cuda", generator=gen) + 0.5).half()
+        self.ln2 = (torch.rand(HIDDEN, device="cuda", generator=gen) + 0.5).half()
         s = HEAD ** -0.5
-        self.kc = torch.empty(num_blocks, self.kvh, HEAD // 8, BLOCK, 8, dtype=torch.half, device="cuda").uniform_(-s, s)
-        self.vc = torch.empty(num_blocks, self.kvh, HEAD, BLOCK, dtype=torch.half, device="cuda").uniform_(-s, s)
+        # the full 8-kv-head cache content is drawn per layer, the rank keeps its heads
+        # (cache_engine.py:39: [num_blocks, kv_heads / tp, ...] per rank)
+        kc = torch.empty(num_blocks, KV_HEADS, HEAD // 8, BLOCK, 8, dtype=torch.half, device="cuda")
+        vc = torch.empty(num_blocks, KV_HEADS, HEAD, BLOCK, dtype=torch.half, device="cuda")
+        kc.uniform_(-s, s, generator=gen)
+        vc.uniform_(-s, s, generator=gen)
+        lo = rank * self.kvh
+        self.kc = kc[:, lo: lo + self.kvh].contiguous() if tp > 1 else kc
+        self.vc = vc[:, lo: lo + self.kvh].contiguous() if tp > 1 else vc
 
     def linear_bytes(self):
         return self.qkv.bytes() + self.o.bytes() + self.gate_up.bytes() + self.down.bytes()
@@ -78,19 +113,26 @@ def rope(x, cos, sin):  # neox style, x [B, H, D]
 
 
 class Decoder:
-    def __init__(self, ops, tp, rank, batch, ctx, lm_head=True, glue="fused", car=None):
-        self.ops, self.tp, self.batch, self.ctx = ops, tp, batch, ctx
+    def __init__(self, ops, tp, rank, batch, ctx, lm_head=True, glue="fused", car=None, num_layers=LAYERS):
+        self.ops, self.tp, self.rank, self.batch, self.ctx = ops, tp, rank, batch, ctx
         self.car = car  # one-shot NVLink all-reduce (None: NCCL)
         self.fuse_ar_norm = True
         self.step = self.step_fused if glue == "fused" else self.step_torch
-        gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
+        # one seed for every rank: each rank draws the full tensors and keeps its shard
+        gen = torch.Generator(device="cuda").manual_seed(1234)
         blocks_per_seq = (ctx + BLOCK) // BLOCK
         self.num_blocks = batch * blocks_per_seq
-        self.layers = [Layer(ops, tp, gen, self.num_blocks) for _ in range(LAYERS)]
-        self.norm = torch.ones(HIDDEN, dtype=torch.half, device="cuda")
-        self.lm_head = (torch.randn(VOCAB // tp, HIDDEN, device="cuda", generator=gen) * 0.02).half() if lm_head else None
         self.embed = (torch.randn(4096, HIDDEN, device="cuda", generator=gen) * 0.02).half()
         perm = torch.randperm(self.num_blocks, device="cuda", generator=gen).to(torch.int32)
+        self.tokens = torch.randint(0, 4096, (batch,), device="cuda", generator=gen)
+        self.norm = (torch.rand(HIDDEN, device="cuda", generator=gen) + 0.5).half()
+        self.layers = [Layer(ops, tp, rank, gen, self.num_blocks) for _ in range(num_layers)]
+        self.lm_head = None
+        if lm_head:
+            full = (torch.randn(VOCAB, HIDDEN, device="cuda", generator=gen) * 0.02).half()
+            vs = VOCAB // tp  # vocab-parallel lm_head (vocab_parallel_embedding.py of the reference)
+            self.lm_head = full[rank * vs: (rank + 1) * vs].contiguous() if tp > 1 else full
+            del full
         self.block_tables = perm.view(batch, blocks_per_seq).contiguous()
         self.seq_lens = torch.full((batch,), ctx + 1, dtype=torch.int32, device="cuda")
         last = self.block_tables[:, ctx // BLOCK].to(torch.int64)
@@ -102,13 +144,31 @@ class Decoder:
         tab = torch.arange(ctx + 1, device="cuda").float()[:, None] * inv[None]
         self.cos_sin_cache = torch.cat((tab.cos(), tab.sin()), -1).half()
         self.positions = torch.full((batch,), ctx, dtype=torch.int64, device="cuda")
-        self.tokens = torch.randint(0, 4096, (batch,), device="cuda", generator=gen)
+        self.next_tokens = torch.zeros(batch, dtype=torch.int64, device="cuda")
         h = self.layers[0].h
         self.parts = (ctx + 1 + 511) // 512
         self.use_v1 = self.parts == 1 or batch * h > 512  # paged_attn.py:118-119 of the reference
         self.tmp = torch.empty(batch, h, self.parts, HEAD, dtype=torch.half, device="cuda")
         self.es = torch.empty(batch, h, self.parts, dtype=torch.float32, device="cuda")
         self.ml = torch.empty_like(self.es)
+
+    def sample(self, hn):
+        """Greedy sampling over the vocab-parallel lm_head: every rank takes (max, argmax) of its
+        vocab shard, the [tp, batch, 2] candidates are all-gathered (NCCL, inside the graph) and
+        every rank picks the global winner -- the same token the reference's gather-to-rank-0 of the
+        full logits + argmax yields (logits_processor.py:59-66 + sampler greedy)."""
+        logits = hn @ self.lm_head.t()
+        if self.tp == 1:
+            nxt = logits.argmax(-1)
+        else:
+            val, idx = logits.float().max(-1)
+            cand = torch.stack((val, (idx + self.rank * (VOCAB // self.tp)).float()), -1)  # ids < 2^24: exact
+            allc = torch.empty(self.tp, self.batch, 2, dtype=torch.float32, device="cuda")
+            dist.all_gather_into_tensor(allc, cand)
+            best = allc[..., 0].argmax(0)
+            nxt = allc[..., 1].gather(0, best[None]).squeeze(0).long()
+        self.next_tokens.copy_(nxt)
+        self.tokens.copy_(nxt % 4096)  # the harness embeds through a 4096-row table (stated)
 
     def all_reduce(self, t):
         """Row-parallel partial sums (linear.py:792-793): one-shot NVLink kernel when the message
@@ -169,8 +229,7 @@ class Decoder:
             ops.fused_add_rms_norm(x, res, self.norm, 1e-5)
         hn = x
         if self.lm_head is not None:
-            logits = hn @ self.lm_head.t()
-            self.tokens.copy_(logits.argmax(-1) % 4096)  # greedy on the local vocab shard (no gather: stated)
+            self.sample(hn)
         return hn
 
     def step_torch(self):
@@ -205,8 +264,7 @@ class Decoder:
             res = res + d
         hn = F.rms_norm(res, (HIDDEN,), self.norm, 1e-5)
         if self.lm_head is not None:
-            logits = hn @ self.lm_head.t()
-            self.tokens.copy_(logits.argmax(-1) % 4096)  # greedy on the local vocab shard (no gather: stated)
+            self.sample(hn)
         return hn
 
     def linear_bytes(self):
@@ -291,7 +349,7 @@ def main():
                 "ar_norm_fused": bool(car is not None and dec.fuse_ar_norm),
                 "hbm_bytes_per_step_per_gpu": byts, "linear_bytes_per_gpu": lin, "kv_bytes_per_gpu": kv,
                 "hbm_GBps": byts / ms / 1e6, "hbm_frac": byts / ms / 1e6 / hbm,
-                "excluded": "scheduler, sampler (greedy argmax on the local vocab shard only), tokenizer",
+                "excluded": "scheduler, tokenizer; sampler = greedy argmax over the vocab-parallel lm_head",
                 "data": "synthetic: random-init packed int4 weights, random KV"}), flush=True)
         del dec, graph
         torch.cuda.empty_cache()

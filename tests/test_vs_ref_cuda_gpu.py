@@ -1,0 +1,283 @@
+"""This repo's kernels against the reference's OWN CUDA kernels on identical inputs, at the
+BASELINE.json shapes (north_star: "checked against the reference's own implementation on identical
+synthetic inputs and random-init weights").
+
+The reference side is oracle/_ref/_C_refcuda.so: /root/reference/csrc/**/*.cu compiled where they
+lie for sm_100 by oracle/build_ref_cuda.py (no CUTLASS needed for these files) and registered as
+torch.ops._C_refcuda*.  The library is built in the development container and shipped to the GPU
+box; when it is absent the whole module is skipped (never silently passed).
+
+Bars: bit-exact for the byte / integer work (repack, cache scatter and copies, fp8 quantisation
+bytes, activation quant scales); rtol 1e-2 / atol 1e-3 for attention; GEMMs: rtol 1e-2 with the
+atol of tests/test_baseline_shapes_gpu.py (both kernels round a K-long fp32 tensor-core
+accumulation to fp16 in different orders).
+"""
+import pytest
+import torch
+
+from oracle import quant_ref as qr
+from oracle import ref_cuda
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+@pytest.fixture(scope="module")
+def ref():
+    if not ref_cuda.available():
+        pytest.skip(ref_cuda.why_unavailable())
+    return ref_cuda.ops()
+
+
+@pytest.fixture(scope="module")
+def ref_cache():
+    if not ref_cuda.available():
+        pytest.skip(ref_cuda.why_unavailable())
+    return ref_cuda.cache_ops()
+
+
+def _ws(n, par=16, thread_n=64):
+    return torch.zeros((n // thread_n) * par, dtype=torch.int32, device=DEV)
+
+
+def _rand_marlin(k, n, bits, group, dtype, seed):
+    """random packed Marlin weights + scales: any bit pattern is a valid quantised weight"""
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    words = 16 * bits // 32
+    q = torch.randint(-2**31, 2**31 - 1, (k // 16, n * words), dtype=torch.int32, device=DEV, generator=g)
+    groups = 1 if group == -1 else k // group
+    s = (torch.rand(groups, n, device=DEV, generator=g) * 0.02 + 0.002).to(dtype)
+    return q, s
+
+
+# ---------------------------------------------------------------------------------------------
+# gptq_marlin_gemm: C3 layers and their TP shards, 4 / 8 bit, every group size
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("m", [1, 16, 64, 256, 2048])
+@pytest.mark.parametrize("k,n", [(4096, 6144), (4096, 4096), (4096, 28672), (14336, 4096),
+                                 (4096, 3584), (1792, 4096)])
+def test_marlin_vs_reference_cuda(ops, ref, k, n, m):
+    q, s = _rand_marlin(k, n, 4, 128, torch.half, k + n)
+    a = torch.randn(m, k, dtype=torch.half, device=DEV, generator=torch.Generator(device=DEV).manual_seed(m))
+    e = torch.empty(0, dtype=torch.int32, device=DEV)
+    ours = ops.gptq_marlin_gemm(a, q, s, e, e, _ws(n), 4, m, n, k, True)
+    theirs = ref.gptq_marlin_gemm(a, q, s, e, e, _ws(n), 4, m, n, k, True)
+    atol = 1e-3 * max(1.0, k / 2048 - 1.0) * 4  # scales here are ~4x those of a randn-quantised layer
+    torch.testing.assert_close(ours.float(), theirs.float(), rtol=1e-2, atol=atol)
+
+
+@pytest.mark.parametrize("bits,group", [(4, -1), (4, 32), (4, 64), (8, -1), (8, 128), (8, 32)])
+@pytest.mark.parametrize("dtype", [torch.half, torch.bfloat16])
+def test_marlin_variants_vs_reference_cuda(ops, ref, bits, group, dtype):
+    k, n = 4096, 4096
+    q, s = _rand_marlin(k, n, bits, group, dtype, bits * 100 + group)
+    if bits == 8:
+        s = s / 16
+    e = torch.empty(0, dtype=torch.int32, device=DEV)
+    for m in (1, 33, 512):
+        a = torch.randn(m, k, dtype=dtype, device=DEV)
+        ours = ops.gptq_marlin_gemm(a, q, s, e, e, _ws(n), bits, m, n, k, True)
+        theirs = ref.gptq_marlin_gemm(a, q, s, e, e, _ws(n), bits, m, n, k, True)
+        atol = 4e-3 if dtype is torch.half else 6e-2
+        torch.testing.assert_close(ours.float(), theirs.float(), rtol=1e-2, atol=atol)
+
+
+def test_marlin_act_order_vs_reference_cuda(ops, ref):
+    k, n, m = 4096, 4096, 48
+    g = torch.Generator().manual_seed(5)
+    w = torch.randn(k, n, dtype=torch.half, generator=g)
+    _, mq, ms, g_idx, sort_idx, _ = qr.marlin_quantize(w, 4, 128, True)
+    a = torch.randn(m, k, dtype=torch.half, device=DEV)
+    args = (a, mq.to(DEV), ms.to(DEV), g_idx.to(DEV), sort_idx.to(DEV))
+    ours = ops.gptq_marlin_gemm(*args, _ws(n), 4, m, n, k, True)
+    theirs = ref.gptq_marlin_gemm(*args, _ws(n), 4, m, n, k, True)
+    torch.testing.assert_close(ours.float(), theirs.float(), rtol=1e-2, atol=2e-3)
+
+
+@pytest.mark.parametrize("bits", [4, 8])
+@pytest.mark.parametrize("act_order", [False, True])
+def test_repack_vs_reference_cuda(ops, ref, bits, act_order):
+    k, n = 4096, 6144
+    g = torch.Generator(device=DEV).manual_seed(bits)
+    qw = torch.randint(-2**31, 2**31 - 1, (k * bits // 32, n), dtype=torch.int32, device=DEV, generator=g)
+    perm = (torch.randperm(k, device=DEV, generator=g).to(torch.int32) if act_order
+            else torch.empty(0, dtype=torch.int32, device=DEV))
+    assert torch.equal(ops.gptq_marlin_repack(qw, perm, k, n, bits), ref.gptq_marlin_repack(qw, perm, k, n, bits))
+
+
+# ---------------------------------------------------------------------------------------------
+# gptq_marlin_24_gemm: C5 layers (TP1 and TP2)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("k,n", [(4096, 12288), (4096, 22016), (11008, 4096), (2048, 4096), (5504, 4096)])
+def test_marlin_24_vs_reference_cuda(ops, ref, k, n):
+    g = torch.Generator(device=DEV).manual_seed(k + n)
+    w = torch.randn(k, n, dtype=torch.half, device=DEV, generator=g)
+    _, mq, meta, ms = qr.marlin_24_quantize(w, 4, 128)
+    del w
+    for m in (1, 16, 128):
+        a = torch.randn(m, k, dtype=torch.half, device=DEV, generator=g)
+        ours = ops.gptq_marlin_24_gemm(a, mq, meta, ms, _ws(n, 64, 128), 4, m, n, k)
+        theirs = ref.gptq_marlin_24_gemm(a, mq, meta, ms, _ws(n, 64, 128), 4, m, n, k)
+        torch.testing.assert_close(ours.float(), theirs.float(), rtol=1e-2, atol=1e-3 * max(1.0, k / 2048 - 1.0))
+
+
+# ---------------------------------------------------------------------------------------------
+# paged attention: C2 at full size, fp16 and fp8 KV, v1 and v2, ragged lengths
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kv", ["auto", "fp8"])
+@pytest.mark.parametrize("version", ["v1", "v2"])
+def test_attention_vs_reference_cuda(ops, kv, version):
+    if not ref_cuda.available():
+        pytest.skip(ref_cuda.why_unavailable())
+    B, H, KVH, D, bs, ctx = 64, 32, 8, 128, 16, 4096
+    nb = B * ctx // bs
+    g = torch.Generator(device=DEV).manual_seed(0)
+    s = D ** -0.5
+    x = 8 if kv == "auto" else 16
+    q = (torch.rand(B, H, D, device=DEV, generator=g) * 2 - 1).mul_(s).half()
+    kc = (torch.rand(nb, KVH, D // x, bs, x, device=DEV, generator=g) * 2 - 1).mul_(s).half()
+    vc = (torch.rand(nb, KVH, D, bs, device=DEV, generator=g) * 2 - 1).mul_(s).half()
+    if kv == "fp8":
+        kc8, vc8 = torch.empty_like(kc, dtype=torch.uint8), torch.empty_like(vc, dtype=torch.uint8)
+        ops.convert_fp8(kc8, kc, 1.0, "fp8")
+        ops.convert_fp8(vc8, vc, 1.0, "fp8")
+        kc, vc = kc8, vc8
+    bt = torch.randperm(nb, device=DEV, generator=g).to(torch.int32).view(B, ctx // bs)
+    sl = torch.full((B,), ctx, dtype=torch.int32, device=DEV)
+    sl[1::2] = torch.randint(1, ctx + 1, (B // 2,), device=DEV, generator=g).to(torch.int32)
+    outs = []
+    for impl in ("ours", "ref"):
+        out = torch.empty_like(q)
+        parts = ctx // 512
+        tmp = torch.empty(B, H, parts, D, dtype=torch.half, device=DEV)
+        es = torch.empty(B, H, parts, dtype=torch.float32, device=DEV)
+        ml = torch.empty_like(es)
+        if impl == "ours":
+            if version == "v2":
+                ops.paged_attention_v2(out, es, ml, tmp, q, kc, vc, KVH, s, bt, sl, bs, ctx, None, kv, 1.0)
+            else:
+                ops.paged_attention_v1(out, q, kc, vc, KVH, s, bt, sl, bs, ctx, None, kv, 1.0)
+        else:
+            if version == "v2":
+                ref_cuda.paged_attention_v2(out, es, ml, tmp, q, kc, vc, KVH, s, bt, sl, bs, ctx, None, kv, 1.0)
+            else:
+                ref_cuda.paged_attention_v1(out, q, kc, vc, KVH, s, bt, sl, bs, ctx, None, kv, 1.0)
+        outs.append(out)
+    torch.cuda.synchronize()
+    atol = 1e-3 if kv == "auto" else 1e-2
+    torch.testing.assert_close(outs[0].float(), outs[1].float(), rtol=1e-2, atol=atol)
+
+
+# ---------------------------------------------------------------------------------------------
+# cache ops: scatter / copy / fp8 bytes, bit-exact
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kv", ["auto", "fp8"])
+@pytest.mark.parametrize("dtype", [torch.half, torch.bfloat16, torch.float])
+def test_reshape_and_cache_vs_reference_cuda(ops, ref_cache, dtype, kv):
+    T, Hh, D, bs, nb = 2048, 8, 128, 16, 1024
+    g = torch.Generator(device=DEV).manual_seed(1)
+    qkv = torch.randn(T, 3, Hh, D, device=DEV, generator=g).to(dtype)
+    key, value = qkv[:, 1], qkv[:, 2]          # strided rows, as a slice of a qkv tensor
+    slots = torch.randperm(nb * bs, device=DEV, generator=g)[:T].to(torch.int64)
+    slots[::7] = -1                             # padding tokens are skipped
+    cdt = dtype if kv == "auto" else torch.uint8
+    x = 16 // torch.tensor([], dtype=cdt).element_size()
+    caches = []
+    for fn in (ops.reshape_and_cache, ref_cache.reshape_and_cache):
+        kc = torch.zeros(nb, Hh, D // x, bs, x, dtype=cdt, device=DEV)
+        vc = torch.zeros(nb, Hh, D, bs, dtype=cdt, device=DEV)
+        fn(key, value, kc, vc, slots, kv, 0.5 if kv == "fp8" else 1.0)
+        caches.append((kc, vc))
+    assert torch.equal(caches[0][0], caches[1][0]) and torch.equal(caches[0][1], caches[1][1])
+
+
+def test_reshape_and_cache_flash_vs_reference_cuda(ops, ref_cache):
+    T, Hh, D, bs, nb = 777, 8, 128, 16, 256
+    g = torch.Generator(device=DEV).manual_seed(2)
+    key = torch.randn(T, Hh, D, device=DEV, generator=g).half()
+    value = torch.randn(T, Hh, D, device=DEV, generator=g).half()
+    slots = torch.randperm(nb * bs, device=DEV, generator=g)[:T].to(torch.int64)
+    res = []
+    for fn in (ops.reshape_and_cache_flash, ref_cache.reshape_and_cache_flash):
+        kc = torch.zeros(nb, bs, Hh, D, dtype=torch.half, device=DEV)
+        vc = torch.zeros_like(kc)
+        fn(key, value, kc, vc, slots, "auto")
+        res.append((kc, vc))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+
+
+def test_copy_blocks_and_convert_fp8_vs_reference_cuda(ops, ref_cache):
+    nb, Hh, D, bs = 128, 8, 128, 16
+    g = torch.Generator(device=DEV).manual_seed(3)
+    src = [torch.randn(nb, Hh, D // 8, bs, 8, device=DEV, generator=g).half() for _ in range(2)]
+    srv = [torch.randn(nb, Hh, D, bs, device=DEV, generator=g).half() for _ in range(2)]
+    mapping = torch.tensor([[i, 64 + i] for i in range(40)], dtype=torch.int64, device=DEV)
+    a_k, a_v = [t.clone() for t in src], [t.clone() for t in srv]
+    b_k, b_v = [t.clone() for t in src], [t.clone() for t in srv]
+    ops.copy_blocks(a_k, a_v, mapping)
+    ref_cache.copy_blocks(b_k, b_v, mapping)
+    for x, y in zip(a_k + a_v, b_k + b_v):
+        assert torch.equal(x, y)
+    big = (torch.rand(nb, Hh, D, bs, device=DEV, generator=g) * 448 - 224).half()
+    o1, o2 = torch.empty_like(big, dtype=torch.uint8), torch.empty_like(big, dtype=torch.uint8)
+    ops.convert_fp8(o1, big, 2.0, "fp8")
+    ref_cache.convert_fp8(o2, big, 2.0, "fp8")
+    assert torch.equal(o1, o2)
+    back1, back2 = torch.empty_like(big), torch.empty_like(big)
+    ops.convert_fp8(back1, o1, 2.0, "fp8")
+    ref_cache.convert_fp8(back2, o2, 2.0, "fp8")
+    assert torch.equal(back1, back2)
+
+
+# ---------------------------------------------------------------------------------------------
+# activation quantisation feeding cutlass_scaled_mm, and the decode-side glue
+# ---------------------------------------------------------------------------------------------
+def test_activation_quant_vs_reference_cuda(ops, ref):
+    g = torch.Generator(device=DEV).manual_seed(4)
+    x = (torch.randn(257, 8192, device=DEV, generator=g) * 3).half()
+    o1, s1 = ops.scaled_fp8_quant(x)
+    o2 = torch.empty_like(x, dtype=torch.float8_e4m3fn)
+    s2 = torch.zeros(1, dtype=torch.float32, device=DEV)
+    ref.dynamic_scaled_fp8_quant(o2, x, s2)
+    assert torch.equal(s1.view(-1), s2.view(-1))
+    assert torch.equal(o1.view(torch.uint8), o2.view(torch.uint8))
+    i1, t1 = ops.scaled_int8_quant(x)
+    i2 = torch.empty_like(x, dtype=torch.int8)
+    t2 = torch.empty(x.shape[0], 1, dtype=torch.float32, device=DEV)
+    ref.dynamic_scaled_int8_quant(i2, x, t2)
+    assert torch.equal(t1, t2)
+    assert int((i1.int() - i2.int()).abs().max()) <= 1  # ties of x / scale: float division order
+
+
+def test_glue_vs_reference_cuda(ops, ref):
+    g = torch.Generator(device=DEV).manual_seed(6)
+    T, Hd = 256, 4096
+    x = torch.randn(T, Hd, device=DEV, generator=g).half()
+    w = (torch.rand(Hd, device=DEV, generator=g) + 0.5).half()
+    o1, o2 = torch.empty_like(x), torch.empty_like(x)
+    ops.rms_norm(o1, x, w, 1e-5)
+    ref.rms_norm(o2, x, w, 1e-5)
+    torch.testing.assert_close(o1.float(), o2.float(), rtol=1e-2, atol=1e-3)
+    r1 = torch.randn(T, Hd, device=DEV, generator=g).half()
+    x1, x2, r2 = x.clone(), x.clone(), r1.clone()
+    ops.fused_add_rms_norm(x1, r1, w, 1e-5)
+    ref.fused_add_rms_norm(x2, r2, w, 1e-5)
+    assert torch.equal(r1, r2)
+    torch.testing.assert_close(x1.float(), x2.float(), rtol=1e-2, atol=1e-3)
+    gu = torch.randn(T, 2 * 14336, device=DEV, generator=g).half()
+    a1 = torch.empty(T, 14336, dtype=torch.half, device=DEV)
+    a2 = torch.empty_like(a1)
+    ops.silu_and_mul(a1, gu)
+    ref.silu_and_mul(a2, gu)
+    torch.testing.assert_close(a1.float(), a2.float(), rtol=1e-2, atol=1e-3)
+    pos = torch.randint(0, 4096, (T,), device=DEV, generator=g)
+    inv = 500000.0 ** (-torch.arange(0, 128, 2, device=DEV).float() / 128)
+    tab = torch.arange(4096, device=DEV).float()[:, None] * inv[None]
+    csc = torch.cat((tab.cos(), tab.sin()), -1).half()
+    q1 = torch.randn(T, 32 * 128, device=DEV, generator=g).half()
+    k1 = torch.randn(T, 8 * 128, device=DEV, generator=g).half()
+    q2, k2 = q1.clone(), k1.clone()
+    ops.rotary_embedding(pos, q1, k1, 128, csc, True)
+    ref.rotary_embedding(pos, q2, k2, 128, csc, True)
+    torch.testing.assert_close(q1.float(), q2.float(), rtol=1e-2, atol=1e-3)
+    torch.testing.assert_close(k1.float(), k2.float(), rtol=1e-2, atol=1e-3)
