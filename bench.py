@@ -386,24 +386,32 @@ def check_vs_reference_cuda(dec, batch, torch):
     except Exception as e:  # the checker is optional on the bench path
         return {"unavailable": repr(e)}
     lins = [L.gate_up for L in dec.layers]
-    x = torch.randn(batch, 4096, dtype=torch.half, device="cuda")
+    out = {}
     with torch.no_grad():
-        ours = lins[0](x)
         ws = torch.zeros(lins[0].n // 64 * 16, dtype=torch.int32, device="cuda")
 
-        def ref_call(lin):
-            return torch.ops._C_refcuda.gptq_marlin_gemm(x, lin.q, lin.s, lin.e, lin.e, ws, 4, batch, lin.n, lin.k, True)
-        ref = ref_call(lins[0])
-        torch.testing.assert_close(ours.float(), ref.float(), rtol=1e-2, atol=2e-3)
+        def ref_call(lin, x):
+            return torch.ops._C_refcuda.gptq_marlin_gemm(x, lin.q, lin.s, lin.e, lin.e, ws, 4, x.shape[0],
+                                                         lin.n, lin.k, True)
+        # parity at M = 16, where the reference kernel recompiled for sm_100 is deterministic (from
+        # M = 48-64 up two identical calls of it disagree on B200: tests/test_vs_ref_cuda_gpu.py)
+        x16 = torch.randn(16, 4096, dtype=torch.half, device="cuda")
+        ours, ref = lins[0](x16), ref_call(lins[0], x16)
+        atol = 2 * 2.0 ** -10 * float(ref.float().abs().max()) + 1e-3  # the reference reduces k-slices in fp16
+        torch.testing.assert_close(ours.float(), ref.float(), rtol=1e-2, atol=atol)
+        out["gate_up_m16_vs_reference_cuda"] = f"ok (rtol 1e-2 atol {atol:.2g})"
+        x = torch.randn(batch, 4096, dtype=torch.half, device="cuda")
+        r1, r2 = ref_call(lins[0], x), ref_call(lins[0], x)
+        out["reference_cuda_deterministic_at_headline_m"] = bool(torch.equal(r1, r2))
         torch.cuda.synchronize()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
         for lin in lins:
-            ref_call(lin)
+            ref_call(lin, x)
         ev1.record()
         torch.cuda.synchronize()
-    return {"gate_up_vs_reference_cuda": "ok (rtol 1e-2 atol 2e-3)",
-            "reference_cuda_us_per_launch": ev0.elapsed_time(ev1) * 1e3 / len(lins)}
+    out["reference_cuda_gate_up_us_per_launch"] = ev0.elapsed_time(ev1) * 1e3 / len(lins)
+    return out
 
 
 def main():
