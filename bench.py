@@ -503,11 +503,13 @@ def main():
     if rank == 0:
         checks.update(check_vs_reference_cuda(dec, HEADLINE_BATCH, torch))
     # keep the headline graph replaying ~1.5 s so the 100 ms nvidia-smi sampler sees it under load
-    t_soak = time.perf_counter()
-    while time.perf_counter() - t_soak < 1.5:
-        for _ in range(20):
-            graph.replay()
-        torch.cuda.synchronize()
+    # (the graph holds collectives at N > 1: every rank must replay it the SAME number of times)
+    t_ms = torch.tensor([head["ms_per_step"]], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    for _ in range(int(1500.0 / max(float(t_ms[0]), 0.05)) + 1):
+        graph.replay()
+    torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
     if clocks is not None:
         clocks["window"] = "timed region + e2e region + 1.5 s continuation of the headline step"
