@@ -880,12 +880,28 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   return B200_OK;
 }
 
+#include "marlin_gemm_stream.cuh"
+
+// which decode kernel: 0 = stream-K persistent (default), 1 = first-generation split-K kernel
+inline int decode_kernel_choice() {
+  static int knob[2] = {0, 0};
+  return env_int_once("B200_MARLIN_DECODE_V1", knob, 0);
+}
+
 template <int BITS, typename T, bool ACT>
 int dispatch_bm(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t lda, cudaStream_t st) {
   // decode kernel: ungrouped, or groups that never change inside a 64-k stage
   // (and power-of-two group sizes, so the group index is a shift: every GPTQ group size is)
   const int gsz = p.num_groups > 1 ? p.size_k / p.num_groups : 0;
   const bool one_group_per_stage = p.num_groups == 1 || (gsz % kStageK == 0 && (gsz & (gsz - 1)) == 0);
+  if (!ACT && one_group_per_stage && p.size_m <= 64 && p.workspace != nullptr && p.splitk_ws != nullptr &&
+      p.splitk_ws_bytes >= stream_ws_bytes(p.size_m) && decode_kernel_choice() == 0) {
+    switch (pick_bm(p.size_m)) {
+      case 16: return launch_stream<BITS, 16, T>(p, st);
+      case 32: return launch_stream<BITS, 32, T>(p, st);
+      default: return launch_stream<BITS, 64, T>(p, st);
+    }
+  }
   if (!ACT && one_group_per_stage) {
     switch (pick_bm(p.size_m)) {
       case 16: return launch_tmem<BITS, 16, T>(p, st);
@@ -929,7 +945,9 @@ extern "C" {
 
 int64_t b200_gptq_marlin_gemm_workspace_bytes(int32_t m, int32_t n, int32_t k) {
   const int splits = b200::pick_splits(m, n, k / b200::kStageK, -1);
-  return splits > 1 ? (int64_t)splits * m * n * 4 : 0;
+  const int64_t v1 = splits > 1 ? (int64_t)splits * m * n * 4 : 0;
+  const int64_t v2 = m <= 64 ? b200::stream_ws_bytes(m) : 0;  // stream-K decode kernel: 2 slots per CTA
+  return v1 > v2 ? v1 : v2;
 }
 
 int b200_gptq_marlin_gemm(const b200_gptq_marlin_gemm_params* pp, void* stream) {

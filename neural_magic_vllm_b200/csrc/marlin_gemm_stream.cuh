@@ -1,0 +1,452 @@
+// gptq_marlin_gemm decode kernel, second generation: persistent, stream-K, one CTA per SM.
+// (included by marlin_gemm.cu; same operator, same layouts, same bit-exact dequant as the kernels
+// there -- replaces the stripe loop of csrc/quantization/gptq_marlin/gptq_marlin.cu:933-988.)
+//
+// Decode (M <= 64) is weight streaming: the only thing that matters is that every SM pulls its
+// 1/148th of the packed weights at the HBM rate and that the dequant warps keep up.
+//
+//   work      the (256-column n tile, 64-k block) units of the layer are laid out tile-major and cut
+//             into `grid` equal contiguous ranges, one per CTA (stream-K): every SM streams the same
+//             number of bytes whatever the layer shape.  A range covers the tail of one tile, whole
+//             tiles, and the head of another ("pieces").
+//   warp 0    TMA producer: per unit one activation tile [BM x 64] (128-byte swizzle), the packed
+//             weights (1 KiB rows of the Marlin tensor) and one group-scale row into a ring of
+//             ~20 stages (~210 KiB in flight per SM -- an epilogue never starves HBM)
+//   warp 1    MMA issuer: tcgen05.mma kind::f16, A = dequantised weights in TMEM, B = activations
+//             in shared memory, D = fp32 in TMEM, double-buffered per piece
+//   warps 2-17  four dequant teams of four warps (one per TMEM quadrant).  A job is one 128 x 64
+//             sub-tile of a stage; jobs go round-robin to the teams, each team owns two 32-column
+//             A slots in TMEM, so four jobs are in flight while the MMA consumes in order.
+//             LDS.64 packed words -> lop3 / hsub2 / hfma2 exact (q - 8) -> x group scale (one
+//             rounding: bit-identical to the reference's w_ref) -> tcgen05.st straight to TMEM.
+//   warps 18-21 epilogue: tcgen05.ld the finished piece; a whole tile is rounded once and stored,
+//             a partial one goes to the fp32 workspace and bumps the tile's arrival counter.  After
+//             its last piece a CTA waits for the tiles it contributed to and sums ITS SLICE of each
+//             (fixed slot order: deterministic), so the split-K reduction is spread over all SMs
+//             and needs no second kernel.  The counters are the caller's `workspace` (zero on entry,
+//             zero on exit, as the reference requires: gptq_marlin.cu:329-332).
+// (no include guard / namespaces: this file is spliced into marlin_gemm.cu's b200::{anonymous})
+
+constexpr int kSNT = 2;                       // 128-row sub-tiles per n tile
+constexpr int kSCtaN = kSNT * kTileN;         // 256
+constexpr int kSTeams = 4;
+constexpr int kSDequantWarps = kSTeams * 4;
+constexpr int kSEpiWarps = 4;
+constexpr int kSThreads = (2 + kSDequantWarps + kSEpiWarps) * 32;  // 704
+constexpr int kSASlots = 2 * kSTeams;         // TMEM A slots of 32 columns (64 k)
+constexpr int kSDCol = kSASlots * kTmemAStageCols;  // 256: first accumulator column
+constexpr int kSMaxStages = 24;
+
+template <int BITS, int BM>
+struct PlanS {
+  static constexpr int kPackedBytes = kStageK * kSCtaN * BITS / 8;  // 8 KiB / 16 KiB
+  static constexpr int kScaleBytes = kSCtaN * 2;                    // one group-scale row
+  static constexpr int kXBytes = BM * 128;
+  static constexpr int kStageBytes = (kXBytes + kPackedBytes + kScaleBytes + 1023) / 1024 * 1024;
+  static constexpr int kBudget = 224 * 1024;
+  static constexpr int kStages = kBudget / kStageBytes > kSMaxStages ? kSMaxStages : kBudget / kStageBytes;
+  static constexpr int kBarBytes = (2 * kStages + 2 * kSASlots + 4) * 8 + 64;
+  static constexpr int kBytes = kStages * kStageBytes + 1024 + kBarBytes;
+  static_assert(kStages >= 4, "ring too shallow");
+  static_assert(kSDCol + 2 * kSNT * BM <= 512, "TMEM columns");
+};
+
+struct StreamArgs {
+  int n_tiles;      // ceil(n / 256)
+  int grid;         // CTAs = ranges
+  int64_t units;    // n_tiles * num_kb
+};
+
+// range start of CTA c; CTA that owns unit u
+__device__ __forceinline__ int64_t s_range_start(const StreamArgs& s, int c) { return (int64_t)c * s.units / s.grid; }
+__device__ __forceinline__ int s_cta_of_unit(const StreamArgs& s, int64_t u) {
+  return (int)(((u + 1) * s.grid - 1) / s.units);
+}
+
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+template <int BITS, int BM, typename T>
+__global__ void __launch_bounds__(kSThreads, 1)
+marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+                          const __grid_constant__ CUtensorMap tm_s, const MarlinArgs args, const StreamArgs sa) {
+  using P = PlanS<BITS, BM>;
+  constexpr int kStages = P::kStages;
+  constexpr int KIND = DT<T>::id == B200_F16 ? KIND_F16 : KIND_BF16;
+  constexpr int kDCols = kSNT * BM;  // accumulator columns of one piece
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stages + kStages * P::kStageBytes);
+  uint64_t* full_p = bars;
+  uint64_t* empty_p = full_p + kStages;
+  uint64_t* full_a = empty_p + kStages;
+  uint64_t* empty_a = full_a + kSASlots;
+  uint64_t* tmem_full = empty_a + kSASlots;   // [2]
+  uint64_t* tmem_empty = tmem_full + 2;       // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+  const int num_kb = args.num_kb;
+  const int64_t u0 = s_range_start(sa, blockIdx.x), u1 = s_range_start(sa, blockIdx.x + 1);
+  const bool grouped = args.num_groups > 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_x);
+    tma_prefetch_desc(&tm_w);
+    if (args.s_rows > 0) tma_prefetch_desc(&tm_s);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_p[s], 1);
+      mbar_init(&empty_p[s], kSNT * 4 + 1);
+    }
+    for (int s = 0; s < kSASlots; ++s) {
+      mbar_init(&full_a[s], 4);
+      mbar_init(&empty_a[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], kSEpiWarps);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ======================= TMA producer =======================
+    const uint64_t pol_w = l2_policy_evict_first();  // streamed exactly once
+    const uint64_t pol_x = l2_policy_evict_last();   // every CTA re-reads the activations
+    constexpr int kWordsPerN = 16 * BITS / 32;
+    constexpr int kLoadsW = kSCtaN * kWordsPerN / 256;
+    const uint32_t tx_bytes = P::kXBytes + P::kPackedBytes + (uint32_t)args.s_rows * (kSCtaN * 2);
+    int tile = (int)(u0 / num_kb), kb = (int)(u0 % num_kb);
+    const int total = (int)(u1 - u0);
+    // Programmatic dependent launch: weights and scales do not depend on the predecessor grid, so
+    // the first pass over the ring streams them in before griddepcontrol.wait; activations after.
+    const int pre = min(total, kStages);
+    if (lane == 0) {
+      int t = tile, k = kb;
+      for (int i = 0; i < pre; ++i) {
+        uint8_t* w_dst = stages + i * P::kStageBytes + P::kXBytes;
+        mbar_arrive_expect_tx(&full_p[i], tx_bytes);
+#pragma unroll
+        for (int l = 0; l < kLoadsW; ++l)
+          tma_load_2d(w_dst + l * 4096, &tm_w, t * kSCtaN * kWordsPerN + l * 256, k * 4, &full_p[i], pol_w);
+        if (args.s_rows > 0)
+          tma_load_2d(w_dst + P::kPackedBytes, &tm_s, t * kSCtaN, (k * kStageK) >> args.group_shift, &full_p[i], pol_x);
+        if (++k == num_kb) k = 0, ++t;
+      }
+    }
+    pdl_wait();
+    if (lane == 0) {
+      int k = kb;
+      for (int i = 0; i < pre; ++i) {
+        tma_load_2d(stages + i * P::kStageBytes, &tm_x, k * kStageK, 0, &full_p[i], pol_x);
+        if (++k == num_kb) k = 0;
+      }
+    }
+    __syncwarp();
+    for (int i = 0; i < pre; ++i)
+      if (++kb == num_kb) kb = 0, ++tile;
+    int stage = pre == kStages ? 0 : pre;
+    uint32_t phase = pre == kStages ? 1 : 0;
+    for (int i = pre; i < total; ++i) {
+      mbar_wait_bounded(&empty_p[stage], phase ^ 1);
+      if (lane == 0) {
+        uint8_t* x_dst = stages + stage * P::kStageBytes;
+        uint8_t* w_dst = x_dst + P::kXBytes;
+        mbar_arrive_expect_tx(&full_p[stage], tx_bytes);
+        tma_load_2d(x_dst, &tm_x, kb * kStageK, 0, &full_p[stage], pol_x);
+#pragma unroll
+        for (int l = 0; l < kLoadsW; ++l)
+          tma_load_2d(w_dst + l * 4096, &tm_w, tile * kSCtaN * kWordsPerN + l * 256, kb * 4, &full_p[stage], pol_w);
+        if (args.s_rows > 0)
+          tma_load_2d(w_dst + P::kPackedBytes, &tm_s, tile * kSCtaN, (kb * kStageK) >> args.group_shift,
+                      &full_p[stage], pol_x);
+      }
+      __syncwarp();
+      if (++kb == num_kb) kb = 0, ++tile;
+      if (++stage == kStages) stage = 0, phase ^= 1;
+    }
+  } else if (warp == 1) {
+    // ======================= MMA issuer =======================
+    if (lane == 0) {
+      constexpr uint32_t idesc = instr_desc<KIND>(kTileN, BM);
+      int stage = 0;
+      uint32_t phase = 0, job = 0, piece = 0;
+      int64_t u = u0;
+      while (u < u1) {
+        const int kb0 = (int)(u % num_kb);
+        const int cnt = (int)min((int64_t)(num_kb - kb0), u1 - u);
+        const uint32_t buf = piece & 1;
+        if (piece >= 2) mbar_wait_bounded(&tmem_empty[buf], ((piece >> 1) - 1) & 1);
+        const uint32_t d_col = tmem_base + kSDCol + buf * kDCols;
+        for (int i = 0; i < cnt; ++i) {
+          mbar_wait_bounded(&full_p[stage], phase);  // activation tile landed
+          const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
+#pragma unroll
+          for (int h = 0; h < kSNT; ++h) {
+            const uint32_t aslot = job & (kSASlots - 1);
+            mbar_wait_bounded(&full_a[aslot], (job >> 3) & 1);
+            fence_after_sync();
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              mma_ts_f16(d_col + h * BM, tmem_base + aslot * kTmemAStageCols + k * 8, desc_advance(dx, k * 32),
+                         idesc, (i > 0 || k > 0) ? 1u : 0u);
+            mma_commit(&empty_a[aslot]);
+            ++job;
+          }
+          mma_commit(&empty_p[stage]);
+          if (++stage == kStages) stage = 0, phase ^= 1;
+        }
+        mma_commit(&tmem_full[buf]);
+        ++piece;
+        u += cnt;
+      }
+      pdl_launch_dependents();
+    }
+  } else if (warp < 2 + kSDequantWarps) {
+    // ======================= dequant teams =======================
+    const int team = (warp - 2) >> 2;
+    const int qd = warp & 3;          // TMEM quadrant = rows 32 qd .. 32 qd + 31 of the 128-row sub-tile
+    const int nt = qd >> 1;           // 64-column Marlin tile inside the sub-tile
+    const int j0 = (qd & 1) * 2;      // first of its two 16-row fragments
+    const int a_row = lane >> 2;
+    uint32_t sc[4];  // sc[2*jj + b]: scale of n = 64 nt + 16 (j0 + jj) + a_row + 8 b, in both halves
+#pragma unroll
+    for (int i = 0; i < 4; ++i) sc[i] = DT<T>::pack2(1.f, 1.f);
+    int sc_key = -1;  // (tile, sub-tile) the channel-wise scales in sc[] belong to
+    const uint32_t lane_src = smem_u32(stages) + P::kXBytes + lane * (BITS * 4) + (qd & 1) * (BITS * 2);
+    const uint32_t scale_src = smem_u32(stages) + P::kXBytes + P::kPackedBytes + (nt * 64 + 8 * a_row) * 2 +
+                               (qd & 1) * 8;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16);
+    int stage = 0;
+    uint32_t phase = 0, job = 0;
+    int tile = (int)(u0 / num_kb), kb = (int)(u0 % num_kb);
+    for (int64_t u = u0; u < u1; ++u) {
+#pragma unroll
+      for (int h = 0; h < kSNT; ++h, ++job) {
+        if ((int)(job & (kSTeams - 1)) != team) continue;
+        const uint32_t aslot = job & (kSASlots - 1);
+        mbar_wait_bounded(&full_p[stage], phase);
+        const uint32_t w_src = lane_src + stage * P::kStageBytes + chunk_off<BITS>(0, 2 * h + nt);
+        uint32_t words[4][BITS == 4 ? 2 : 4];
+#pragma unroll
+        for (int kt = 0; kt < 4; ++kt) {
+          if constexpr (BITS == 4) {
+            const uint2 v = lds64(w_src + kt * 1024);
+            words[kt][0] = v.x, words[kt][1] = v.y;
+          } else {
+            const uint4 v = lds128(w_src + kt * 1024);
+            words[kt][0] = v.x, words[kt][1] = v.y, words[kt][2] = v.z, words[kt][3] = v.w;
+          }
+        }
+        if (grouped) {
+          const uint2 v = lds64(scale_src + stage * P::kStageBytes + h * (kTileN * 2));
+          sc[0] = dup16(v.x, 0), sc[1] = dup16(v.x, 1), sc[2] = dup16(v.y, 0), sc[3] = dup16(v.y, 1);
+        } else if (sc_key != tile * kSNT + h) {
+          sc_key = tile * kSNT + h;
+          const uint16_t* s = reinterpret_cast<const uint16_t*>(args.scales);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int n = tile * kSCtaN + h * kTileN + nt * 64 + 16 * (j0 + (i >> 1)) + a_row + 8 * (i & 1);
+            const uint32_t v = n < args.n ? s[scale_pos_single(n)] : 0u;
+            sc[i] = v | (v << 16);
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_p[stage]);  // packed words + scales are in registers
+        mbar_wait_bounded(&empty_a[aslot], ((job >> 3) & 1) ^ 1);
+        fence_after_sync();
+        const uint32_t t_dst = t_lane + aslot * kTmemAStageCols;
+#pragma unroll
+        for (int kt = 0; kt < 4; ++kt) {
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj) {
+            uint32_t rg[4];
+            if constexpr (BITS == 4) {
+              unpack4<T>(words[kt][jj], rg);
+            } else {
+              unpack8<T>(words[kt][2 * jj], rg[0], rg[1]);
+              unpack8<T>(words[kt][2 * jj + 1], rg[2], rg[3]);
+            }
+            rg[0] = mul2<T>(rg[0], sc[2 * jj]);
+            rg[1] = mul2<T>(rg[1], sc[2 * jj]);
+            rg[2] = mul2<T>(rg[2], sc[2 * jj + 1]);
+            rg[3] = mul2<T>(rg[3], sc[2 * jj + 1]);
+            // rg = {b0 k-lo, b0 k-hi, b1 k-lo, b1 k-hi} -> st order {b0 lo, b1 lo, b0 hi, b1 hi}
+            tmem_st_16x128b_x2(t_dst + ((uint32_t)(16 * jj) << 16) + kt * 8, rg[0], rg[2], rg[1], rg[3]);
+          }
+        }
+        tmem_st_wait();
+        fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full_a[aslot]);
+      }
+      if (++kb == num_kb) kb = 0, ++tile;
+      if (++stage == kStages) stage = 0, phase ^= 1;
+    }
+  } else {
+    // ======================= epilogue + distributed split-K reduction =======================
+    const int qd = warp & 3;
+    const int et = (warp - 2 - kSDequantWarps) * 32 + lane;  // 0..127
+    const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16) + kSDCol;
+    constexpr int kSlotFloats = BM * kSCtaN;
+    float* my_slots = args.partial + (int64_t)blockIdx.x * 2 * kSlotFloats;
+    const int first_tile = (int)(u0 / num_kb);
+    int pend_tile[2];
+    int n_pend = 0;
+    uint32_t piece = 0;
+    int64_t u = u0;
+    while (u < u1) {
+      const int tile = (int)(u / num_kb), kb0 = (int)(u % num_kb);
+      const int cnt = (int)min((int64_t)(num_kb - kb0), u1 - u);
+      const bool whole = cnt == num_kb;
+      const uint32_t buf = piece & 1;
+      mbar_wait_bounded(&tmem_full[buf], (piece >> 1) & 1);
+      fence_after_sync();
+      float* slot = my_slots + (tile == first_tile ? 0 : kSlotFloats);
+#pragma unroll 1
+      for (int h = 0; h < kSNT; ++h) {
+        const int ncol = h * kTileN + qd * 32 + lane;
+        const int n = tile * kSCtaN + ncol;
+#pragma unroll 1
+        for (int c = 0; c < BM / 16; ++c) {
+          if (c * 16 >= args.m) break;
+          uint32_t rr[16];
+          tmem_ld16(t_lane + buf * kDCols + h * BM + c * 16, rr);
+          tmem_ld_wait();
+          if (whole) {
+            if (n < args.n) {
+              T* out = reinterpret_cast<T*>(args.c);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const int mm = c * 16 + j;
+                if (mm < args.m) out[(int64_t)mm * args.n + n] = DT<T>::from_f(__uint_as_float(rr[j]));
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int mm = c * 16 + j;
+              if (mm < args.m) slot[mm * kSCtaN + ncol] = __uint_as_float(rr[j]);
+            }
+          }
+        }
+      }
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+      if (!whole) {
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) atomicAdd(&args.locks[tile], 1);
+        pend_tile[n_pend++] = tile;
+      }
+      ++piece;
+      u += cnt;
+    }
+    // every partial of this CTA is published; now sum this CTA's slice of each tile it touched
+    for (int i = 0; i < n_pend; ++i) {
+      const int tile = pend_tile[i];
+      const int c_lo = s_cta_of_unit(sa, (int64_t)tile * num_kb);
+      const int c_hi = s_cta_of_unit(sa, (int64_t)(tile + 1) * num_kb - 1);
+      const int parts = c_hi - c_lo + 1;
+      if (et == 0) {
+        uint32_t spins = 0;
+        uint64_t t0 = 0;
+        while (ld_acquire_gpu(&args.locks[tile]) < parts) {
+          if ((++spins & 0x3ffu) == 0) {
+            const uint64_t t = global_timer_ns();
+            if (t0 == 0) t0 = t;
+            else if (t - t0 > kMbarTimeoutNs) __trap();
+          }
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      __threadfence();
+      // chunks of 4 consecutive columns of one token row; contributor r sums chunks [q0, q1)
+      const int chunks = args.m * (kSCtaN / 4);
+      const int per = (chunks + parts - 1) / parts;
+      const int r = (int)blockIdx.x - c_lo;
+      const int q0 = r * per, q1 = min(chunks, q0 + per);
+      for (int q = q0 + et; q < q1; q += 128) {
+        const int mm = q / (kSCtaN / 4), ncol = (q % (kSCtaN / 4)) * 4;
+        const int n = tile * kSCtaN + ncol;
+        if (n >= args.n) continue;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int c = c_lo; c <= c_hi; ++c) {
+          const int c_first = (int)(s_range_start(sa, c) / num_kb);
+          const float* src = args.partial + ((int64_t)c * 2 + (c_first == tile ? 0 : 1)) * kSlotFloats +
+                             mm * kSCtaN + ncol;
+          const float4 v = __ldcg(reinterpret_cast<const float4*>(src));
+          acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+        }
+        uint2 o;
+        o.x = DT<T>::pack2(acc.x, acc.y);
+        o.y = DT<T>::pack2(acc.z, acc.w);
+        *reinterpret_cast<uint2*>(reinterpret_cast<T*>(args.c) + (int64_t)mm * args.n + n) = o;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (et == 0) {
+        const int old = atomicAdd(&args.locks[tile], 1);
+        if (old == 2 * parts - 1) args.locks[tile] = 0;  // last reader hands the counter back as zero
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    fence_after_sync();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+inline int64_t stream_ws_bytes(int m) {
+  const int bm = m <= 16 ? 16 : m <= 32 ? 32 : 64;
+  return (int64_t)num_sms() * 2 * bm * kSCtaN * 4;
+}
+
+template <int BITS, int BM, typename T>
+int launch_stream(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
+  using P = PlanS<BITS, BM>;
+  CUtensorMap tm_x;
+  int rc = make_tmap_2d(&tm_x, p.a, (uint64_t)p.size_m, (uint64_t)p.size_k, (uint64_t)p.lda * 2, 2, BM);
+  if (rc != B200_OK) return rc;
+  MarlinArgs a{};
+  a.c = p.c;
+  a.w = p.b_q_weight;
+  a.scales = p.b_scales;
+  a.m = p.size_m, a.n = p.size_n, a.k = p.size_k;
+  a.num_groups = p.num_groups;
+  a.group_size = p.num_groups > 1 ? p.size_k / p.num_groups : p.size_k;
+  a.group_shift = (a.group_size & (a.group_size - 1)) == 0 ? __builtin_ctz(a.group_size) : -1;
+  a.num_kb = p.size_k / kStageK;
+  CUtensorMap tm_w, tm_s;
+  rc = make_weight_maps(p, p.num_groups > 1, kSCtaN, &tm_w, &tm_s, &a);
+  if (rc != B200_OK) return rc;
+  StreamArgs sa{};
+  sa.n_tiles = (p.size_n + kSCtaN - 1) / kSCtaN;
+  sa.units = (int64_t)sa.n_tiles * a.num_kb;
+  sa.grid = (int)(sa.units < num_sms() ? sa.units : num_sms());
+  a.partial = reinterpret_cast<float*>(p.splitk_ws);
+  a.locks = p.workspace;
+  auto kern = marlin_gemm_stream_kernel<BITS, BM, T>;
+  static size_t smem_configured[kMaxDevices] = {};
+  if (ensure_dyn_smem(kern, P::kBytes, smem_configured) != cudaSuccess) {
+    cudaGetLastError();
+    set_error("gptq_marlin_gemm: cannot reserve %d B of shared memory", (int)P::kBytes);
+    return B200_ECUDA;
+  }
+  cudaError_t le = launch_pdl(kern, dim3(sa.grid), dim3(kSThreads), (size_t)P::kBytes, st, tm_x, tm_w, tm_s, a, sa);
+  if (le != cudaSuccess) {
+    cudaGetLastError();
+    set_error("gptq_marlin_gemm: launch failed: %s", cudaGetErrorString(le));
+    return B200_ECUDA;
+  }
+  return B200_OK;
+}
