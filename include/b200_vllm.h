@@ -228,6 +228,10 @@ B200_API int64_t b200_gptq_marlin_gemm_workspace_bytes(int32_t m, int32_t n, int
 /* test hook: out [size_k, size_n] (dtype) = dequantised weights, produced by the same unpack /
  * scale device code the GEMM uses (bit-exact against the reference's w_ref,
  * quant_utils.py:73). No act-order. */
+/* debug only: cycle accounting of the stream-K decode kernel; returns the number of uint64 copied
+ * (0 unless built with -DB200_STREAM_PROF) */
+B200_API int b200_debug_stream_prof(unsigned long long* dst, int32_t n);
+
 B200_API int b200_marlin_dequant(void* out, const uint32_t* b_q_weight, const void* b_scales,
                                  int32_t size_k, int32_t size_n, int32_t num_groups,
                                  int32_t num_bits, int32_t dtype, void* stream);

@@ -30,7 +30,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
     f"-I{INC}", f"-I{CSRC}",
-]
+] + os.environ.get("B200_EXTRA_NVCC_FLAGS", "").split()
 
 
 def _nvcc() -> str:

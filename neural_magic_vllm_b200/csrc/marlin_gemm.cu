@@ -980,6 +980,19 @@ int b200_gptq_marlin_gemm(const b200_gptq_marlin_gemm_params* pp, void* stream) 
   return B200_EINVAL;
 }
 
+// debug: per-CTA cycle accounting of the stream-K decode kernel (all zeros unless the library was
+// built with -DB200_STREAM_PROF).  dst = 160 x 32 uint64 on the host.
+int b200_debug_stream_prof(unsigned long long* dst, int32_t n) {
+#ifdef B200_STREAM_PROF
+  if (n > 160 * 32) n = 160 * 32;
+  return cudaMemcpyFromSymbol(dst, b200::g_stream_prof, (size_t)n * 8) == cudaSuccess ? n : -1;
+#else
+  (void)dst;
+  (void)n;
+  return 0;
+#endif
+}
+
 int b200_marlin_dequant(void* out, const uint32_t* b_q_weight, const void* b_scales, int32_t size_k,
                         int32_t size_n, int32_t num_groups, int32_t num_bits, int32_t dtype,
                         void* stream) {

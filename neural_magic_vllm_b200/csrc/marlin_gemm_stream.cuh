@@ -51,6 +51,22 @@ struct PlanS {
   static_assert(kSDCol + 2 * kSNT * BM <= 512, "TMEM columns");
 };
 
+// Optional cycle accounting per role (build with -DB200_STREAM_PROF; read back through
+// b200_debug_stream_prof): where each warp role of one CTA spends its time.
+#ifdef B200_STREAM_PROF
+__device__ unsigned long long g_stream_prof[160 * 32];
+#define SPROF_DECL long long sp_t = clock64(), sp_n; unsigned long long sp_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}
+#define SPROF(i) (sp_n = clock64(), sp_acc[i] += (unsigned long long)(sp_n - sp_t), sp_t = sp_n)
+#define SPROF_FLUSH(base)                                                              \
+  do {                                                                                 \
+    for (int sp_i = 0; sp_i < 8; ++sp_i) g_stream_prof[blockIdx.x * 32 + (base) + sp_i] = sp_acc[sp_i]; \
+  } while (0)
+#else
+#define SPROF_DECL
+#define SPROF(i)
+#define SPROF_FLUSH(base)
+#endif
+
 struct StreamArgs {
   int n_tiles;      // ceil(n / 256)
   int grid;         // CTAs = ranges
@@ -155,8 +171,11 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       if (++kb == num_kb) kb = 0, ++tile;
     int stage = pre == kStages ? 0 : pre;
     uint32_t phase = pre == kStages ? 1 : 0;
+    SPROF_DECL;
     for (int i = pre; i < total; ++i) {
+      SPROF(1);
       mbar_wait_bounded(&empty_p[stage], phase ^ 1);
+      SPROF(0);
       if (lane == 0) {
         uint8_t* x_dst = stages + stage * P::kStageBytes;
         uint8_t* w_dst = x_dst + P::kXBytes;
@@ -173,6 +192,8 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       if (++kb == num_kb) kb = 0, ++tile;
       if (++stage == kStages) stage = 0, phase ^= 1;
     }
+    SPROF(1);
+    if (lane == 0) SPROF_FLUSH(16);
   } else if (warp == 1) {
     // ======================= MMA issuer =======================
     if (lane == 0) {
@@ -180,19 +201,26 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       int stage = 0;
       uint32_t phase = 0, job = 0, piece = 0;
       int64_t u = u0;
+      SPROF_DECL;
       while (u < u1) {
         const int kb0 = (int)(u % num_kb);
         const int cnt = (int)min((int64_t)(num_kb - kb0), u1 - u);
         const uint32_t buf = piece & 1;
+        SPROF(2);
         if (piece >= 2) mbar_wait_bounded(&tmem_empty[buf], ((piece >> 1) - 1) & 1);
+        SPROF(3);
         const uint32_t d_col = tmem_base + kSDCol + buf * kDCols;
         for (int i = 0; i < cnt; ++i) {
+          SPROF(2);
           mbar_wait_bounded(&full_p[stage], phase);  // activation tile landed
+          SPROF(0);
           const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
 #pragma unroll
           for (int h = 0; h < kSNT; ++h) {
             const uint32_t aslot = job & (kSASlots - 1);
+            SPROF(2);
             mbar_wait_bounded(&full_a[aslot], (job >> 3) & 1);
+            SPROF(1);
             fence_after_sync();
 #pragma unroll
             for (int k = 0; k < 4; ++k)
@@ -209,6 +237,8 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
         u += cnt;
       }
       pdl_launch_dependents();
+      SPROF(2);
+      SPROF_FLUSH(0);
     }
   } else if (warp < 2 + kSDequantWarps) {
     // ======================= dequant teams =======================
@@ -228,12 +258,15 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     int stage = 0;
     uint32_t phase = 0, job = 0;
     int tile = (int)(u0 / num_kb), kb = (int)(u0 % num_kb);
+    SPROF_DECL;
     for (int64_t u = u0; u < u1; ++u) {
 #pragma unroll
       for (int h = 0; h < kSNT; ++h, ++job) {
         if ((int)(job & (kSTeams - 1)) != team) continue;
         const uint32_t aslot = job & (kSASlots - 1);
+        SPROF(5);
         mbar_wait_bounded(&full_p[stage], phase);
+        SPROF(0);
         const uint32_t w_src = lane_src + stage * P::kStageBytes + chunk_off<BITS>(0, 2 * h + nt);
         uint32_t words[4][BITS == 4 ? 2 : 4];
 #pragma unroll
@@ -261,7 +294,9 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty_p[stage]);  // packed words + scales are in registers
+        SPROF(1);
         mbar_wait_bounded(&empty_a[aslot], ((job >> 3) & 1) ^ 1);
+        SPROF(2);
         fence_after_sync();
         const uint32_t t_dst = t_lane + aslot * kTmemAStageCols;
 #pragma unroll
@@ -283,14 +318,18 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
             tmem_st_16x128b_x2(t_dst + ((uint32_t)(16 * jj) << 16) + kt * 8, rg[0], rg[2], rg[1], rg[3]);
           }
         }
+        SPROF(3);
         tmem_st_wait();
         fence_before_sync();
         __syncwarp();
         if (lane == 0) mbar_arrive(&full_a[aslot]);
+        SPROF(4);
       }
       if (++kb == num_kb) kb = 0, ++tile;
       if (++stage == kStages) stage = 0, phase ^= 1;
     }
+    SPROF(5);
+    if (warp == 2 && lane == 0) SPROF_FLUSH(8);
   } else {
     // ======================= epilogue + distributed split-K reduction =======================
     const int qd = warp & 3;
@@ -303,12 +342,15 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     int n_pend = 0;
     uint32_t piece = 0;
     int64_t u = u0;
+    SPROF_DECL;
     while (u < u1) {
       const int tile = (int)(u / num_kb), kb0 = (int)(u % num_kb);
       const int cnt = (int)min((int64_t)(num_kb - kb0), u1 - u);
       const bool whole = cnt == num_kb;
       const uint32_t buf = piece & 1;
+      SPROF(1);
       mbar_wait_bounded(&tmem_full[buf], (piece >> 1) & 1);
+      SPROF(0);
       fence_after_sync();
       float* slot = my_slots + (tile == first_tile ? 0 : kSlotFloats);
 #pragma unroll 1
@@ -357,6 +399,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       const int c_lo = s_cta_of_unit(sa, (int64_t)tile * num_kb);
       const int c_hi = s_cta_of_unit(sa, (int64_t)(tile + 1) * num_kb - 1);
       const int parts = c_hi - c_lo + 1;
+      SPROF(1);
       if (et == 0) {
         uint32_t spins = 0;
         uint64_t t0 = 0;
@@ -369,6 +412,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
         }
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
+      SPROF(2);
       __threadfence();
       // chunks of 4 consecutive columns of one token row; contributor r sums chunks [q0, q1)
       const int chunks = args.m * (kSCtaN / 4);
@@ -397,7 +441,10 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
         const int old = atomicAdd(&args.locks[tile], 1);
         if (old == 2 * parts - 1) args.locks[tile] = 0;  // last reader hands the counter back as zero
       }
+      SPROF(3);
     }
+    SPROF(1);
+    if (et == 0) SPROF_FLUSH(24);
   }
   __syncthreads();
   if (warp == 1) {
