@@ -20,7 +20,7 @@ ROLES = {
     "mma": (0, ["wait full_p", "wait full_a", "issue/other", "wait tmem_empty"]),
     "dequant(warp2)": (8, ["wait full_p", "lds+release", "wait empty_a", "unpack+st", "st_wait+arrive", "loop/skip"]),
     "producer": (16, ["wait empty_p", "issue/other"]),
-    "epilogue": (24, ["ld+store", "wait tmem_full/other", "spin+barrier", "reduce"]),
+    "epilogue": (24, ["wait tmem_full", "ld+store+publish", "spin+barrier", "reduce"]),
 }
 
 

@@ -895,7 +895,8 @@ int dispatch_bm(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64
   const int gsz = p.num_groups > 1 ? p.size_k / p.num_groups : 0;
   const bool one_group_per_stage = p.num_groups == 1 || (gsz % kStageK == 0 && (gsz & (gsz - 1)) == 0);
   if (!ACT && one_group_per_stage && p.size_m <= 64 && p.workspace != nullptr && p.splitk_ws != nullptr &&
-      p.splitk_ws_bytes >= stream_ws_bytes(p.size_m) && decode_kernel_choice() == 0) {
+      p.splitk_ws_bytes >= stream_ws_bytes(p.size_m) && decode_kernel_choice() == 0 &&
+      ((int64_t)(p.size_n + kSCtaN - 1) / kSCtaN * (p.size_k / kStageK) + 1) * num_sms() < (1ll << 31)) {
     switch (pick_bm(p.size_m)) {
       case 16: return launch_stream<BITS, 16, T>(p, st);
       case 32: return launch_stream<BITS, 32, T>(p, st);

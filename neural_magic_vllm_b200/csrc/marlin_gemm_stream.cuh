@@ -70,13 +70,16 @@ __device__ unsigned long long g_stream_prof[160 * 32];
 struct StreamArgs {
   int n_tiles;      // ceil(n / 256)
   int grid;         // CTAs = ranges
-  int64_t units;    // n_tiles * num_kb
+  int units;        // n_tiles * num_kb
 };
 
 // range start of CTA c; CTA that owns unit u
-__device__ __forceinline__ int64_t s_range_start(const StreamArgs& s, int c) { return (int64_t)c * s.units / s.grid; }
-__device__ __forceinline__ int s_cta_of_unit(const StreamArgs& s, int64_t u) {
-  return (int)(((u + 1) * s.grid - 1) / s.units);
+__device__ __forceinline__ uint32_t s_range_start(const StreamArgs& s, int c) {
+  return (uint32_t)c * (uint32_t)s.units / (uint32_t)s.grid;
+}
+// (the host guarantees (units + 1) * grid < 2^31: 32-bit divisions)
+__device__ __forceinline__ int s_cta_of_unit(const StreamArgs& s, int u) {
+  return (int)(((uint32_t)(u + 1) * (uint32_t)s.grid - 1u) / (uint32_t)s.units);
 }
 
 __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
@@ -104,9 +107,12 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
   uint64_t* tmem_empty = tmem_full + 2;       // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
+  // warp-uniform by construction: say so, so that role code keeps its operands in uniform registers
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int num_kb = args.num_kb;
-  const int64_t u0 = s_range_start(sa, blockIdx.x), u1 = s_range_start(sa, blockIdx.x + 1);
+  const int u0 = (int)s_range_start(sa, blockIdx.x), u1 = (int)s_range_start(sa, blockIdx.x + 1);
+  const int total = u1 - u0;
+  const int tile0 = u0 / num_kb, kb0 = u0 - tile0 * num_kb;
   const bool grouped = args.num_groups > 1;
 
   if (warp == 0 && lane == 0) {
@@ -131,44 +137,44 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0) {
     // ======================= TMA producer =======================
+    // The whole warp runs the loops (uniform control flow: coordinates, shared-memory addresses and
+    // barrier addresses stay in uniform registers); one elected lane issues.
+    const bool leader = elect_one();
     const uint64_t pol_w = l2_policy_evict_first();  // streamed exactly once
     const uint64_t pol_x = l2_policy_evict_last();   // every CTA re-reads the activations
     constexpr int kWordsPerN = 16 * BITS / 32;
     constexpr int kLoadsW = kSCtaN * kWordsPerN / 256;
     const uint32_t tx_bytes = P::kXBytes + P::kPackedBytes + (uint32_t)args.s_rows * (kSCtaN * 2);
-    int tile = (int)(u0 / num_kb), kb = (int)(u0 % num_kb);
-    const int total = (int)(u1 - u0);
+    const bool staged_scales = args.s_rows > 0;
     // Programmatic dependent launch: weights and scales do not depend on the predecessor grid, so
     // the first pass over the ring streams them in before griddepcontrol.wait; activations after.
     const int pre = min(total, kStages);
-    if (lane == 0) {
-      int t = tile, k = kb;
+    {
+      int t = tile0, k = kb0;
       for (int i = 0; i < pre; ++i) {
         uint8_t* w_dst = stages + i * P::kStageBytes + P::kXBytes;
-        mbar_arrive_expect_tx(&full_p[i], tx_bytes);
+        if (leader) {
+          mbar_arrive_expect_tx(&full_p[i], tx_bytes);
 #pragma unroll
-        for (int l = 0; l < kLoadsW; ++l)
-          tma_load_2d(w_dst + l * 4096, &tm_w, t * kSCtaN * kWordsPerN + l * 256, k * 4, &full_p[i], pol_w);
-        if (args.s_rows > 0)
-          tma_load_2d(w_dst + P::kPackedBytes, &tm_s, t * kSCtaN, (k * kStageK) >> args.group_shift, &full_p[i], pol_x);
+          for (int l = 0; l < kLoadsW; ++l)
+            tma_load_2d(w_dst + l * 4096, &tm_w, t * (kSCtaN * kWordsPerN) + l * 256, k * 4, &full_p[i], pol_w);
+          if (staged_scales)
+            tma_load_2d(w_dst + P::kPackedBytes, &tm_s, t * kSCtaN, (k * kStageK) >> args.group_shift, &full_p[i],
+                        pol_x);
+        }
         if (++k == num_kb) k = 0, ++t;
       }
     }
     pdl_wait();
-    if (lane == 0) {
-      int k = kb;
-      for (int i = 0; i < pre; ++i) {
-        tma_load_2d(stages + i * P::kStageBytes, &tm_x, k * kStageK, 0, &full_p[i], pol_x);
-        if (++k == num_kb) k = 0;
-      }
-    }
-    __syncwarp();
-    for (int i = 0; i < pre; ++i)
+    int tile = tile0, kb = kb0;
+    for (int i = 0; i < pre; ++i) {
+      if (leader) tma_load_2d(stages + i * P::kStageBytes, &tm_x, kb * kStageK, 0, &full_p[i], pol_x);
       if (++kb == num_kb) kb = 0, ++tile;
+    }
     int stage = pre == kStages ? 0 : pre;
     uint32_t phase = pre == kStages ? 1 : 0;
     SPROF_DECL;
@@ -176,19 +182,18 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       SPROF(1);
       mbar_wait_bounded(&empty_p[stage], phase ^ 1);
       SPROF(0);
-      if (lane == 0) {
-        uint8_t* x_dst = stages + stage * P::kStageBytes;
-        uint8_t* w_dst = x_dst + P::kXBytes;
+      uint8_t* x_dst = stages + stage * P::kStageBytes;
+      uint8_t* w_dst = x_dst + P::kXBytes;
+      if (leader) {
         mbar_arrive_expect_tx(&full_p[stage], tx_bytes);
         tma_load_2d(x_dst, &tm_x, kb * kStageK, 0, &full_p[stage], pol_x);
 #pragma unroll
         for (int l = 0; l < kLoadsW; ++l)
-          tma_load_2d(w_dst + l * 4096, &tm_w, tile * kSCtaN * kWordsPerN + l * 256, kb * 4, &full_p[stage], pol_w);
-        if (args.s_rows > 0)
+          tma_load_2d(w_dst + l * 4096, &tm_w, tile * (kSCtaN * kWordsPerN) + l * 256, kb * 4, &full_p[stage], pol_w);
+        if (staged_scales)
           tma_load_2d(w_dst + P::kPackedBytes, &tm_s, tile * kSCtaN, (kb * kStageK) >> args.group_shift,
                       &full_p[stage], pol_x);
       }
-      __syncwarp();
       if (++kb == num_kb) kb = 0, ++tile;
       if (++stage == kStages) stage = 0, phase ^= 1;
     }
@@ -196,53 +201,59 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     if (lane == 0) SPROF_FLUSH(16);
   } else if (warp == 1) {
     // ======================= MMA issuer =======================
-    if (lane == 0) {
-      constexpr uint32_t idesc = instr_desc<KIND>(kTileN, BM);
-      int stage = 0;
-      uint32_t phase = 0, job = 0, piece = 0;
-      int64_t u = u0;
-      SPROF_DECL;
-      while (u < u1) {
-        const int kb0 = (int)(u % num_kb);
-        const int cnt = (int)min((int64_t)(num_kb - kb0), u1 - u);
-        const uint32_t buf = piece & 1;
+    // uniform control flow again: all lanes wait on the barriers, one elected lane issues the MMAs
+    // with descriptors / TMEM addresses that were computed in uniform registers
+    const bool leader = elect_one();
+    constexpr uint32_t idesc = instr_desc<KIND>(kTileN, BM);
+    int stage = 0;
+    uint32_t phase = 0, job = 0, piece = 0;
+    int done = 0, kb = kb0;
+    SPROF_DECL;
+    while (done < total) {
+      const int cnt = min(num_kb - kb, total - done);
+      const uint32_t buf = piece & 1;
+      SPROF(2);
+      if (piece >= 2) mbar_wait_bounded(&tmem_empty[buf], ((piece >> 1) - 1) & 1);
+      SPROF(3);
+      const uint32_t d_col = tmem_base + kSDCol + buf * kDCols;
+      for (int i = 0; i < cnt; ++i) {
         SPROF(2);
-        if (piece >= 2) mbar_wait_bounded(&tmem_empty[buf], ((piece >> 1) - 1) & 1);
-        SPROF(3);
-        const uint32_t d_col = tmem_base + kSDCol + buf * kDCols;
-        for (int i = 0; i < cnt; ++i) {
-          SPROF(2);
-          mbar_wait_bounded(&full_p[stage], phase);  // activation tile landed
-          SPROF(0);
-          const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
+        mbar_wait_bounded(&full_p[stage], phase);  // activation tile landed
+        SPROF(0);
+        const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
 #pragma unroll
-          for (int h = 0; h < kSNT; ++h) {
-            const uint32_t aslot = job & (kSASlots - 1);
-            SPROF(2);
-            mbar_wait_bounded(&full_a[aslot], (job >> 3) & 1);
-            SPROF(1);
-            fence_after_sync();
+        for (int h = 0; h < kSNT; ++h) {
+          const uint32_t aslot = job & (kSASlots - 1);
+          SPROF(2);
+          mbar_wait_bounded(&full_a[aslot], (job >> 3) & 1);
+          SPROF(1);
+          fence_after_sync();
+          const uint32_t a_col = tmem_base + aslot * kTmemAStageCols;
+          if (leader) {
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              mma_ts_f16(d_col + h * BM, tmem_base + aslot * kTmemAStageCols + k * 8, desc_advance(dx, k * 32),
-                         idesc, (i > 0 || k > 0) ? 1u : 0u);
+              mma_ts_f16(d_col + h * BM, a_col + k * 8, desc_advance(dx, k * 32), idesc, (i > 0 || k > 0) ? 1u : 0u);
             mma_commit(&empty_a[aslot]);
-            ++job;
           }
-          mma_commit(&empty_p[stage]);
-          if (++stage == kStages) stage = 0, phase ^= 1;
+          ++job;
         }
-        mma_commit(&tmem_full[buf]);
-        ++piece;
-        u += cnt;
+        if (leader) mma_commit(&empty_p[stage]);
+        if (++stage == kStages) stage = 0, phase ^= 1;
       }
-      pdl_launch_dependents();
-      SPROF(2);
-      SPROF_FLUSH(0);
+      if (leader) mma_commit(&tmem_full[buf]);
+      ++piece;
+      done += cnt;
+      kb = 0;
     }
+    pdl_launch_dependents();
+    SPROF(2);
+    if (lane == 0) SPROF_FLUSH(0);
   } else if (warp < 2 + kSDequantWarps) {
     // ======================= dequant teams =======================
+    // job (unit i, sub-tile h) has index 2 i + h and goes to team (2 i + h) % 4: team t takes
+    // sub-tile t & 1 of the units i = t >> 1 (mod 2)
     const int team = (warp - 2) >> 2;
+    const int h = team & 1;
     const int qd = warp & 3;          // TMEM quadrant = rows 32 qd .. 32 qd + 31 of the 128-row sub-tile
     const int nt = qd >> 1;           // 64-column Marlin tile inside the sub-tile
     const int j0 = (qd & 1) * 2;      // first of its two 16-row fragments
@@ -250,83 +261,85 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     uint32_t sc[4];  // sc[2*jj + b]: scale of n = 64 nt + 16 (j0 + jj) + a_row + 8 b, in both halves
 #pragma unroll
     for (int i = 0; i < 4; ++i) sc[i] = DT<T>::pack2(1.f, 1.f);
-    int sc_key = -1;  // (tile, sub-tile) the channel-wise scales in sc[] belong to
-    const uint32_t lane_src = smem_u32(stages) + P::kXBytes + lane * (BITS * 4) + (qd & 1) * (BITS * 2);
-    const uint32_t scale_src = smem_u32(stages) + P::kXBytes + P::kPackedBytes + (nt * 64 + 8 * a_row) * 2 +
+    int sc_tile = -1;  // tile the channel-wise scales in sc[] belong to
+    const uint32_t lane_src = smem_u32(stages) + P::kXBytes + chunk_off<BITS>(0, 2 * h + nt) + lane * (BITS * 4) +
+                              (qd & 1) * (BITS * 2);
+    const uint32_t scale_src = smem_u32(stages) + P::kXBytes + P::kPackedBytes + (h * kTileN + nt * 64 + 8 * a_row) * 2 +
                                (qd & 1) * 8;
     const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16);
-    int stage = 0;
-    uint32_t phase = 0, job = 0;
-    int tile = (int)(u0 / num_kb), kb = (int)(u0 % num_kb);
+    int i = team >> 1;
+    int stage = i % kStages;
+    uint32_t phase = (i / kStages) & 1;
+    int tile = tile0, kb = kb0 + i;
+    while (kb >= num_kb) kb -= num_kb, ++tile;
     SPROF_DECL;
-    for (int64_t u = u0; u < u1; ++u) {
+    for (; i < total; i += 2) {
+      const uint32_t job = 2 * i + h;
+      const uint32_t aslot = job & (kSASlots - 1);
+      SPROF(5);
+      mbar_wait_bounded(&full_p[stage], phase);
+      SPROF(0);
+      const uint32_t w_src = lane_src + stage * P::kStageBytes;
+      uint32_t words[4][BITS == 4 ? 2 : 4];
 #pragma unroll
-      for (int h = 0; h < kSNT; ++h, ++job) {
-        if ((int)(job & (kSTeams - 1)) != team) continue;
-        const uint32_t aslot = job & (kSASlots - 1);
-        SPROF(5);
-        mbar_wait_bounded(&full_p[stage], phase);
-        SPROF(0);
-        const uint32_t w_src = lane_src + stage * P::kStageBytes + chunk_off<BITS>(0, 2 * h + nt);
-        uint32_t words[4][BITS == 4 ? 2 : 4];
-#pragma unroll
-        for (int kt = 0; kt < 4; ++kt) {
-          if constexpr (BITS == 4) {
-            const uint2 v = lds64(w_src + kt * 1024);
-            words[kt][0] = v.x, words[kt][1] = v.y;
-          } else {
-            const uint4 v = lds128(w_src + kt * 1024);
-            words[kt][0] = v.x, words[kt][1] = v.y, words[kt][2] = v.z, words[kt][3] = v.w;
-          }
+      for (int kt = 0; kt < 4; ++kt) {
+        if constexpr (BITS == 4) {
+          const uint2 v = lds64(w_src + kt * 1024);
+          words[kt][0] = v.x, words[kt][1] = v.y;
+        } else {
+          const uint4 v = lds128(w_src + kt * 1024);
+          words[kt][0] = v.x, words[kt][1] = v.y, words[kt][2] = v.z, words[kt][3] = v.w;
         }
-        if (grouped) {
-          const uint2 v = lds64(scale_src + stage * P::kStageBytes + h * (kTileN * 2));
-          sc[0] = dup16(v.x, 0), sc[1] = dup16(v.x, 1), sc[2] = dup16(v.y, 0), sc[3] = dup16(v.y, 1);
-        } else if (sc_key != tile * kSNT + h) {
-          sc_key = tile * kSNT + h;
-          const uint16_t* s = reinterpret_cast<const uint16_t*>(args.scales);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int n = tile * kSCtaN + h * kTileN + nt * 64 + 16 * (j0 + (i >> 1)) + a_row + 8 * (i & 1);
-            const uint32_t v = n < args.n ? s[scale_pos_single(n)] : 0u;
-            sc[i] = v | (v << 16);
-          }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty_p[stage]);  // packed words + scales are in registers
-        SPROF(1);
-        mbar_wait_bounded(&empty_a[aslot], ((job >> 3) & 1) ^ 1);
-        SPROF(2);
-        fence_after_sync();
-        const uint32_t t_dst = t_lane + aslot * kTmemAStageCols;
-#pragma unroll
-        for (int kt = 0; kt < 4; ++kt) {
-#pragma unroll
-          for (int jj = 0; jj < 2; ++jj) {
-            uint32_t rg[4];
-            if constexpr (BITS == 4) {
-              unpack4<T>(words[kt][jj], rg);
-            } else {
-              unpack8<T>(words[kt][2 * jj], rg[0], rg[1]);
-              unpack8<T>(words[kt][2 * jj + 1], rg[2], rg[3]);
-            }
-            rg[0] = mul2<T>(rg[0], sc[2 * jj]);
-            rg[1] = mul2<T>(rg[1], sc[2 * jj]);
-            rg[2] = mul2<T>(rg[2], sc[2 * jj + 1]);
-            rg[3] = mul2<T>(rg[3], sc[2 * jj + 1]);
-            // rg = {b0 k-lo, b0 k-hi, b1 k-lo, b1 k-hi} -> st order {b0 lo, b1 lo, b0 hi, b1 hi}
-            tmem_st_16x128b_x2(t_dst + ((uint32_t)(16 * jj) << 16) + kt * 8, rg[0], rg[2], rg[1], rg[3]);
-          }
-        }
-        SPROF(3);
-        tmem_st_wait();
-        fence_before_sync();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&full_a[aslot]);
-        SPROF(4);
       }
-      if (++kb == num_kb) kb = 0, ++tile;
-      if (++stage == kStages) stage = 0, phase ^= 1;
+      if (grouped) {
+        const uint2 v = lds64(scale_src + stage * P::kStageBytes);
+        sc[0] = dup16(v.x, 0), sc[1] = dup16(v.x, 1), sc[2] = dup16(v.y, 0), sc[3] = dup16(v.y, 1);
+      } else if (sc_tile != tile) {
+        sc_tile = tile;
+        const uint16_t* s = reinterpret_cast<const uint16_t*>(args.scales);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int n = tile * kSCtaN + h * kTileN + nt * 64 + 16 * (j0 + (e >> 1)) + a_row + 8 * (e & 1);
+          const uint32_t v = n < args.n ? s[scale_pos_single(n)] : 0u;
+          sc[e] = v | (v << 16);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_p[stage]);  // packed words + scales are in registers
+      SPROF(1);
+      mbar_wait_bounded(&empty_a[aslot], ((job >> 3) & 1) ^ 1);
+      SPROF(2);
+      fence_after_sync();
+      const uint32_t t_dst = t_lane + aslot * kTmemAStageCols;
+#pragma unroll
+      for (int kt = 0; kt < 4; ++kt) {
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          uint32_t rg[4];
+          if constexpr (BITS == 4) {
+            unpack4<T>(words[kt][jj], rg);
+          } else {
+            unpack8<T>(words[kt][2 * jj], rg[0], rg[1]);
+            unpack8<T>(words[kt][2 * jj + 1], rg[2], rg[3]);
+          }
+          rg[0] = mul2<T>(rg[0], sc[2 * jj]);
+          rg[1] = mul2<T>(rg[1], sc[2 * jj]);
+          rg[2] = mul2<T>(rg[2], sc[2 * jj + 1]);
+          rg[3] = mul2<T>(rg[3], sc[2 * jj + 1]);
+          // rg = {b0 k-lo, b0 k-hi, b1 k-lo, b1 k-hi} -> st order {b0 lo, b1 lo, b0 hi, b1 hi}
+          tmem_st_16x128b_x2(t_dst + ((uint32_t)(16 * jj) << 16) + kt * 8, rg[0], rg[2], rg[1], rg[3]);
+        }
+      }
+      SPROF(3);
+      tmem_st_wait();
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full_a[aslot]);
+      SPROF(4);
+      kb += 2;
+      while (kb >= num_kb) kb -= num_kb, ++tile;
+      stage += 2;
+      if (stage >= kStages) stage -= kStages, phase ^= 1;
     }
     SPROF(5);
     if (warp == 2 && lane == 0) SPROF_FLUSH(8);
@@ -337,22 +350,20 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16) + kSDCol;
     constexpr int kSlotFloats = BM * kSCtaN;
     float* my_slots = args.partial + (int64_t)blockIdx.x * 2 * kSlotFloats;
-    const int first_tile = (int)(u0 / num_kb);
     int pend_tile[2];
     int n_pend = 0;
     uint32_t piece = 0;
-    int64_t u = u0;
+    int done = 0, tile = tile0, kb = kb0;
     SPROF_DECL;
-    while (u < u1) {
-      const int tile = (int)(u / num_kb), kb0 = (int)(u % num_kb);
-      const int cnt = (int)min((int64_t)(num_kb - kb0), u1 - u);
+    while (done < total) {
+      const int cnt = min(num_kb - kb, total - done);
       const bool whole = cnt == num_kb;
       const uint32_t buf = piece & 1;
       SPROF(1);
       mbar_wait_bounded(&tmem_full[buf], (piece >> 1) & 1);
       SPROF(0);
       fence_after_sync();
-      float* slot = my_slots + (tile == first_tile ? 0 : kSlotFloats);
+      float* slot = my_slots + (tile == tile0 ? 0 : kSlotFloats);
 #pragma unroll 1
       for (int h = 0; h < kSNT; ++h) {
         const int ncol = h * kTileN + qd * 32 + lane;
@@ -391,19 +402,25 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
         pend_tile[n_pend++] = tile;
       }
       ++piece;
-      u += cnt;
+      done += cnt;
+      kb = 0;
+      ++tile;
     }
     // every partial of this CTA is published; now sum this CTA's slice of each tile it touched
     for (int i = 0; i < n_pend; ++i) {
-      const int tile = pend_tile[i];
-      const int c_lo = s_cta_of_unit(sa, (int64_t)tile * num_kb);
-      const int c_hi = s_cta_of_unit(sa, (int64_t)(tile + 1) * num_kb - 1);
+      const int tl = pend_tile[i];
+      const int c_lo = s_cta_of_unit(sa, tl * num_kb);
+      const int c_hi = s_cta_of_unit(sa, (tl + 1) * num_kb - 1);
       const int parts = c_hi - c_lo + 1;
+      // a contributor's piece of this tile sits in its slot 0 when the tile is the first one of its
+      // range -- true for every contributor but possibly the lowest
+      const int lo_slot = ((int)s_range_start(sa, c_lo) / num_kb == tl) ? 0 : 1;
+      const float* base = args.partial + ((int64_t)c_lo * 2) * kSlotFloats;
       SPROF(1);
       if (et == 0) {
         uint32_t spins = 0;
         uint64_t t0 = 0;
-        while (ld_acquire_gpu(&args.locks[tile]) < parts) {
+        while (ld_acquire_gpu(&args.locks[tl]) < parts) {
           if ((++spins & 0x3ffu) == 0) {
             const uint64_t t = global_timer_ns();
             if (t0 == 0) t0 = t;
@@ -418,18 +435,21 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       const int chunks = args.m * (kSCtaN / 4);
       const int per = (chunks + parts - 1) / parts;
       const int r = (int)blockIdx.x - c_lo;
-      const int q0 = r * per, q1 = min(chunks, q0 + per);
-      for (int q = q0 + et; q < q1; q += 128) {
+      const int q1 = min(chunks, (r + 1) * per);
+      for (int q = r * per + et; q < q1; q += 128) {
         const int mm = q / (kSCtaN / 4), ncol = (q % (kSCtaN / 4)) * 4;
-        const int n = tile * kSCtaN + ncol;
+        const int n = tl * kSCtaN + ncol;
         if (n >= args.n) continue;
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int c = c_lo; c <= c_hi; ++c) {
-          const int c_first = (int)(s_range_start(sa, c) / num_kb);
-          const float* src = args.partial + ((int64_t)c * 2 + (c_first == tile ? 0 : 1)) * kSlotFloats +
-                             mm * kSCtaN + ncol;
-          const float4 v = __ldcg(reinterpret_cast<const float4*>(src));
-          acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+        const float* src = base + mm * kSCtaN + ncol;
+        float4 acc = __ldcg(reinterpret_cast<const float4*>(src + lo_slot * kSlotFloats));
+        for (int c = 1; c < parts; c += 4) {  // fixed order, four loads in flight
+          float4 v[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            v[e] = c + e < parts ? __ldcg(reinterpret_cast<const float4*>(src + (int64_t)(c + e) * 2 * kSlotFloats))
+                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc.x += v[e].x, acc.y += v[e].y, acc.z += v[e].z, acc.w += v[e].w;
         }
         uint2 o;
         o.x = DT<T>::pack2(acc.x, acc.y);
@@ -438,8 +458,8 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (et == 0) {
-        const int old = atomicAdd(&args.locks[tile], 1);
-        if (old == 2 * parts - 1) args.locks[tile] = 0;  // last reader hands the counter back as zero
+        const int old = atomicAdd(&args.locks[tl], 1);
+        if (old == 2 * parts - 1) args.locks[tl] = 0;  // last reader hands the counter back as zero
       }
       SPROF(3);
     }
@@ -478,7 +498,7 @@ int launch_stream(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   if (rc != B200_OK) return rc;
   StreamArgs sa{};
   sa.n_tiles = (p.size_n + kSCtaN - 1) / kSCtaN;
-  sa.units = (int64_t)sa.n_tiles * a.num_kb;
+  sa.units = sa.n_tiles * a.num_kb;
   sa.grid = (int)(sa.units < num_sms() ? sa.units : num_sms());
   a.partial = reinterpret_cast<float*>(p.splitk_ws);
   a.locks = p.workspace;

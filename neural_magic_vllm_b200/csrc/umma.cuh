@@ -41,6 +41,16 @@ __device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity
   }
 }
 
+// one lane of a converged warp (elect.sync): role loops run warp-uniform and only the issue of
+// TMA / MMA instructions sits under this predicate, so their operands stay in uniform registers
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ---- TMEM allocation (one warp, power-of-two columns >= 32) ---------------------------------------
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t cols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
