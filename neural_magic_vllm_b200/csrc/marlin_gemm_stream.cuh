@@ -32,7 +32,8 @@ constexpr int kSCtaN = kSNT * kTileN;         // 256
 constexpr int kSTeams = 4;
 constexpr int kSDequantWarps = kSTeams * 4;
 constexpr int kSEpiWarps = 4;
-constexpr int kSThreads = (2 + kSDequantWarps + kSEpiWarps) * 32;  // 704
+constexpr int kSMma1Warp = 2 + kSDequantWarps + kSEpiWarps;       // 22: MMA issuer of sub-tile 1
+constexpr int kSThreads = (kSMma1Warp + 1) * 32;                  // 736
 constexpr int kSASlots = 2 * kSTeams;         // TMEM A slots of 32 columns (64 k)
 constexpr int kSDCol = kSASlots * kTmemAStageCols;  // 256: first accumulator column
 constexpr int kSMaxStages = 24;
@@ -82,6 +83,10 @@ __device__ __forceinline__ int s_cta_of_unit(const StreamArgs& s, int u) {
   return (int)(((uint32_t)(u + 1) * (uint32_t)s.grid - 1u) / (uint32_t)s.units);
 }
 
+// fire-and-forget *p = (*p >= wrap) ? 0 : *p + 1 with gpu-scope release
+__device__ __forceinline__ void red_release_inc(int* p, int wrap) {
+  asm volatile("red.release.gpu.global.inc.u32 [%0], %1;" ::"l"(p), "r"(wrap) : "memory");
+}
 __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
   int v;
   asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -121,14 +126,14 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     if (args.s_rows > 0) tma_prefetch_desc(&tm_s);
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&full_p[s], 1);
-      mbar_init(&empty_p[s], kSNT * 4 + 1);
+      mbar_init(&empty_p[s], kSNT * 4 + kSNT);
     }
     for (int s = 0; s < kSASlots; ++s) {
       mbar_init(&full_a[s], 4);
       mbar_init(&empty_a[s], 1);
     }
     for (int s = 0; s < 2; ++s) {
-      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_full[s], kSNT);
       mbar_init(&tmem_empty[s], kSEpiWarps);
     }
     fence_mbar_init();
@@ -199,14 +204,17 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     }
     SPROF(1);
     if (lane == 0) SPROF_FLUSH(16);
-  } else if (warp == 1) {
-    // ======================= MMA issuer =======================
-    // uniform control flow again: all lanes wait on the barriers, one elected lane issues the MMAs
-    // with descriptors / TMEM addresses that were computed in uniform registers
+  } else if (warp == 1 || warp == kSMma1Warp) {
+    // ======================= MMA issuers (one warp per 128-row sub-tile) =======================
+    // Uniform control flow again: all lanes wait on the barrier, one elected lane issues the MMAs
+    // with descriptors / TMEM addresses computed in uniform registers.  A full_a arrival implies
+    // the stage's full_p (the dequant warps waited on it first), so the activation tile is visible
+    // without a second barrier wait.  One issuer per accumulator keeps the summation order fixed.
+    const int h = warp == 1 ? 0 : 1;
     const bool leader = elect_one();
     constexpr uint32_t idesc = instr_desc<KIND>(kTileN, BM);
     int stage = 0;
-    uint32_t phase = 0, job = 0, piece = 0;
+    uint32_t job = h, piece = 0;
     int done = 0, kb = kb0;
     SPROF_DECL;
     while (done < total) {
@@ -215,30 +223,24 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       SPROF(2);
       if (piece >= 2) mbar_wait_bounded(&tmem_empty[buf], ((piece >> 1) - 1) & 1);
       SPROF(3);
-      const uint32_t d_col = tmem_base + kSDCol + buf * kDCols;
+      const uint32_t d_col = tmem_base + kSDCol + buf * kDCols + h * BM;
       for (int i = 0; i < cnt; ++i) {
-        SPROF(2);
-        mbar_wait_bounded(&full_p[stage], phase);  // activation tile landed
-        SPROF(0);
+        const uint32_t aslot = job & (kSASlots - 1);
         const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
+        const uint32_t a_col = tmem_base + aslot * kTmemAStageCols;
+        SPROF(2);
+        mbar_wait_bounded(&full_a[aslot], (job >> 3) & 1);
+        SPROF(1);
+        fence_after_sync();
+        if (leader) {
 #pragma unroll
-        for (int h = 0; h < kSNT; ++h) {
-          const uint32_t aslot = job & (kSASlots - 1);
-          SPROF(2);
-          mbar_wait_bounded(&full_a[aslot], (job >> 3) & 1);
-          SPROF(1);
-          fence_after_sync();
-          const uint32_t a_col = tmem_base + aslot * kTmemAStageCols;
-          if (leader) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-              mma_ts_f16(d_col + h * BM, a_col + k * 8, desc_advance(dx, k * 32), idesc, (i > 0 || k > 0) ? 1u : 0u);
-            mma_commit(&empty_a[aslot]);
-          }
-          ++job;
+          for (int k = 0; k < 4; ++k)
+            mma_ts_f16(d_col, a_col + k * 8, desc_advance(dx, k * 32), idesc, (i > 0 || k > 0) ? 1u : 0u);
+          mma_commit(&empty_a[aslot]);
+          mma_commit(&empty_p[stage]);
         }
-        if (leader) mma_commit(&empty_p[stage]);
-        if (++stage == kStages) stage = 0, phase ^= 1;
+        job += kSNT;
+        if (++stage == kStages) stage = 0;
       }
       if (leader) mma_commit(&tmem_full[buf]);
       ++piece;
@@ -247,7 +249,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     }
     pdl_launch_dependents();
     SPROF(2);
-    if (lane == 0) SPROF_FLUSH(0);
+    if (warp == 1 && lane == 0) SPROF_FLUSH(0);
   } else if (warp < 2 + kSDequantWarps) {
     // ======================= dequant teams =======================
     // job (unit i, sub-tile h) has index 2 i + h and goes to team (2 i + h) % 4: team t takes
@@ -273,14 +275,12 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     int tile = tile0, kb = kb0 + i;
     while (kb >= num_kb) kb -= num_kb, ++tile;
     SPROF_DECL;
-    for (; i < total; i += 2) {
-      const uint32_t job = 2 * i + h;
-      const uint32_t aslot = job & (kSASlots - 1);
-      SPROF(5);
-      mbar_wait_bounded(&full_p[stage], phase);
-      SPROF(0);
-      const uint32_t w_src = lane_src + stage * P::kStageBytes;
-      uint32_t words[4][BITS == 4 ? 2 : 4];
+    // software pipeline: the packed words (and scales) of the team's NEXT job are fetched from
+    // shared memory before the current job is unpacked
+    uint32_t words[4][BITS == 4 ? 2 : 4];
+    uint2 sv = make_uint2(0u, 0u);
+    auto fetch = [&](int st) {
+      const uint32_t w_src = lane_src + st * P::kStageBytes;
 #pragma unroll
       for (int kt = 0; kt < 4; ++kt) {
         if constexpr (BITS == 4) {
@@ -291,9 +291,24 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
           words[kt][0] = v.x, words[kt][1] = v.y, words[kt][2] = v.z, words[kt][3] = v.w;
         }
       }
+      if (grouped) sv = lds64(scale_src + st * P::kStageBytes);
+    };
+    if (i < total) {
+      mbar_wait_bounded(&full_p[stage], phase);
+      fetch(stage);
+    }
+    for (; i < total; i += 2) {
+      const uint32_t job = 2 * i + h;
+      const uint32_t aslot = job & (kSASlots - 1);
+      SPROF(5);
+      // this job's operands -> private registers, then start the next job's fetch
+      uint32_t cur[4][BITS == 4 ? 2 : 4];
+#pragma unroll
+      for (int kt = 0; kt < 4; ++kt)
+#pragma unroll
+        for (int e = 0; e < (BITS == 4 ? 2 : 4); ++e) cur[kt][e] = words[kt][e];
       if (grouped) {
-        const uint2 v = lds64(scale_src + stage * P::kStageBytes);
-        sc[0] = dup16(v.x, 0), sc[1] = dup16(v.x, 1), sc[2] = dup16(v.y, 0), sc[3] = dup16(v.y, 1);
+        sc[0] = dup16(sv.x, 0), sc[1] = dup16(sv.x, 1), sc[2] = dup16(sv.y, 0), sc[3] = dup16(sv.y, 1);
       } else if (sc_tile != tile) {
         sc_tile = tile;
         const uint16_t* s = reinterpret_cast<const uint16_t*>(args.scales);
@@ -306,7 +321,15 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty_p[stage]);  // packed words + scales are in registers
+      int nstage = stage + 2;
+      uint32_t nphase = phase;
+      if (nstage >= kStages) nstage -= kStages, nphase ^= 1;
       SPROF(1);
+      if (i + 2 < total) {
+        mbar_wait_bounded(&full_p[nstage], nphase);
+        fetch(nstage);
+      }
+      SPROF(0);
       mbar_wait_bounded(&empty_a[aslot], ((job >> 3) & 1) ^ 1);
       SPROF(2);
       fence_after_sync();
@@ -317,10 +340,10 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
         for (int jj = 0; jj < 2; ++jj) {
           uint32_t rg[4];
           if constexpr (BITS == 4) {
-            unpack4<T>(words[kt][jj], rg);
+            unpack4<T>(cur[kt][jj], rg);
           } else {
-            unpack8<T>(words[kt][2 * jj], rg[0], rg[1]);
-            unpack8<T>(words[kt][2 * jj + 1], rg[2], rg[3]);
+            unpack8<T>(cur[kt][2 * jj], rg[0], rg[1]);
+            unpack8<T>(cur[kt][2 * jj + 1], rg[2], rg[3]);
           }
           rg[0] = mul2<T>(rg[0], sc[2 * jj]);
           rg[1] = mul2<T>(rg[1], sc[2 * jj]);
@@ -338,8 +361,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       SPROF(4);
       kb += 2;
       while (kb >= num_kb) kb -= num_kb, ++tile;
-      stage += 2;
-      if (stage >= kStages) stage -= kStages, phase ^= 1;
+      stage = nstage, phase = nphase;
     }
     SPROF(5);
     if (warp == 2 && lane == 0) SPROF_FLUSH(8);
@@ -396,9 +418,13 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[buf]);
       if (!whole) {
-        __threadfence();
+        // publish: the barrier orders the 128 threads' partial stores before thread 0's gpu-scope
+        // release (cumulative); the counter wraps to zero after 2 x parts increments (see below)
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (et == 0) atomicAdd(&args.locks[tile], 1);
+        if (et == 0) {
+          const int c_lo = s_cta_of_unit(sa, tile * num_kb), c_hi = s_cta_of_unit(sa, (tile + 1) * num_kb - 1);
+          red_release_inc(&args.locks[tile], 2 * (c_hi - c_lo + 1) - 1);
+        }
         pend_tile[n_pend++] = tile;
       }
       ++piece;
@@ -428,9 +454,8 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
           }
         }
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // thread 0's acquire covers the CTA
       SPROF(2);
-      __threadfence();
       // chunks of 4 consecutive columns of one token row; contributor r sums chunks [q0, q1)
       const int chunks = args.m * (kSCtaN / 4);
       const int per = (chunks + parts - 1) / parts;
@@ -457,10 +482,9 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
         *reinterpret_cast<uint2*>(reinterpret_cast<T*>(args.c) + (int64_t)mm * args.n + n) = o;
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (et == 0) {
-        const int old = atomicAdd(&args.locks[tl], 1);
-        if (old == 2 * parts - 1) args.locks[tl] = 0;  // last reader hands the counter back as zero
-      }
+      // second round of increments: the 2 x parts-th one wraps the counter back to zero (atom.inc
+      // semantics), which cannot happen before every contributor has passed its spin above
+      if (et == 0) red_release_inc(&args.locks[tl], 2 * parts - 1);
       SPROF(3);
     }
     SPROF(1);
