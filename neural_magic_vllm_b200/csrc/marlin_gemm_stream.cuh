@@ -93,7 +93,7 @@ __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
   return v;
 }
 
-template <int BITS, int BM, typename T>
+template <int BITS, int BM, typename T, bool GROUPED>
 __global__ void __launch_bounds__(kSThreads, 1)
 marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                           const __grid_constant__ CUtensorMap tm_s, const MarlinArgs args, const StreamArgs sa) {
@@ -111,6 +111,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
   uint64_t* tmem_full = empty_a + kSASlots;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;       // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint32_t* tail = tmem_slot + 1;  // [3]: number of partial tiles of this CTA, their indices
 
   // warp-uniform by construction: say so, so that role code keeps its operands in uniform registers
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
@@ -118,7 +119,6 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
   const int u0 = (int)s_range_start(sa, blockIdx.x), u1 = (int)s_range_start(sa, blockIdx.x + 1);
   const int total = u1 - u0;
   const int tile0 = u0 / num_kb, kb0 = u0 - tile0 * num_kb;
-  const bool grouped = args.num_groups > 1;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_x);
@@ -275,40 +275,37 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     int tile = tile0, kb = kb0 + i;
     while (kb >= num_kb) kb -= num_kb, ++tile;
     SPROF_DECL;
-    // software pipeline: the packed words (and scales) of the team's NEXT job are fetched from
-    // shared memory before the current job is unpacked
-    uint32_t words[4][BITS == 4 ? 2 : 4];
-    uint2 sv = make_uint2(0u, 0u);
-    auto fetch = [&](int st) {
+    constexpr int kW = BITS == 4 ? 2 : 4;
+    // software pipeline over two register sets: the packed words (and scales) of the team's NEXT
+    // job are fetched from shared memory before the current job is unpacked
+    auto fetch = [&](uint32_t (&w)[4][kW], uint2& sv, int st) {
       const uint32_t w_src = lane_src + st * P::kStageBytes;
 #pragma unroll
       for (int kt = 0; kt < 4; ++kt) {
         if constexpr (BITS == 4) {
           const uint2 v = lds64(w_src + kt * 1024);
-          words[kt][0] = v.x, words[kt][1] = v.y;
+          w[kt][0] = v.x, w[kt][1] = v.y;
         } else {
           const uint4 v = lds128(w_src + kt * 1024);
-          words[kt][0] = v.x, words[kt][1] = v.y, words[kt][2] = v.z, words[kt][3] = v.w;
+          w[kt][0] = v.x, w[kt][1] = v.y, w[kt][2] = v.z, w[kt][3] = v.w;
         }
       }
-      if (grouped) sv = lds64(scale_src + st * P::kStageBytes);
+      if constexpr (GROUPED) sv = lds64(scale_src + st * P::kStageBytes);
     };
-    if (i < total) {
-      mbar_wait_bounded(&full_p[stage], phase);
-      fetch(stage);
-    }
-    for (; i < total; i += 2) {
+    auto job_step = [&](uint32_t (&cur)[4][kW], uint2& cur_sv, uint32_t (&nxt)[4][kW], uint2& nxt_sv) {
       const uint32_t job = 2 * i + h;
       const uint32_t aslot = job & (kSASlots - 1);
       SPROF(5);
-      // this job's operands -> private registers, then start the next job's fetch
-      uint32_t cur[4][BITS == 4 ? 2 : 4];
-#pragma unroll
-      for (int kt = 0; kt < 4; ++kt)
-#pragma unroll
-        for (int e = 0; e < (BITS == 4 ? 2 : 4); ++e) cur[kt][e] = words[kt][e];
-      if (grouped) {
-        sc[0] = dup16(sv.x, 0), sc[1] = dup16(sv.x, 1), sc[2] = dup16(sv.y, 0), sc[3] = dup16(sv.y, 1);
+      int nstage = stage + 2;
+      uint32_t nphase = phase;
+      if (nstage >= kStages) nstage -= kStages, nphase ^= 1;
+      if (i + 2 < total) {
+        mbar_wait_bounded(&full_p[nstage], nphase);
+        fetch(nxt, nxt_sv, nstage);
+      }
+      SPROF(0);
+      if constexpr (GROUPED) {
+        sc[0] = dup16(cur_sv.x, 0), sc[1] = dup16(cur_sv.x, 1), sc[2] = dup16(cur_sv.y, 0), sc[3] = dup16(cur_sv.y, 1);
       } else if (sc_tile != tile) {
         sc_tile = tile;
         const uint16_t* s = reinterpret_cast<const uint16_t*>(args.scales);
@@ -319,25 +316,17 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
           sc[e] = v | (v << 16);
         }
       }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&empty_p[stage]);  // packed words + scales are in registers
-      int nstage = stage + 2;
-      uint32_t nphase = phase;
-      if (nstage >= kStages) nstage -= kStages, nphase ^= 1;
-      SPROF(1);
-      if (i + 2 < total) {
-        mbar_wait_bounded(&full_p[nstage], nphase);
-        fetch(nstage);
-      }
-      SPROF(0);
       mbar_wait_bounded(&empty_a[aslot], ((job >> 3) & 1) ^ 1);
       SPROF(2);
       fence_after_sync();
       const uint32_t t_dst = t_lane + aslot * kTmemAStageCols;
 #pragma unroll
-      for (int kt = 0; kt < 4; ++kt) {
+      for (int jj = 0; jj < 2; ++jj) {
+        // 16 rows x 64 k of the job = 32 TMEM columns = one tcgen05.st 16x128b.x8:
+        // unit 2 kt = {b0, b1} of the k-lo quad, unit 2 kt + 1 = {b0, b1} of the k-hi quad
+        uint32_t st[16];
 #pragma unroll
-        for (int jj = 0; jj < 2; ++jj) {
+        for (int kt = 0; kt < 4; ++kt) {
           uint32_t rg[4];
           if constexpr (BITS == 4) {
             unpack4<T>(cur[kt][jj], rg);
@@ -345,14 +334,15 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
             unpack8<T>(cur[kt][2 * jj], rg[0], rg[1]);
             unpack8<T>(cur[kt][2 * jj + 1], rg[2], rg[3]);
           }
-          rg[0] = mul2<T>(rg[0], sc[2 * jj]);
-          rg[1] = mul2<T>(rg[1], sc[2 * jj]);
-          rg[2] = mul2<T>(rg[2], sc[2 * jj + 1]);
-          rg[3] = mul2<T>(rg[3], sc[2 * jj + 1]);
-          // rg = {b0 k-lo, b0 k-hi, b1 k-lo, b1 k-hi} -> st order {b0 lo, b1 lo, b0 hi, b1 hi}
-          tmem_st_16x128b_x2(t_dst + ((uint32_t)(16 * jj) << 16) + kt * 8, rg[0], rg[2], rg[1], rg[3]);
+          st[4 * kt + 0] = mul2<T>(rg[0], sc[2 * jj]);
+          st[4 * kt + 2] = mul2<T>(rg[1], sc[2 * jj]);
+          st[4 * kt + 1] = mul2<T>(rg[2], sc[2 * jj + 1]);
+          st[4 * kt + 3] = mul2<T>(rg[3], sc[2 * jj + 1]);
         }
+        tmem_st_16x128b_x8(t_dst + ((uint32_t)(16 * jj) << 16), st);
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_p[stage]);  // every lane has consumed its packed words + scales
       SPROF(3);
       tmem_st_wait();
       fence_before_sync();
@@ -362,6 +352,18 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       kb += 2;
       while (kb >= num_kb) kb -= num_kb, ++tile;
       stage = nstage, phase = nphase;
+      i += 2;
+    };
+    uint32_t wa[4][kW], wb[4][kW];
+    uint2 sva = make_uint2(0u, 0u), svb = make_uint2(0u, 0u);
+    if (i < total) {
+      mbar_wait_bounded(&full_p[stage], phase);
+      fetch(wa, sva, stage);
+    }
+    while (i < total) {
+      job_step(wa, sva, wb, svb);
+      if (i >= total) break;
+      job_step(wb, svb, wa, sva);
     }
     SPROF(5);
     if (warp == 2 && lane == 0) SPROF_FLUSH(8);
@@ -372,7 +374,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16) + kSDCol;
     constexpr int kSlotFloats = BM * kSCtaN;
     float* my_slots = args.partial + (int64_t)blockIdx.x * 2 * kSlotFloats;
-    int pend_tile[2];
+    int pend_tile[2] = {0, 0};
     int n_pend = 0;
     uint32_t piece = 0;
     int done = 0, tile = tile0, kb = kb0;
@@ -432,9 +434,29 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       kb = 0;
       ++tile;
     }
-    // every partial of this CTA is published; now sum this CTA's slice of each tile it touched
+    if (et == 0) {
+      tail[0] = (uint32_t)n_pend;
+      tail[1] = (uint32_t)pend_tile[0];
+      tail[2] = (uint32_t)pend_tile[1];
+    }
+    SPROF(1);
+    if (et == 0) SPROF_FLUSH(24);
+  }
+  __syncthreads();
+  if (warp == 1) {
+    fence_after_sync();
+    tmem_dealloc(tmem_base, 512);
+  }
+  // ======================= distributed split-K reduction (all warps) =======================
+  // Every partial of this CTA is published.  For each tile it contributed to, the CTA waits until
+  // all contributors have arrived and then sums ITS slice of the tile from the contributors' slots
+  // in a fixed order (deterministic), rounds once and stores.
+  {
+    constexpr int kSlotFloats = BM * kSCtaN;
+    const int n_pend = (int)tail[0];
+    const int tid = threadIdx.x;
     for (int i = 0; i < n_pend; ++i) {
-      const int tl = pend_tile[i];
+      const int tl = (int)tail[1 + i];
       const int c_lo = s_cta_of_unit(sa, tl * num_kb);
       const int c_hi = s_cta_of_unit(sa, (tl + 1) * num_kb - 1);
       const int parts = c_hi - c_lo + 1;
@@ -442,8 +464,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       // range -- true for every contributor but possibly the lowest
       const int lo_slot = ((int)s_range_start(sa, c_lo) / num_kb == tl) ? 0 : 1;
       const float* base = args.partial + ((int64_t)c_lo * 2) * kSlotFloats;
-      SPROF(1);
-      if (et == 0) {
+      if (tid == 0) {
         uint32_t spins = 0;
         uint64_t t0 = 0;
         while (ld_acquire_gpu(&args.locks[tl]) < parts) {
@@ -454,46 +475,57 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
           }
         }
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // thread 0's acquire covers the CTA
-      SPROF(2);
+      __syncthreads();  // thread 0's gpu-scope acquire covers the CTA
       // chunks of 4 consecutive columns of one token row; contributor r sums chunks [q0, q1)
       const int chunks = args.m * (kSCtaN / 4);
       const int per = (chunks + parts - 1) / parts;
       const int r = (int)blockIdx.x - c_lo;
       const int q1 = min(chunks, (r + 1) * per);
-      for (int q = r * per + et; q < q1; q += 128) {
-        const int mm = q / (kSCtaN / 4), ncol = (q % (kSCtaN / 4)) * 4;
-        const int n = tl * kSCtaN + ncol;
-        if (n >= args.n) continue;
-        const float* src = base + mm * kSCtaN + ncol;
-        float4 acc = __ldcg(reinterpret_cast<const float4*>(src + lo_slot * kSlotFloats));
-        for (int c = 1; c < parts; c += 4) {  // fixed order, four loads in flight
-          float4 v[4];
+      constexpr int kB = 4;  // chunks per thread in flight
+      for (int q = r * per + tid; q < q1; q += kSThreads * kB) {
+        const float* src[kB];
+        float4 acc[kB];
+        int64_t dst[kB];
 #pragma unroll
-          for (int e = 0; e < 4; ++e)
-            v[e] = c + e < parts ? __ldcg(reinterpret_cast<const float4*>(src + (int64_t)(c + e) * 2 * kSlotFloats))
-                                 : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-          for (int e = 0; e < 4; ++e) acc.x += v[e].x, acc.y += v[e].y, acc.z += v[e].z, acc.w += v[e].w;
+        for (int e = 0; e < kB; ++e) {
+          const int qq = q + e * kSThreads;
+          const int mm = qq / (kSCtaN / 4), ncol = (qq % (kSCtaN / 4)) * 4;
+          const int n = tl * kSCtaN + ncol;
+          const bool ok = qq < q1 && n < args.n;
+          src[e] = ok ? base + mm * kSCtaN + ncol : nullptr;
+          dst[e] = (int64_t)mm * args.n + n;
+          acc[e] = ok ? __ldcg(reinterpret_cast<const float4*>(src[e] + lo_slot * kSlotFloats))
+                      : make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        uint2 o;
-        o.x = DT<T>::pack2(acc.x, acc.y);
-        o.y = DT<T>::pack2(acc.z, acc.w);
-        *reinterpret_cast<uint2*>(reinterpret_cast<T*>(args.c) + (int64_t)mm * args.n + n) = o;
+        for (int c = 1; c < parts; c += 2) {  // fixed order; kB x 2 loads in flight
+          float4 v[kB][2];
+#pragma unroll
+          for (int e = 0; e < kB; ++e)
+#pragma unroll
+            for (int d = 0; d < 2; ++d)
+              v[e][d] = (src[e] != nullptr && c + d < parts)
+                            ? __ldcg(reinterpret_cast<const float4*>(src[e] + (int64_t)(c + d) * 2 * kSlotFloats))
+                            : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int e = 0; e < kB; ++e)
+#pragma unroll
+            for (int d = 0; d < 2; ++d)
+              acc[e].x += v[e][d].x, acc[e].y += v[e][d].y, acc[e].z += v[e][d].z, acc[e].w += v[e][d].w;
+        }
+#pragma unroll
+        for (int e = 0; e < kB; ++e) {
+          if (src[e] == nullptr) continue;
+          uint2 o;
+          o.x = DT<T>::pack2(acc[e].x, acc[e].y);
+          o.y = DT<T>::pack2(acc[e].z, acc[e].w);
+          *reinterpret_cast<uint2*>(reinterpret_cast<T*>(args.c) + dst[e]) = o;
+        }
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      __syncthreads();
       // second round of increments: the 2 x parts-th one wraps the counter back to zero (atom.inc
       // semantics), which cannot happen before every contributor has passed its spin above
-      if (et == 0) red_release_inc(&args.locks[tl], 2 * parts - 1);
-      SPROF(3);
+      if (tid == 0) red_release_inc(&args.locks[tl], 2 * parts - 1);
     }
-    SPROF(1);
-    if (et == 0) SPROF_FLUSH(24);
-  }
-  __syncthreads();
-  if (warp == 1) {
-    fence_after_sync();
-    tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -526,9 +558,10 @@ int launch_stream(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   sa.grid = (int)(sa.units < num_sms() ? sa.units : num_sms());
   a.partial = reinterpret_cast<float*>(p.splitk_ws);
   a.locks = p.workspace;
-  auto kern = marlin_gemm_stream_kernel<BITS, BM, T>;
-  static size_t smem_configured[kMaxDevices] = {};
-  if (ensure_dyn_smem(kern, P::kBytes, smem_configured) != cudaSuccess) {
+  auto kern = p.num_groups > 1 ? marlin_gemm_stream_kernel<BITS, BM, T, true>
+                               : marlin_gemm_stream_kernel<BITS, BM, T, false>;
+  static size_t smem_configured[2][kMaxDevices] = {};
+  if (ensure_dyn_smem(kern, P::kBytes, smem_configured[p.num_groups > 1 ? 1 : 0]) != cudaSuccess) {
     cudaGetLastError();
     set_error("gptq_marlin_gemm: cannot reserve %d B of shared memory", (int)P::kBytes);
     return B200_ECUDA;

@@ -144,6 +144,16 @@ __device__ __forceinline__ void tmem_st_16x128b_x2(uint32_t taddr, uint32_t r0, 
                "r"(r1), "r"(r2), "r"(r3)
                : "memory");
 }
+// shape 16x128b.x8: 16 lanes x 32 columns; unit u (4 columns) takes r[2u] = (lane t/4, col 4u + t%4)
+// and r[2u+1] = (lane t/4 + 8, col 4u + t%4)
+__device__ __forceinline__ void tmem_st_16x128b_x8(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.16x128b.x8.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+      "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
 __device__ __forceinline__ void tmem_st_wait() {
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
