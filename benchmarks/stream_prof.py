@@ -51,12 +51,19 @@ def main():
         print("library was not built with -DB200_STREAM_PROF")
         return
     prof = buf.reshape(160, 32)[:148].astype(np.float64)
+    marks(prof)
     for role, (base, names) in ROLES.items():
-        tot = prof[:, base:base + 8].sum(axis=1)
+        tot = prof[:, base:base + 6].sum(axis=1)
         print(f"{role}: total cycles avg {tot.mean():.0f} (min {tot.min():.0f} max {tot.max():.0f})")
         for j, nm in enumerate(names):
             c = prof[:, base + j]
             print(f"    {nm:24s} avg {c.mean():9.0f}  ({100 * c.mean() / max(tot.mean(), 1):5.1f} %)  max {c.max():9.0f}")
+
+
+def marks(prof):
+    for nm, j in (("prologue done", 6), ("MMA warp done", 7), ("epilogue role done", 30), ("kernel end", 31)):
+        c = prof[:, j]
+        print(f"  since kernel entry: {nm:20s} avg {c.mean():9.0f}  min {c.min():9.0f}  max {c.max():9.0f}")
 
 
 if __name__ == "__main__":

@@ -58,6 +58,8 @@ struct PlanS {
 __device__ unsigned long long g_stream_prof[160 * 32];
 #define SPROF_DECL long long sp_t = clock64(), sp_n; unsigned long long sp_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}
 #define SPROF(i) (sp_n = clock64(), sp_acc[i] += (unsigned long long)(sp_n - sp_t), sp_t = sp_n)
+#define SPROF_ENTRY const long long sp_entry = clock64()
+#define SPROF_MARK(slot) g_stream_prof[blockIdx.x * 32 + (slot)] = (unsigned long long)(clock64() - sp_entry)
 #define SPROF_FLUSH(base)                                                              \
   do {                                                                                 \
     for (int sp_i = 0; sp_i < 8; ++sp_i) g_stream_prof[blockIdx.x * 32 + (base) + sp_i] = sp_acc[sp_i]; \
@@ -66,6 +68,8 @@ __device__ unsigned long long g_stream_prof[160 * 32];
 #define SPROF_DECL
 #define SPROF(i)
 #define SPROF_FLUSH(base)
+#define SPROF_ENTRY
+#define SPROF_MARK(slot)
 #endif
 
 struct StreamArgs {
@@ -87,6 +91,11 @@ __device__ __forceinline__ int s_cta_of_unit(const StreamArgs& s, int u) {
 __device__ __forceinline__ void red_release_inc(int* p, int wrap) {
   asm volatile("red.release.gpu.global.inc.u32 [%0], %1;" ::"l"(p), "r"(wrap) : "memory");
 }
+__device__ __forceinline__ int atom_add_acq_rel(int* p, int v) {
+  int old;
+  asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+  return old;
+}
 __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
   int v;
   asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -101,6 +110,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
   constexpr int kStages = P::kStages;
   constexpr int KIND = DT<T>::id == B200_F16 ? KIND_F16 : KIND_BF16;
   constexpr int kDCols = kSNT * BM;  // accumulator columns of one piece
+  SPROF_ENTRY;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(stages + kStages * P::kStageBytes);
@@ -111,7 +121,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
   uint64_t* tmem_full = empty_a + kSASlots;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;       // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  uint32_t* tail = tmem_slot + 1;  // [3]: number of partial tiles of this CTA, their indices
+  uint32_t* tail = tmem_slot + 1;  // epilogue scratch: "this CTA arrived last"
 
   // warp-uniform by construction: say so, so that role code keeps its operands in uniform registers
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
@@ -143,6 +153,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
   __syncthreads();
   fence_after_sync();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  if (threadIdx.x == 0) SPROF_MARK(6);
 
   if (warp == 0) {
     // ======================= TMA producer =======================
@@ -249,7 +260,10 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     }
     pdl_launch_dependents();
     SPROF(2);
-    if (warp == 1 && lane == 0) SPROF_FLUSH(0);
+    if (warp == 1 && lane == 0) {
+      SPROF_FLUSH(0);
+      SPROF_MARK(7);
+    }
   } else if (warp < 2 + kSDequantWarps) {
     // ======================= dequant teams =======================
     // job (unit i, sub-tile h) has index 2 i + h and goes to team (2 i + h) % 4: team t takes
@@ -368,14 +382,20 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     SPROF(5);
     if (warp == 2 && lane == 0) SPROF_FLUSH(8);
   } else {
-    // ======================= epilogue + distributed split-K reduction =======================
+    // ======================= epilogue + split-K fix-up =======================
+    // A whole tile is rounded once and stored.  A partial piece is published to this CTA's fp32
+    // slot ([column][token]: 64 contiguous bytes per thread) and the tile's arrival counter is
+    // bumped; whoever arrives LAST sums the contributors in CTA order -- its own piece straight from
+    // TMEM, the others from their slots -- rounds once, stores, and hands the counter back as zero.
+    // Nobody ever waits for another CTA; the summation order is fixed, so the result is
+    // deterministic.  A piece at the head of a range (the tile's other contributors finish later)
+    // is thus fixed up by someone else, a piece at the tail by this CTA, usually at once.
     const int qd = warp & 3;
     const int et = (warp - 2 - kSDequantWarps) * 32 + lane;  // 0..127
     const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16) + kSDCol;
     constexpr int kSlotFloats = BM * kSCtaN;
     float* my_slots = args.partial + (int64_t)blockIdx.x * 2 * kSlotFloats;
-    int pend_tile[2] = {0, 0};
-    int n_pend = 0;
+    T* out = reinterpret_cast<T*>(args.c);
     uint32_t piece = 0;
     int done = 0, tile = tile0, kb = kb0;
     SPROF_DECL;
@@ -387,146 +407,125 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       mbar_wait_bounded(&tmem_full[buf], (piece >> 1) & 1);
       SPROF(0);
       fence_after_sync();
-      float* slot = my_slots + (tile == tile0 ? 0 : kSlotFloats);
+      const uint32_t t_src = t_lane + buf * kDCols;
+      if (whole) {
 #pragma unroll 1
-      for (int h = 0; h < kSNT; ++h) {
-        const int ncol = h * kTileN + qd * 32 + lane;
-        const int n = tile * kSCtaN + ncol;
+        for (int h = 0; h < kSNT; ++h) {
+          const int n = tile * kSCtaN + h * kTileN + qd * 32 + lane;
 #pragma unroll 1
-        for (int c = 0; c < BM / 16; ++c) {
-          if (c * 16 >= args.m) break;
-          uint32_t rr[16];
-          tmem_ld16(t_lane + buf * kDCols + h * BM + c * 16, rr);
-          tmem_ld_wait();
-          if (whole) {
+          for (int c = 0; c < BM / 16; ++c) {
+            if (c * 16 >= args.m) break;
+            uint32_t rr[16];
+            tmem_ld16(t_src + h * BM + c * 16, rr);
+            tmem_ld_wait();
             if (n < args.n) {
-              T* out = reinterpret_cast<T*>(args.c);
 #pragma unroll
               for (int j = 0; j < 16; ++j) {
                 const int mm = c * 16 + j;
                 if (mm < args.m) out[(int64_t)mm * args.n + n] = DT<T>::from_f(__uint_as_float(rr[j]));
               }
             }
-          } else {
+          }
+        }
+      } else {
+        float* slot = my_slots + (tile == tile0 ? 0 : kSlotFloats);
+#pragma unroll 1
+        for (int h = 0; h < kSNT; ++h) {
+          float* dst = slot + (h * kTileN + qd * 32 + lane) * BM;
+#pragma unroll 1
+          for (int c = 0; c < BM / 16; ++c) {
+            if (c * 16 >= args.m) break;
+            uint32_t rr[16];
+            tmem_ld16(t_src + h * BM + c * 16, rr);
+            tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const int mm = c * 16 + j;
-              if (mm < args.m) slot[mm * kSCtaN + ncol] = __uint_as_float(rr[j]);
+            for (int j = 0; j < 16; j += 4)
+              if (c * 16 + j < args.m)
+                *reinterpret_cast<uint4*>(dst + c * 16 + j) = make_uint4(rr[j], rr[j + 1], rr[j + 2], rr[j + 3]);
+          }
+        }
+        // publish: the barrier orders the 128 threads' stores before thread 0's gpu-scope
+        // acq_rel increment (cumulative); its return value says whether this CTA arrived last
+        const int c_lo = s_cta_of_unit(sa, tile * num_kb), c_hi = s_cta_of_unit(sa, (tile + 1) * num_kb - 1);
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) tail[0] = atom_add_acq_rel(&args.locks[tile], 1) == c_hi - c_lo ? 1u : 0u;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (tail[0] != 0) {
+          // a contributor's piece sits in its slot 0 when the tile is the first of its range: true
+          // for every contributor except possibly the lowest
+          const int lo_slot = ((int)s_range_start(sa, c_lo) / num_kb == tile) ? 0 : 1;
+          const int me = (int)blockIdx.x;
+#pragma unroll 1
+          for (int h = 0; h < kSNT; ++h) {
+            const int ncol = h * kTileN + qd * 32 + lane;
+            const int n = tile * kSCtaN + ncol;
+#pragma unroll 1
+            for (int c = 0; c < BM / 16; ++c) {
+              if (c * 16 >= args.m) break;
+              const int nq = (min(args.m - c * 16, 16) + 3) >> 2;  // float4 per thread
+              uint32_t own[16];
+              tmem_ld16(t_src + h * BM + c * 16, own);
+              float acc[16];
+#pragma unroll
+              for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+              const float* src = args.partial + ((int64_t)c_lo * 2 + lo_slot) * kSlotFloats + ncol * BM + c * 16;
+              for (int cc = c_lo; cc <= c_hi; cc += 2) {  // fixed order, two contributors in flight
+                float4 v[2][4];
+#pragma unroll
+                for (int d = 0; d < 2; ++d) {
+                  const float* sp = cc + d == c_lo ? src : src + ((int64_t)(cc + d - c_lo) * 2 - lo_slot) * kSlotFloats;
+#pragma unroll
+                  for (int e = 0; e < 4; ++e)
+                    v[d][e] = (cc + d <= c_hi && cc + d != me && e < nq && n < args.n)
+                                  ? __ldcg(reinterpret_cast<const float4*>(sp) + e)
+                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                tmem_ld_wait();
+#pragma unroll
+                for (int d = 0; d < 2; ++d) {
+                  if (cc + d == me) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) acc[j] += __uint_as_float(own[j]);
+                  } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                      acc[4 * e] += v[d][e].x, acc[4 * e + 1] += v[d][e].y, acc[4 * e + 2] += v[d][e].z,
+                          acc[4 * e + 3] += v[d][e].w;
+                  }
+                }
+              }
+              if (n < args.n) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  const int mm = c * 16 + j;
+                  if (mm < args.m) out[(int64_t)mm * args.n + n] = DT<T>::from_f(acc[j]);
+                }
+              }
             }
           }
+          if (et == 0) args.locks[tile] = 0;
         }
       }
       fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[buf]);
-      if (!whole) {
-        // publish: the barrier orders the 128 threads' partial stores before thread 0's gpu-scope
-        // release (cumulative); the counter wraps to zero after 2 x parts increments (see below)
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (et == 0) {
-          const int c_lo = s_cta_of_unit(sa, tile * num_kb), c_hi = s_cta_of_unit(sa, (tile + 1) * num_kb - 1);
-          red_release_inc(&args.locks[tile], 2 * (c_hi - c_lo + 1) - 1);
-        }
-        pend_tile[n_pend++] = tile;
-      }
       ++piece;
       done += cnt;
       kb = 0;
       ++tile;
     }
-    if (et == 0) {
-      tail[0] = (uint32_t)n_pend;
-      tail[1] = (uint32_t)pend_tile[0];
-      tail[2] = (uint32_t)pend_tile[1];
-    }
     SPROF(1);
-    if (et == 0) SPROF_FLUSH(24);
+    if (et == 0) {
+      SPROF_FLUSH(24);
+      SPROF_MARK(30);
+    }
   }
   __syncthreads();
   if (warp == 1) {
     fence_after_sync();
     tmem_dealloc(tmem_base, 512);
   }
-  // ======================= distributed split-K reduction (all warps) =======================
-  // Every partial of this CTA is published.  For each tile it contributed to, the CTA waits until
-  // all contributors have arrived and then sums ITS slice of the tile from the contributors' slots
-  // in a fixed order (deterministic), rounds once and stores.
-  {
-    constexpr int kSlotFloats = BM * kSCtaN;
-    const int n_pend = (int)tail[0];
-    const int tid = threadIdx.x;
-    for (int i = 0; i < n_pend; ++i) {
-      const int tl = (int)tail[1 + i];
-      const int c_lo = s_cta_of_unit(sa, tl * num_kb);
-      const int c_hi = s_cta_of_unit(sa, (tl + 1) * num_kb - 1);
-      const int parts = c_hi - c_lo + 1;
-      // a contributor's piece of this tile sits in its slot 0 when the tile is the first one of its
-      // range -- true for every contributor but possibly the lowest
-      const int lo_slot = ((int)s_range_start(sa, c_lo) / num_kb == tl) ? 0 : 1;
-      const float* base = args.partial + ((int64_t)c_lo * 2) * kSlotFloats;
-      if (tid == 0) {
-        uint32_t spins = 0;
-        uint64_t t0 = 0;
-        while (ld_acquire_gpu(&args.locks[tl]) < parts) {
-          if ((++spins & 0x3ffu) == 0) {
-            const uint64_t t = global_timer_ns();
-            if (t0 == 0) t0 = t;
-            else if (t - t0 > kMbarTimeoutNs) __trap();
-          }
-        }
-      }
-      __syncthreads();  // thread 0's gpu-scope acquire covers the CTA
-      // chunks of 4 consecutive columns of one token row; contributor r sums chunks [q0, q1)
-      const int chunks = args.m * (kSCtaN / 4);
-      const int per = (chunks + parts - 1) / parts;
-      const int r = (int)blockIdx.x - c_lo;
-      const int q1 = min(chunks, (r + 1) * per);
-      constexpr int kB = 4;  // chunks per thread in flight
-      for (int q = r * per + tid; q < q1; q += kSThreads * kB) {
-        const float* src[kB];
-        float4 acc[kB];
-        int64_t dst[kB];
-#pragma unroll
-        for (int e = 0; e < kB; ++e) {
-          const int qq = q + e * kSThreads;
-          const int mm = qq / (kSCtaN / 4), ncol = (qq % (kSCtaN / 4)) * 4;
-          const int n = tl * kSCtaN + ncol;
-          const bool ok = qq < q1 && n < args.n;
-          src[e] = ok ? base + mm * kSCtaN + ncol : nullptr;
-          dst[e] = (int64_t)mm * args.n + n;
-          acc[e] = ok ? __ldcg(reinterpret_cast<const float4*>(src[e] + lo_slot * kSlotFloats))
-                      : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        for (int c = 1; c < parts; c += 2) {  // fixed order; kB x 2 loads in flight
-          float4 v[kB][2];
-#pragma unroll
-          for (int e = 0; e < kB; ++e)
-#pragma unroll
-            for (int d = 0; d < 2; ++d)
-              v[e][d] = (src[e] != nullptr && c + d < parts)
-                            ? __ldcg(reinterpret_cast<const float4*>(src[e] + (int64_t)(c + d) * 2 * kSlotFloats))
-                            : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-          for (int e = 0; e < kB; ++e)
-#pragma unroll
-            for (int d = 0; d < 2; ++d)
-              acc[e].x += v[e][d].x, acc[e].y += v[e][d].y, acc[e].z += v[e][d].z, acc[e].w += v[e][d].w;
-        }
-#pragma unroll
-        for (int e = 0; e < kB; ++e) {
-          if (src[e] == nullptr) continue;
-          uint2 o;
-          o.x = DT<T>::pack2(acc[e].x, acc[e].y);
-          o.y = DT<T>::pack2(acc[e].z, acc[e].w);
-          *reinterpret_cast<uint2*>(reinterpret_cast<T*>(args.c) + dst[e]) = o;
-        }
-      }
-      __syncthreads();
-      // second round of increments: the 2 x parts-th one wraps the counter back to zero (atom.inc
-      // semantics), which cannot happen before every contributor has passed its spin above
-      if (tid == 0) red_release_inc(&args.locks[tl], 2 * parts - 1);
-    }
-  }
+  if (threadIdx.x == 0) SPROF_MARK(31);
 }
 
 inline int64_t stream_ws_bytes(int m) {
