@@ -87,14 +87,8 @@ __device__ __forceinline__ int s_cta_of_unit(const StreamArgs& s, int u) {
   return (int)(((uint32_t)(u + 1) * (uint32_t)s.grid - 1u) / (uint32_t)s.units);
 }
 
-// fire-and-forget *p = (*p >= wrap) ? 0 : *p + 1 with gpu-scope release
-__device__ __forceinline__ void red_release_inc(int* p, int wrap) {
-  asm volatile("red.release.gpu.global.inc.u32 [%0], %1;" ::"l"(p), "r"(wrap) : "memory");
-}
-__device__ __forceinline__ int atom_add_acq_rel(int* p, int v) {
-  int old;
-  asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
-  return old;
+__device__ __forceinline__ void red_release_add(int* p, int v) {
+  asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
   int v;
@@ -121,7 +115,6 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
   uint64_t* tmem_full = empty_a + kSASlots;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;       // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  uint32_t* tail = tmem_slot + 1;  // epilogue scratch: "this CTA arrived last"
 
   // warp-uniform by construction: say so, so that role code keeps its operands in uniform registers
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
@@ -383,18 +376,20 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     if (warp == 2 && lane == 0) SPROF_FLUSH(8);
   } else {
     // ======================= epilogue + split-K fix-up =======================
-    // A whole tile is rounded once and stored.  A partial piece is published to this CTA's fp32
-    // slot ([column][token]: 64 contiguous bytes per thread) and the tile's arrival counter is
-    // bumped; whoever arrives LAST sums the contributors in CTA order -- its own piece straight from
-    // TMEM, the others from their slots -- rounds once, stores, and hands the counter back as zero.
-    // Nobody ever waits for another CTA; the summation order is fixed, so the result is
-    // deterministic.  A piece at the head of a range (the tile's other contributors finish later)
-    // is thus fixed up by someone else, a piece at the tail by this CTA, usually at once.
+    // A whole tile is rounded once and stored.  A tile that is split over several CTAs is fixed up
+    // by the CTA that owns its LOWEST k range: the unit order makes that piece the last one of its
+    // CTA's range, while the pieces of the higher k ranges come first in theirs -- the other
+    // contributors have usually published long before the fixer gets there.
+    //   publisher (piece starts at kb > 0): fp32 piece -> its slot ([column][token], 64 contiguous
+    //     bytes per thread) -> barrier -> one gpu-scope release increment of the tile's counter
+    //   fixer (piece starts at kb = 0): waits for parts - 1 arrivals (acquire), then sums in CTA
+    //     order -- its own piece straight from TMEM first, then the slots -- rounds once, stores,
+    //     and hands the counter back as zero.  Fixed order: deterministic.
     const int qd = warp & 3;
     const int et = (warp - 2 - kSDequantWarps) * 32 + lane;  // 0..127
     const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16) + kSDCol;
     constexpr int kSlotFloats = BM * kSCtaN;
-    float* my_slots = args.partial + (int64_t)blockIdx.x * 2 * kSlotFloats;
+    float* my_slot = args.partial + (int64_t)blockIdx.x * kSlotFloats;
     T* out = reinterpret_cast<T*>(args.c);
     uint32_t piece = 0;
     int done = 0, tile = tile0, kb = kb0;
@@ -402,36 +397,35 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     while (done < total) {
       const int cnt = min(num_kb - kb, total - done);
       const bool whole = cnt == num_kb;
+      const bool fixer = !whole && kb == 0;
       const uint32_t buf = piece & 1;
+      int c_hi = 0;
+      if (fixer) {
+        // contributors: this CTA (lowest k) .. c_hi; they publish parts - 1 pieces
+        c_hi = s_cta_of_unit(sa, (tile + 1) * num_kb - 1);
+        if (et == 0) {
+          const int need = c_hi - (int)blockIdx.x;
+          uint32_t spins = 0;
+          uint64_t t0 = 0;
+          while (ld_acquire_gpu(&args.locks[tile]) < need) {
+            if ((++spins & 0x3ffu) == 0) {
+              const uint64_t t = global_timer_ns();
+              if (t0 == 0) t0 = t;
+              else if (t - t0 > kMbarTimeoutNs) __trap();
+            }
+          }
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // thread 0's acquire covers the role
+      }
       SPROF(1);
       mbar_wait_bounded(&tmem_full[buf], (piece >> 1) & 1);
       SPROF(0);
       fence_after_sync();
       const uint32_t t_src = t_lane + buf * kDCols;
-      if (whole) {
+      if (!whole && !fixer) {
 #pragma unroll 1
         for (int h = 0; h < kSNT; ++h) {
-          const int n = tile * kSCtaN + h * kTileN + qd * 32 + lane;
-#pragma unroll 1
-          for (int c = 0; c < BM / 16; ++c) {
-            if (c * 16 >= args.m) break;
-            uint32_t rr[16];
-            tmem_ld16(t_src + h * BM + c * 16, rr);
-            tmem_ld_wait();
-            if (n < args.n) {
-#pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                const int mm = c * 16 + j;
-                if (mm < args.m) out[(int64_t)mm * args.n + n] = DT<T>::from_f(__uint_as_float(rr[j]));
-              }
-            }
-          }
-        }
-      } else {
-        float* slot = my_slots + (tile == tile0 ? 0 : kSlotFloats);
-#pragma unroll 1
-        for (int h = 0; h < kSNT; ++h) {
-          float* dst = slot + (h * kTileN + qd * 32 + lane) * BM;
+          float* dst = my_slot + (h * kTileN + qd * 32 + lane) * BM;
 #pragma unroll 1
           for (int c = 0; c < BM / 16; ++c) {
             if (c * 16 >= args.m) break;
@@ -444,67 +438,64 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
                 *reinterpret_cast<uint4*>(dst + c * 16 + j) = make_uint4(rr[j], rr[j + 1], rr[j + 2], rr[j + 3]);
           }
         }
-        // publish: the barrier orders the 128 threads' stores before thread 0's gpu-scope
-        // acq_rel increment (cumulative); its return value says whether this CTA arrived last
-        const int c_lo = s_cta_of_unit(sa, tile * num_kb), c_hi = s_cta_of_unit(sa, (tile + 1) * num_kb - 1);
+        // the barrier orders the 128 threads' stores before thread 0's release (cumulative)
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (et == 0) tail[0] = atom_add_acq_rel(&args.locks[tile], 1) == c_hi - c_lo ? 1u : 0u;
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (tail[0] != 0) {
-          // a contributor's piece sits in its slot 0 when the tile is the first of its range: true
-          // for every contributor except possibly the lowest
-          const int lo_slot = ((int)s_range_start(sa, c_lo) / num_kb == tile) ? 0 : 1;
-          const int me = (int)blockIdx.x;
+        if (et == 0) red_release_add(&args.locks[tile], 1);
+      } else {
+        const int me = (int)blockIdx.x;
 #pragma unroll 1
-          for (int h = 0; h < kSNT; ++h) {
-            const int ncol = h * kTileN + qd * 32 + lane;
-            const int n = tile * kSCtaN + ncol;
+        for (int h = 0; h < kSNT; ++h) {
+          const int ncol = h * kTileN + qd * 32 + lane;
+          const int n = tile * kSCtaN + ncol;
 #pragma unroll 1
-            for (int c = 0; c < BM / 16; ++c) {
-              if (c * 16 >= args.m) break;
+          for (int c = 0; c < BM / 16; ++c) {
+            if (c * 16 >= args.m) break;
+            uint32_t own[16];
+            tmem_ld16(t_src + h * BM + c * 16, own);
+            float acc[16];
+            if (fixer) {
               const int nq = (min(args.m - c * 16, 16) + 3) >> 2;  // float4 per thread
-              uint32_t own[16];
-              tmem_ld16(t_src + h * BM + c * 16, own);
-              float acc[16];
+              const float* src = args.partial + (int64_t)(me + 1) * kSlotFloats + ncol * BM + c * 16;
+              float4 v[2][4];
+              auto load = [&](int cc, float4 (&dstv)[4]) {
 #pragma unroll
-              for (int j = 0; j < 16; ++j) acc[j] = 0.f;
-              const float* src = args.partial + ((int64_t)c_lo * 2 + lo_slot) * kSlotFloats + ncol * BM + c * 16;
-              for (int cc = c_lo; cc <= c_hi; cc += 2) {  // fixed order, two contributors in flight
-                float4 v[2][4];
+                for (int e = 0; e < 4; ++e)
+                  dstv[e] = (cc <= c_hi && e < nq && n < args.n)
+                                ? __ldcg(reinterpret_cast<const float4*>(src + (int64_t)(cc - me - 1) * kSlotFloats) + e)
+                                : make_float4(0.f, 0.f, 0.f, 0.f);
+              };
+              load(me + 1, v[0]);
+              load(me + 2, v[1]);
+              tmem_ld_wait();
 #pragma unroll
-                for (int d = 0; d < 2; ++d) {
-                  const float* sp = cc + d == c_lo ? src : src + ((int64_t)(cc + d - c_lo) * 2 - lo_slot) * kSlotFloats;
+              for (int j = 0; j < 16; ++j) acc[j] = __uint_as_float(own[j]);
+              for (int cc = me + 1; cc <= c_hi; cc += 2) {  // fixed order, two contributors in flight
+#pragma unroll
+                for (int d = 0; d < 2; ++d)
 #pragma unroll
                   for (int e = 0; e < 4; ++e)
-                    v[d][e] = (cc + d <= c_hi && cc + d != me && e < nq && n < args.n)
-                                  ? __ldcg(reinterpret_cast<const float4*>(sp) + e)
-                                  : make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-                tmem_ld_wait();
-#pragma unroll
-                for (int d = 0; d < 2; ++d) {
-                  if (cc + d == me) {
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) acc[j] += __uint_as_float(own[j]);
-                  } else {
-#pragma unroll
-                    for (int e = 0; e < 4; ++e)
-                      acc[4 * e] += v[d][e].x, acc[4 * e + 1] += v[d][e].y, acc[4 * e + 2] += v[d][e].z,
-                          acc[4 * e + 3] += v[d][e].w;
-                  }
+                    acc[4 * e] += v[d][e].x, acc[4 * e + 1] += v[d][e].y, acc[4 * e + 2] += v[d][e].z,
+                        acc[4 * e + 3] += v[d][e].w;
+                if (cc + 2 <= c_hi) {
+                  load(cc + 2, v[0]);
+                  load(cc + 3, v[1]);
                 }
               }
-              if (n < args.n) {
+            } else {
+              tmem_ld_wait();
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                  const int mm = c * 16 + j;
-                  if (mm < args.m) out[(int64_t)mm * args.n + n] = DT<T>::from_f(acc[j]);
-                }
+              for (int j = 0; j < 16; ++j) acc[j] = __uint_as_float(own[j]);
+            }
+            if (n < args.n) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const int mm = c * 16 + j;
+                if (mm < args.m) out[(int64_t)mm * args.n + n] = DT<T>::from_f(acc[j]);
               }
             }
           }
-          if (et == 0) args.locks[tile] = 0;
         }
+        if (fixer && et == 0) args.locks[tile] = 0;
       }
       fence_before_sync();
       __syncwarp();
@@ -530,7 +521,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
 
 inline int64_t stream_ws_bytes(int m) {
   const int bm = m <= 16 ? 16 : m <= 32 ? 32 : 64;
-  return (int64_t)num_sms() * 2 * bm * kSCtaN * 4;
+  return (int64_t)num_sms() * bm * kSCtaN * 4;  // one fp32 slot per CTA (a range publishes at most one piece)
 }
 
 template <int BITS, int BM, typename T>
