@@ -888,6 +888,20 @@ inline int decode_kernel_choice() {
   return env_int_once("B200_MARLIN_DECODE_V1", knob, 0);
 }
 
+// The stream-K kernel wins where every n tile is shared by at most ~3 CTAs (the split-K fix-up is
+// then one or two slot reads by a CTA that is done anyway): layers with at least num_sms / 2 tiles
+// of 256 columns, e.g. Llama-3-8B gate_up.  Narrow layers (qkv, o, down: 16-24 tiles, each split
+// over ~10 CTAs) stay with the first-generation kernel -- measured, profiles/r2_marlin_stream.md.
+// B200_MARLIN_DECODE_V1 = 1 forces the first-generation kernel, 2 forces the stream-K kernel.
+inline bool stream_kernel_pays(const b200_gptq_marlin_gemm_params& p) {
+  const int64_t n_tiles = (p.size_n + kSCtaN - 1) / kSCtaN;
+  if ((n_tiles * (p.size_k / kStageK) + 1) * num_sms() >= (1ll << 31)) return false;
+  const int choice = decode_kernel_choice();
+  if (choice == 1) return false;
+  if (choice == 2) return true;
+  return n_tiles * 2 >= num_sms();
+}
+
 template <int BITS, typename T, bool ACT>
 int dispatch_bm(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t lda, cudaStream_t st) {
   // decode kernel: ungrouped, or groups that never change inside a 64-k stage
@@ -895,8 +909,7 @@ int dispatch_bm(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64
   const int gsz = p.num_groups > 1 ? p.size_k / p.num_groups : 0;
   const bool one_group_per_stage = p.num_groups == 1 || (gsz % kStageK == 0 && (gsz & (gsz - 1)) == 0);
   if (!ACT && one_group_per_stage && p.size_m <= 64 && p.workspace != nullptr && p.splitk_ws != nullptr &&
-      p.splitk_ws_bytes >= stream_ws_bytes(p.size_m) && decode_kernel_choice() == 0 &&
-      ((int64_t)(p.size_n + kSCtaN - 1) / kSCtaN * (p.size_k / kStageK) + 1) * num_sms() < (1ll << 31)) {
+      p.splitk_ws_bytes >= stream_ws_bytes(p.size_m) && stream_kernel_pays(p)) {
     switch (pick_bm(p.size_m)) {
       case 16: return launch_stream<BITS, 16, T>(p, st);
       case 32: return launch_stream<BITS, 32, T>(p, st);
