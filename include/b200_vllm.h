@@ -228,6 +228,10 @@ B200_API int64_t b200_gptq_marlin_gemm_workspace_bytes(int32_t m, int32_t n, int
 /* test hook: out [size_k, size_n] (dtype) = dequantised weights, produced by the same unpack /
  * scale device code the GEMM uses (bit-exact against the reference's w_ref,
  * quant_utils.py:73). No act-order. */
+/* test hook: which W4A16/W8A16 decode kernel gptq_marlin_gemm takes at M <= 64 (0 heuristic,
+ * 1 first-generation split-K kernel, 2 stream-K kernel wherever eligible, -1 environment) */
+B200_API void b200_debug_set_marlin_decode_kernel(int32_t choice);
+
 /* debug only: cycle accounting of the stream-K decode kernel; returns the number of uint64 copied
  * (0 unless built with -DB200_STREAM_PROF) */
 B200_API int b200_debug_stream_prof(unsigned long long* dst, int32_t n);

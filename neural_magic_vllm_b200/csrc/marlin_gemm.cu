@@ -883,7 +883,9 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
 #include "marlin_gemm_stream.cuh"
 
 // which decode kernel: 0 = stream-K persistent (default), 1 = first-generation split-K kernel
+int g_decode_choice_override = -1;  // tests: b200_debug_set_marlin_decode_kernel
 inline int decode_kernel_choice() {
+  if (g_decode_choice_override >= 0) return g_decode_choice_override;
   static int knob[2] = {0, 0};
   return env_int_once("B200_MARLIN_DECODE_V1", knob, 0);
 }
@@ -993,6 +995,10 @@ int b200_gptq_marlin_gemm(const b200_gptq_marlin_gemm_params* pp, void* stream) 
   set_error("gpt_marlin_gemm only supports bfloat16 and float16");
   return B200_EINVAL;
 }
+
+// test hook: 0 = heuristic, 1 = first-generation decode kernel, 2 = stream-K kernel wherever it is
+// eligible, -1 = back to the environment (B200_MARLIN_DECODE_V1)
+void b200_debug_set_marlin_decode_kernel(int32_t choice) { b200::g_decode_choice_override = choice; }
 
 // debug: per-CTA cycle accounting of the stream-K decode kernel (all zeros unless the library was
 // built with -DB200_STREAM_PROF).  dst = 160 x 32 uint64 on the host.

@@ -442,56 +442,53 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
         asm volatile("bar.sync 1, 128;" ::: "memory");
         if (et == 0) red_release_add(&args.locks[tile], 1);
       } else {
+        // chunks of 16 tokens x this thread's column, flattened over (sub-tile, token chunk); the
+        // fixer prefetches the first other contributor's piece of chunk i + 1 while it sums chunk i
         const int me = (int)blockIdx.x;
+        const int n_chunks = kSNT * ((min(args.m, BM) + 15) / 16);
+        const int per_h = n_chunks / kSNT;
+        const float* slot1 = args.partial + (int64_t)(me + 1) * kSlotFloats;
+        auto chunk_src = [&](int i) { return slot1 + ((i / per_h) * kTileN + qd * 32 + lane) * BM + (i % per_h) * 16; };
+        auto load4 = [&](const float* sp, int i, float4 (&dstv)[4]) {
+          const int nq = (min(args.m - (i % per_h) * 16, 16) + 3) >> 2;  // float4 per thread
+          const bool ok = tile * kSCtaN + (i / per_h) * kTileN + qd * 32 + lane < args.n;
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            dstv[e] = (ok && e < nq) ? __ldcg(reinterpret_cast<const float4*>(sp) + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+        };
+        float4 nxt[4];
+        if (fixer) load4(chunk_src(0), 0, nxt);
 #pragma unroll 1
-        for (int h = 0; h < kSNT; ++h) {
-          const int ncol = h * kTileN + qd * 32 + lane;
-          const int n = tile * kSCtaN + ncol;
-#pragma unroll 1
-          for (int c = 0; c < BM / 16; ++c) {
-            if (c * 16 >= args.m) break;
-            uint32_t own[16];
-            tmem_ld16(t_src + h * BM + c * 16, own);
-            float acc[16];
-            if (fixer) {
-              const int nq = (min(args.m - c * 16, 16) + 3) >> 2;  // float4 per thread
-              const float* src = args.partial + (int64_t)(me + 1) * kSlotFloats + ncol * BM + c * 16;
-              float4 v[2][4];
-              auto load = [&](int cc, float4 (&dstv)[4]) {
+        for (int i = 0; i < n_chunks; ++i) {
+          const int h = i / per_h, c = i % per_h;
+          const int n = tile * kSCtaN + h * kTileN + qd * 32 + lane;
+          uint32_t own[16];
+          tmem_ld16(t_src + h * BM + c * 16, own);
+          float4 cur[4];
 #pragma unroll
-                for (int e = 0; e < 4; ++e)
-                  dstv[e] = (cc <= c_hi && e < nq && n < args.n)
-                                ? __ldcg(reinterpret_cast<const float4*>(src + (int64_t)(cc - me - 1) * kSlotFloats) + e)
-                                : make_float4(0.f, 0.f, 0.f, 0.f);
-              };
-              load(me + 1, v[0]);
-              load(me + 2, v[1]);
-              tmem_ld_wait();
+          for (int e = 0; e < 4; ++e) cur[e] = nxt[e];
+          if (fixer && i + 1 < n_chunks) load4(chunk_src(i + 1), i + 1, nxt);
+          tmem_ld_wait();
+          float acc[16];
 #pragma unroll
-              for (int j = 0; j < 16; ++j) acc[j] = __uint_as_float(own[j]);
-              for (int cc = me + 1; cc <= c_hi; cc += 2) {  // fixed order, two contributors in flight
+          for (int j = 0; j < 16; ++j) acc[j] = __uint_as_float(own[j]);
+          if (fixer) {
 #pragma unroll
-                for (int d = 0; d < 2; ++d)
+            for (int e = 0; e < 4; ++e)
+              acc[4 * e] += cur[e].x, acc[4 * e + 1] += cur[e].y, acc[4 * e + 2] += cur[e].z, acc[4 * e + 3] += cur[e].w;
+            for (int cc = me + 2; cc <= c_hi; ++cc) {  // further contributors, fixed order
+              float4 v[4];
+              load4(chunk_src(i) + (int64_t)(cc - me - 1) * kSlotFloats, i, v);
 #pragma unroll
-                  for (int e = 0; e < 4; ++e)
-                    acc[4 * e] += v[d][e].x, acc[4 * e + 1] += v[d][e].y, acc[4 * e + 2] += v[d][e].z,
-                        acc[4 * e + 3] += v[d][e].w;
-                if (cc + 2 <= c_hi) {
-                  load(cc + 2, v[0]);
-                  load(cc + 3, v[1]);
-                }
-              }
-            } else {
-              tmem_ld_wait();
-#pragma unroll
-              for (int j = 0; j < 16; ++j) acc[j] = __uint_as_float(own[j]);
+              for (int e = 0; e < 4; ++e)
+                acc[4 * e] += v[e].x, acc[4 * e + 1] += v[e].y, acc[4 * e + 2] += v[e].z, acc[4 * e + 3] += v[e].w;
             }
-            if (n < args.n) {
+          }
+          if (n < args.n) {
 #pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                const int mm = c * 16 + j;
-                if (mm < args.m) out[(int64_t)mm * args.n + n] = DT<T>::from_f(acc[j]);
-              }
+            for (int j = 0; j < 16; ++j) {
+              const int mm = c * 16 + j;
+              if (mm < args.m) out[(int64_t)mm * args.n + n] = DT<T>::from_f(acc[j]);
             }
           }
         }
