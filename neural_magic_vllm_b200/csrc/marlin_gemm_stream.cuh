@@ -306,11 +306,6 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       int nstage = stage + 2;
       uint32_t nphase = phase;
       if (nstage >= kStages) nstage -= kStages, nphase ^= 1;
-      if (i + 2 < total) {
-        mbar_wait_bounded(&full_p[nstage], nphase);
-        fetch(nxt, nxt_sv, nstage);
-      }
-      SPROF(0);
       if constexpr (GROUPED) {
         sc[0] = dup16(cur_sv.x, 0), sc[1] = dup16(cur_sv.x, 1), sc[2] = dup16(cur_sv.y, 0), sc[3] = dup16(cur_sv.y, 1);
       } else if (sc_tile != tile) {
@@ -351,6 +346,12 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty_p[stage]);  // every lane has consumed its packed words + scales
       SPROF(3);
+      // the next job's operands are fetched while the tcgen05.st above drain into TMEM
+      if (i + 2 < total) {
+        mbar_wait_bounded(&full_p[nstage], nphase);
+        fetch(nxt, nxt_sv, nstage);
+      }
+      SPROF(0);
       tmem_st_wait();
       fence_before_sync();
       __syncwarp();
@@ -380,8 +381,8 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
     // by the CTA that owns its LOWEST k range: the unit order makes that piece the last one of its
     // CTA's range, while the pieces of the higher k ranges come first in theirs -- the other
     // contributors have usually published long before the fixer gets there.
-    //   publisher (piece starts at kb > 0): fp32 piece -> its slot ([column][token], 64 contiguous
-    //     bytes per thread) -> barrier -> one gpu-scope release increment of the tile's counter
+    //   publisher (piece starts at kb > 0): fp32 piece -> its slot ([token][column]: one 128-byte
+    //     line per warp access) -> barrier -> one gpu-scope release increment of the tile's counter
     //   fixer (piece starts at kb = 0): waits for parts - 1 arrivals (acquire), then sums in CTA
     //     order -- its own piece straight from TMEM first, then the slots -- rounds once, stores,
     //     and hands the counter back as zero.  Fixed order: deterministic.
@@ -425,7 +426,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
       if (!whole && !fixer) {
 #pragma unroll 1
         for (int h = 0; h < kSNT; ++h) {
-          float* dst = my_slot + (h * kTileN + qd * 32 + lane) * BM;
+          float* dst = my_slot + h * kTileN + qd * 32 + lane;
 #pragma unroll 1
           for (int c = 0; c < BM / 16; ++c) {
             if (c * 16 >= args.m) break;
@@ -433,9 +434,8 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
             tmem_ld16(t_src + h * BM + c * 16, rr);
             tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 16; j += 4)
-              if (c * 16 + j < args.m)
-                *reinterpret_cast<uint4*>(dst + c * 16 + j) = make_uint4(rr[j], rr[j + 1], rr[j + 2], rr[j + 3]);
+            for (int j = 0; j < 16; ++j)
+              if (c * 16 + j < args.m) dst[(c * 16 + j) * kSCtaN] = __uint_as_float(rr[j]);
           }
         }
         // the barrier orders the 128 threads' stores before thread 0's release (cumulative)
@@ -448,40 +448,39 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
         const int n_chunks = kSNT * ((min(args.m, BM) + 15) / 16);
         const int per_h = n_chunks / kSNT;
         const float* slot1 = args.partial + (int64_t)(me + 1) * kSlotFloats;
-        auto chunk_src = [&](int i) { return slot1 + ((i / per_h) * kTileN + qd * 32 + lane) * BM + (i % per_h) * 16; };
-        auto load4 = [&](const float* sp, int i, float4 (&dstv)[4]) {
-          const int nq = (min(args.m - (i % per_h) * 16, 16) + 3) >> 2;  // float4 per thread
+        auto chunk_src = [&](int i) {
+          return slot1 + (i % per_h) * 16 * kSCtaN + (i / per_h) * kTileN + qd * 32 + lane;
+        };
+        auto load16 = [&](const float* sp, int i, float (&dstv)[16]) {
+          const int rows = min(args.m - (i % per_h) * 16, 16);
           const bool ok = tile * kSCtaN + (i / per_h) * kTileN + qd * 32 + lane < args.n;
 #pragma unroll
-          for (int e = 0; e < 4; ++e)
-            dstv[e] = (ok && e < nq) ? __ldcg(reinterpret_cast<const float4*>(sp) + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int j = 0; j < 16; ++j) dstv[j] = (ok && j < rows) ? __ldcg(sp + j * kSCtaN) : 0.f;
         };
-        float4 nxt[4];
-        if (fixer) load4(chunk_src(0), 0, nxt);
+        float nxt[16];
+        if (fixer) load16(chunk_src(0), 0, nxt);
 #pragma unroll 1
         for (int i = 0; i < n_chunks; ++i) {
           const int h = i / per_h, c = i % per_h;
           const int n = tile * kSCtaN + h * kTileN + qd * 32 + lane;
           uint32_t own[16];
           tmem_ld16(t_src + h * BM + c * 16, own);
-          float4 cur[4];
+          float cur[16];
 #pragma unroll
-          for (int e = 0; e < 4; ++e) cur[e] = nxt[e];
-          if (fixer && i + 1 < n_chunks) load4(chunk_src(i + 1), i + 1, nxt);
+          for (int j = 0; j < 16; ++j) cur[j] = nxt[j];
+          if (fixer && i + 1 < n_chunks) load16(chunk_src(i + 1), i + 1, nxt);
           tmem_ld_wait();
           float acc[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) acc[j] = __uint_as_float(own[j]);
           if (fixer) {
 #pragma unroll
-            for (int e = 0; e < 4; ++e)
-              acc[4 * e] += cur[e].x, acc[4 * e + 1] += cur[e].y, acc[4 * e + 2] += cur[e].z, acc[4 * e + 3] += cur[e].w;
+            for (int j = 0; j < 16; ++j) acc[j] += cur[j];
             for (int cc = me + 2; cc <= c_hi; ++cc) {  // further contributors, fixed order
-              float4 v[4];
-              load4(chunk_src(i) + (int64_t)(cc - me - 1) * kSlotFloats, i, v);
+              float v[16];
+              load16(chunk_src(i) + (int64_t)(cc - me - 1) * kSlotFloats, i, v);
 #pragma unroll
-              for (int e = 0; e < 4; ++e)
-                acc[4 * e] += v[e].x, acc[4 * e + 1] += v[e].y, acc[4 * e + 2] += v[e].z, acc[4 * e + 3] += v[e].w;
+              for (int j = 0; j < 16; ++j) acc[j] += v[j];
             }
           }
           if (n < args.n) {
