@@ -110,7 +110,7 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
   uint2* lut = reinterpret_cast<uint2*>(bars + 32);  // 16 x 8 bytes, 256 bytes into the barrier block
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * BM;
   const int n0 = blockIdx.y * kTileN;
   const int split = blockIdx.z;
@@ -138,16 +138,17 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0) {
+    const bool leader = elect_one();  // issue under elect.sync: uniform-register operands (see scaled_mm.cu)
     const uint64_t pol_w = l2_policy_evict_first();
     const uint64_t pol_x = l2_policy_evict_last();
     const uint32_t tx_bytes = P::kXBytes + kValBytes + kMetaBytes + (grouped ? kTileN * 2 : 0);
     // programmatic dependent launch: values / metadata / scales of the first ring of stages
     // stream in before the wait; only the activation tiles depend on the predecessor
     const int pre = min(kb_end - kb_begin, kStages);
-    if (lane == 0) {
+    if (leader) {
       for (int i = 0; i < pre; ++i) {
         const int kb = kb_begin + i;
         uint8_t* w_dst = stages + i * P::kStageBytes + P::kXBytes;
@@ -160,7 +161,7 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
       }
     }
     pdl_wait();
-    if (lane == 0) {
+    if (leader) {
       for (int i = 0; i < pre; ++i)
         tma_load_2d(stages + i * P::kStageBytes, &tm_x, (kb_begin + i) * kStageK, m0, &full_p[i], pol_x);
     }
@@ -169,7 +170,7 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
     uint32_t phase = pre == kStages ? 1 : 0;
     for (int kb = kb_begin + pre; kb < kb_end; ++kb) {
       mbar_wait_bounded(&empty_p[stage], phase ^ 1);
-      if (lane == 0) {
+      if (leader) {
         uint8_t* x_dst = stages + stage * P::kStageBytes;
         uint8_t* w_dst = x_dst + P::kXBytes;
         mbar_arrive_expect_tx(&full_p[stage], tx_bytes);
@@ -184,25 +185,29 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
       if (++stage == kStages) stage = 0, phase ^= 1;
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    // whole warp runs the loop (uniform operands); one elected lane issues (see scaled_mm.cu)
+    const bool leader = elect_one();
+    {
       constexpr uint32_t idesc = instr_desc<KIND_F16>(kTileN, BM);
       int stage = 0, as = 0;
-      uint32_t phase = 0, aphase = 0;
+      uint32_t aphase = 0;
       for (int kb = kb_begin; kb < kb_end; ++kb) {
-        mbar_wait_bounded(&full_p[stage], phase);
+        // a full_a arrival implies the stage's full_p: the dequant warps waited on it first
         mbar_wait_bounded(&full_a[as], aphase);
         fence_after_sync();
         const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
+        if (leader) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          mma_ts_f16(tmem_base + kDCol, tmem_base + as * kACols + k * 8, desc_advance(dx, k * 32), idesc,
-                     (kb > kb_begin || k > 0) ? 1u : 0u);
-        mma_commit(&empty_a[as]);
-        mma_commit(&empty_p[stage]);
-        if (++stage == kStages) stage = 0, phase ^= 1;
+          for (int k = 0; k < 4; ++k)
+            mma_ts_f16(tmem_base + kDCol, tmem_base + as * kACols + k * 8, desc_advance(dx, k * 32), idesc,
+                       (kb > kb_begin || k > 0) ? 1u : 0u);
+          mma_commit(&empty_a[as]);
+          mma_commit(&empty_p[stage]);
+        }
+        if (++stage == kStages) stage = 0;
         if (++as == kAStages) as = 0, aphase ^= 1;
       }
-      mma_commit(tmem_full);
+      if (leader) mma_commit(tmem_full);
       pdl_launch_dependents();  // main loop issued: the next kernel may become resident and wait
     }
   } else {

@@ -106,7 +106,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
   uint64_t* tmem_full = empty_a + kAStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * BM;
   const int n0 = blockIdx.y * kCtaN;
   const int split = blockIdx.z;
@@ -132,9 +132,10 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0) {
+    const bool leader = elect_one();  // issue under elect.sync: uniform-register operands (see scaled_mm.cu)
     // ======================= producer =======================
     // the whole warp runs the loop (uniform control flow keeps every operand in uniform
     // registers); lane 0 issues: one TMA per operand per stage
@@ -147,7 +148,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
     uint32_t phase = 0;
     for (int kb = kb_begin; kb < kb_end; ++kb) {
       mbar_wait_bounded(&empty_p[stage], phase ^ 1);
-      if (lane == 0) {
+      if (leader) {
         uint8_t* x_dst = stages + stage * P::kStageBytes;
         uint8_t* w_dst = x_dst + P::kXBytes;
         uint8_t* s_dst = w_dst + P::kPackedBytes;
@@ -164,29 +165,33 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
     }
   } else if (warp == 1) {
     // ======================= MMA issuer =======================
-    if (lane == 0) {
+    // whole warp runs the loop (uniform operands); one elected lane issues (see scaled_mm.cu)
+    const bool leader = elect_one();
+    {
       constexpr uint32_t idesc = instr_desc<KIND>(kTileN, BM);
       int stage = 0, as = 0;
-      uint32_t phase = 0, aphase = 0;
+      uint32_t aphase = 0;
       for (int kb = kb_begin; kb < kb_end; ++kb) {
-        mbar_wait_bounded(&full_p[stage], phase);  // activation tile landed
-        mbar_wait_bounded(&full_a[as], aphase);    // dequantised weights written
+        // dequantised weights written; implies the stage's full_p (the dequant warps waited on it)
+        mbar_wait_bounded(&full_a[as], aphase);
         fence_after_sync();
         const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
+        if (leader) {
 #pragma unroll
-        for (int h = 0; h < NT; ++h) {
-          const uint64_t dw = smem_desc_sw128(smem_u32(a_tiles + as * kATileBytes + h * kSubTileBytes));
+          for (int h = 0; h < NT; ++h) {
+            const uint64_t dw = smem_desc_sw128(smem_u32(a_tiles + as * kATileBytes + h * kSubTileBytes));
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            mma_ss<KIND>(tmem_base + h * BM, desc_advance(dw, k * 32), desc_advance(dx, k * 32), idesc,
-                         (kb > kb_begin || k > 0) ? 1u : 0u);
+            for (int k = 0; k < 4; ++k)
+              mma_ss<KIND>(tmem_base + h * BM, desc_advance(dw, k * 32), desc_advance(dx, k * 32), idesc,
+                           (kb > kb_begin || k > 0) ? 1u : 0u);
+          }
+          mma_commit(&empty_a[as]);
+          mma_commit(&empty_p[stage]);
         }
-        mma_commit(&empty_a[as]);
-        mma_commit(&empty_p[stage]);
-        if (++stage == kStages) stage = 0, phase ^= 1;
+        if (++stage == kStages) stage = 0;
         if (++as == kAStages) as = 0, aphase ^= 1;
       }
-      mma_commit(tmem_full);
+      if (leader) mma_commit(tmem_full);
     }
   } else {
     // ======================= dequant (8 warps) + epilogue (first 4 of them) ==================
@@ -413,9 +418,10 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0) {
+    const bool leader = elect_one();  // issue under elect.sync: uniform-register operands (see scaled_mm.cu)
     // the whole warp runs the loop (uniform control flow keeps every operand in uniform
     // registers); lane 0 issues: one TMA per operand per stage
     const uint64_t pol_w = args.w_evict_first ? l2_policy_evict_first() : l2_policy_evict_last();
@@ -427,7 +433,7 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
     // that produces the activations) is still running.  Weights and scales do not depend on it, so
     // the first ring of stages streams them in right away; only the activation tiles wait.
     const int pre = min(kb_end - kb_begin, kStages);
-    if (lane == 0) {
+    if (leader) {
       for (int i = 0; i < pre; ++i) {  // fresh ring: every stage is empty
         const int kb = kb_begin + i;
         uint8_t* w_dst = stages + i * P::kStageBytes + P::kXBytes;
@@ -440,7 +446,7 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
       }
     }
     pdl_wait();  // the predecessor grid has completed: activations are visible
-    if (lane == 0) {
+    if (leader) {
       for (int i = 0; i < pre; ++i)
         tma_load_2d(stages + i * P::kStageBytes, &tm_x, (kb_begin + i) * kStageK, m0, &full_p[i], pol_x);
     }
@@ -449,7 +455,7 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
     uint32_t phase = pre == kStages ? 1 : 0;
     for (int kb = kb_begin + pre; kb < kb_end; ++kb) {
       mbar_wait_bounded(&empty_p[stage], phase ^ 1);
-      if (lane == 0) {
+      if (leader) {
         uint8_t* x_dst = stages + stage * P::kStageBytes;
         uint8_t* w_dst = x_dst + P::kXBytes;
         uint8_t* s_dst = w_dst + P::kPackedBytes;
@@ -465,25 +471,29 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
       if (++stage == kStages) stage = 0, phase ^= 1;
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    // whole warp runs the loop (uniform operands); one elected lane issues (see scaled_mm.cu)
+    const bool leader = elect_one();
+    {
       constexpr uint32_t idesc = instr_desc<KIND>(kTileN, BM);
       int stage = 0, as = 0;
-      uint32_t phase = 0, aphase = 0;
+      uint32_t aphase = 0;
       for (int kb = kb_begin; kb < kb_end; ++kb) {
-        mbar_wait_bounded(&full_p[stage], phase);
+        // a full_a arrival implies the stage's full_p: the dequant warps waited on it first
         mbar_wait_bounded(&full_a[as], aphase);
         fence_after_sync();
         const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
+        if (leader) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          mma_ts_f16(tmem_base + kTmemDCol, tmem_base + as * kTmemAStageCols + k * 8,
-                     desc_advance(dx, k * 32), idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
-        mma_commit(&empty_a[as]);
-        mma_commit(&empty_p[stage]);
-        if (++stage == kStages) stage = 0, phase ^= 1;
+          for (int k = 0; k < 4; ++k)
+            mma_ts_f16(tmem_base + kTmemDCol, tmem_base + as * kTmemAStageCols + k * 8,
+                       desc_advance(dx, k * 32), idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
+          mma_commit(&empty_a[as]);
+          mma_commit(&empty_p[stage]);
+        }
+        if (++stage == kStages) stage = 0;
         if (++as == kAStages) as = 0, aphase ^= 1;
       }
-      mma_commit(tmem_full);
+      if (leader) mma_commit(tmem_full);
       // main loop issued: the next kernel in the stream may become resident (its prologue and, for
       // a GEMM, its first weight stages overlap this grid's epilogue) and wait for our completion
       pdl_launch_dependents();

@@ -62,7 +62,8 @@ scaled_mm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
   float* s_ascale = reinterpret_cast<float*>(smem + kStages * S::kStageBytes + 256);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp-uniform by construction: say so, so the role loops keep their operands in uniform registers
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * BM;
   const int n0 = blockIdx.y * kTileN;
   const int split = blockIdx.z;
@@ -83,37 +84,48 @@ scaled_mm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
+  // Producer and MMA issuer run their loops with the whole warp (uniform control flow); only the
+  // TMA / MMA instructions themselves sit under elect_one().  Issued from inside an `if (lane == 0)`
+  // region their uniform-register operands were rebuilt per instruction (R2UR + a one-trip
+  // waterfall loop, ~100 cycles per tcgen05.mma): measured, profiles/r2_marlin_stream.md.
   if (warp == 0) {
-    if (lane == 0) {
+    const bool leader = elect_one();
+    {
       const uint64_t pol_w = args.w_evict_first ? l2_policy_evict_first() : l2_policy_evict_last();
       const uint64_t pol_x = l2_policy_evict_last();
       // programmatic dependent launch: weights do not depend on the predecessor (the activation
       // quantiser), so the first ring of weight tiles streams in before the wait
       const int pre = min(kb_end - kb_begin, kStages);
       for (int i = 0; i < pre; ++i) {
-        mbar_arrive_expect_tx(&full_bar[i], S::kStageBytes);
-        tma_load_2d(tiles + i * S::kStageBytes, &tm_w, (kb_begin + i) * kStageKBytes, n0, &full_bar[i], pol_w);
+        if (leader) {
+          mbar_arrive_expect_tx(&full_bar[i], S::kStageBytes);
+          tma_load_2d(tiles + i * S::kStageBytes, &tm_w, (kb_begin + i) * kStageKBytes, n0, &full_bar[i], pol_w);
+        }
       }
       pdl_wait();
       for (int i = 0; i < pre; ++i)
-        tma_load_2d(tiles + i * S::kStageBytes + kTileN * kStageKBytes, &tm_x, (kb_begin + i) * kStageKBytes, m0,
-                    &full_bar[i], pol_x);
+        if (leader)
+          tma_load_2d(tiles + i * S::kStageBytes + kTileN * kStageKBytes, &tm_x, (kb_begin + i) * kStageKBytes, m0,
+                      &full_bar[i], pol_x);
       int stage = pre == kStages ? 0 : pre;
       uint32_t phase = pre == kStages ? 1 : 0;
       for (int kb = kb_begin + pre; kb < kb_end; ++kb) {
         mbar_wait_bounded(&empty_bar[stage], phase ^ 1);
         uint8_t* w_dst = tiles + stage * S::kStageBytes;
         uint8_t* x_dst = w_dst + kTileN * kStageKBytes;
-        mbar_arrive_expect_tx(&full_bar[stage], S::kStageBytes);
-        tma_load_2d(w_dst, &tm_w, kb * kStageKBytes, n0, &full_bar[stage], pol_w);
-        tma_load_2d(x_dst, &tm_x, kb * kStageKBytes, m0, &full_bar[stage], pol_x);
+        if (leader) {
+          mbar_arrive_expect_tx(&full_bar[stage], S::kStageBytes);
+          tma_load_2d(w_dst, &tm_w, kb * kStageKBytes, n0, &full_bar[stage], pol_w);
+          tma_load_2d(x_dst, &tm_x, kb * kStageKBytes, m0, &full_bar[stage], pol_x);
+        }
         if (++stage == kStages) stage = 0, phase ^= 1;
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    const bool leader = elect_one();
+    {
       constexpr uint32_t idesc = instr_desc<KIND>(kTileN, BM);
       int stage = 0;
       uint32_t phase = 0;
@@ -123,14 +135,16 @@ scaled_mm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant
         const uint32_t w_addr = smem_u32(tiles + stage * S::kStageBytes);
         const uint64_t dw = smem_desc_sw128(w_addr);
         const uint64_t dx = smem_desc_sw128(w_addr + kTileN * kStageKBytes);
+        if (leader) {
 #pragma unroll
-        for (int k = 0; k < kStageKBytes / 32; ++k)
-          mma_ss<KIND>(tmem_base, desc_advance(dw, k * 32), desc_advance(dx, k * 32), idesc,
-                       (kb > kb_begin || k > 0) ? 1u : 0u);
-        mma_commit(&empty_bar[stage]);
+          for (int k = 0; k < kStageKBytes / 32; ++k)
+            mma_ss<KIND>(tmem_base, desc_advance(dw, k * 32), desc_advance(dx, k * 32), idesc,
+                         (kb > kb_begin || k > 0) ? 1u : 0u);
+          mma_commit(&empty_bar[stage]);
+        }
         if (++stage == kStages) stage = 0, phase ^= 1;
       }
-      mma_commit(tmem_full);
+      if (leader) mma_commit(tmem_full);
       pdl_launch_dependents();  // main loop issued: the next kernel may become resident and wait
     }
   } else {
