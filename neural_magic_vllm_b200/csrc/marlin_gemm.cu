@@ -674,6 +674,8 @@ __global__ void __launch_bounds__(256) permute_cols_kernel(T* __restrict__ dst, 
 template <typename T>
 __global__ void __launch_bounds__(256) splitk_sum_kernel(T* __restrict__ out, const float* __restrict__ ws,
                                                          int64_t total, int splits) {
+  pdl_wait();                // launched as a programmatic dependent of the GEMM: partials complete
+  pdl_launch_dependents();   // (a no-op wait / trigger for a normal launch)
   for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < total;
        i += (int64_t)gridDim.x * blockDim.x * 4) {
     float4 acc = *reinterpret_cast<const float4*>(ws + i);
@@ -865,8 +867,8 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   cfg.attrs = pdl_attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
   cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tm_x, tm_w, tm_s, a);
-  cfg.attrs = nullptr;
-  cfg.numAttrs = 0;
+  // (the split-K sum kernel below is launched as a programmatic dependent too: it waits for the
+  // GEMM grid at its top, so only its launch latency overlaps the GEMM's tail)
   if (le != cudaSuccess) {
     cudaGetLastError();
     set_error("gptq_marlin_gemm: launch failed: %s", cudaGetErrorString(le));
@@ -900,10 +902,11 @@ inline int decode_kernel_choice() {
   return env_int_once("B200_MARLIN_DECODE_V1", knob, 0);
 }
 
-// The stream-K kernel wins where every n tile is shared by at most ~3 CTAs (the split-K fix-up is
+// The stream-K kernel pays where every n tile is shared by at most ~3 CTAs (the split-K fix-up is
 // then one or two slot reads by a CTA that is done anyway): layers with at least num_sms / 2 tiles
-// of 256 columns, e.g. Llama-3-8B gate_up.  Narrow layers (qkv, o, down: 16-24 tiles, each split
-// over ~10 CTAs) stay with the first-generation kernel -- measured, profiles/r2_marlin_stream.md.
+// of 256 columns, e.g. Llama-3-8B gate_up (20.3 vs 21.6 us at M = 1).  Narrow layers (qkv, o, down:
+// 16-24 tiles, each split over ~10 CTAs) stay with the first-generation kernel -- measured,
+// profiles/r2_marlin_stream.md.
 // B200_MARLIN_DECODE_V1 = 1 forces the first-generation kernel, 2 forces the stream-K kernel.
 inline bool stream_kernel_pays(const b200_gptq_marlin_gemm_params& p) {
   const int64_t n_tiles = (p.size_n + kSCtaN - 1) / kSCtaN;
@@ -911,7 +914,8 @@ inline bool stream_kernel_pays(const b200_gptq_marlin_gemm_params& p) {
   const int choice = decode_kernel_choice();
   if (choice == 1) return false;
   if (choice == 2) return true;
-  return n_tiles * 2 >= num_sms();
+  // (at M = 64 the fp32 pieces are 64 KiB each and the first-generation kernel wins: measured)
+  return n_tiles * 2 >= num_sms() && p.size_m <= 32;
 }
 
 template <int BITS, typename T, bool ACT>
