@@ -1,5 +1,5 @@
-// gptq_marlin_24_gemm on tcgen05 / TMEM (sm_100a): C[M,N] = A[M,K] * W, W 4-bit, 2:4 sparse along K,
-// in the reference's Marlin-24 layout (values [K/32, 2N] int32, metadata [K/32, 2N] int16, scales
+// gptq_marlin_24_gemm on tcgen05 / TMEM (sm_100a): C[M,N] = A[M,K] * W, W 4-bit or 8-bit, 2:4 sparse
+// along K, in the reference's Marlin-24 layout (values [K/32, 2N | 4N] int32, metadata [K/32, 2N] int16, scales
 // [K/128 | 1, N] fp16).  Replaces csrc/quantization/marlin/sparse/marlin_24_cuda_kernel.cu:1015-1125
 // (mma.sp.m16n8k32).  fp16 only, like the reference (:1100-1103: group 128 or channelwise).
 //
@@ -20,6 +20,9 @@
 //            owns words 4i..4i+3; word j holds n = 8c + 4b + j for b = 0,1 and the kept pairs of the
 //            4-groups g = r and g = r + 4:  nibbles (0,4) = (b0, g=r), (1,5) = (b0, g=r+4),
 //            (2,6) = (b1, g=r), (3,7) = (b1, g=r+4)
+//            8-bit (interleave {0,2,1,3} instead of {0,2,4,6,1,3,5,7}): the tile is 256 int32, lane i
+//            owns words 8i..8i+7, word 2j + b holds n = 8c + 4b + j with bytes = (g=r first value,
+//            g=r+4 first, g=r second, g=r+4 second) -- the byte order unpack8 of the dense kernel takes
 //   metadata per (32-k row, 64-n chunk) 256 bytes; the 8 bytes at unit u = (j%2) + 16 (j/2) + 2c are
 //            four int16 [b0 groups 0-3, b1 groups 0-3, b0 groups 4-7, b1 groups 4-7] for n = 8c+4b+j;
 //            group g's nibble = idx0 | idx1 << 2 (positions of the two kept values)
@@ -43,7 +46,6 @@ constexpr int kACols = kStageK / 2;          // 32 TMEM columns per dense 64-k s
 constexpr int kDCol = kAStages * kACols;     // accumulator behind the A ring
 constexpr int kWarps = 4;                    // dequant warps
 constexpr int kThreads = 64 + kWarps * 32;
-constexpr int kValBytes = 2 * 1024;          // 2 rows of 32 dense k x 128 n
 constexpr int kMetaBytes = 2 * 512;
 constexpr int kScaleBytes = 1024;            // one row (256 B) padded: stages stay 1 KiB aligned
 
@@ -56,8 +58,9 @@ struct Args24 {
   int kb_per_split, num_kb;
 };
 
-template <int BM>
+template <int BM, int BITS>
 struct Plan24 {
+  static constexpr int kValBytes = 2 * 1024 * BITS / 4;  // 2 rows of 32 dense k x 128 n
   static constexpr int kXBytes = BM * 128;
   static constexpr int kStageBytes = kXBytes + kValBytes + kMetaBytes + kScaleBytes;
   static constexpr int kBytes = kStages * kStageBytes + 1024 + 512;
@@ -93,12 +96,14 @@ __device__ __forceinline__ uint2 expand_selectors(int m4) {
   return make_uint2(sel(0) | (sel(1) << 8), sel(2) | (sel(3) << 8));
 }
 
-template <int BM>
+template <int BM, int BITS>
 __global__ void __launch_bounds__(kThreads, (BM <= 32 ? 4 : 2))
 marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                      const __grid_constant__ CUtensorMap tm_m, const __grid_constant__ CUtensorMap tm_s,
                      const Args24 args) {
-  using P = Plan24<BM>;
+  using P = Plan24<BM, BITS>;
+  constexpr int kValBytes = P::kValBytes;
+  constexpr int kWordsPerN = BITS / 2;  // int32 per output column in one 32-k row: 2 | 4
   extern __shared__ uint8_t smem_raw[];
   uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(stages + kStages * P::kStageBytes);
@@ -153,7 +158,9 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
         const int kb = kb_begin + i;
         uint8_t* w_dst = stages + i * P::kStageBytes + P::kXBytes;
         mbar_arrive_expect_tx(&full_p[i], tx_bytes);
-        tma_load_2d(w_dst, &tm_w, n0 * 2, kb * 2, &full_p[i], pol_w);
+#pragma unroll
+        for (int l = 0; l < BITS / 4; ++l)
+          tma_load_2d(w_dst + l * 2048, &tm_w, n0 * kWordsPerN + l * 256, kb * 2, &full_p[i], pol_w);
         tma_load_2d(w_dst + kValBytes, &tm_m, n0 * 2, kb * 2, &full_p[i], pol_w);
         if (grouped)
           tma_load_2d(w_dst + kValBytes + kMetaBytes, &tm_s, n0, (kb * kStageK) >> args.group_shift,
@@ -175,7 +182,9 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
         uint8_t* w_dst = x_dst + P::kXBytes;
         mbar_arrive_expect_tx(&full_p[stage], tx_bytes);
         tma_load_2d(x_dst, &tm_x, kb * kStageK, m0, &full_p[stage], pol_x);
-        tma_load_2d(w_dst, &tm_w, n0 * 2, kb * 2, &full_p[stage], pol_w);
+#pragma unroll
+        for (int l = 0; l < BITS / 4; ++l)
+          tma_load_2d(w_dst + l * 2048, &tm_w, n0 * kWordsPerN + l * 256, kb * 2, &full_p[stage], pol_w);
         tma_load_2d(w_dst + kValBytes, &tm_m, n0 * 2, kb * 2, &full_p[stage], pol_w);
         if (grouped)
           tma_load_2d(w_dst + kValBytes + kMetaBytes, &tm_s, n0, (kb * kStageK) >> args.group_shift,
@@ -228,7 +237,8 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
       }
     }
     const uint32_t stage0 = smem_u32(stages) + P::kXBytes;
-    const uint32_t val_off = nt * 512 + lane * 16;
+    // 4-bit: one 128-column box, rows 1 KiB, chunk nt at +512; 8-bit: one 64-column box per chunk
+    const uint32_t val_off = BITS == 4 ? nt * 512 + lane * 16 : nt * 2048 + lane * 32;
     const uint32_t meta_off = kValBytes + nt * 256 + c * 16;
     const uint32_t scale_off = kValBytes + kMetaBytes + (nt * 64 + 8 * c) * 2;
     const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16);
@@ -249,9 +259,15 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
       uint32_t words[2][4], meta[2][8];
 #pragma unroll
       for (int kt = 0; kt < 2; ++kt) {
-        const uint4 w = lds128(base + val_off + kt * 1024);
-        words[kt][0] = w.x >> (8 * hb), words[kt][1] = w.y >> (8 * hb);
-        words[kt][2] = w.z >> (8 * hb), words[kt][3] = w.w >> (8 * hb);
+        if constexpr (BITS == 4) {
+          const uint4 w = lds128(base + val_off + kt * 1024);
+          words[kt][0] = w.x >> (8 * hb), words[kt][1] = w.y >> (8 * hb);
+          words[kt][2] = w.z >> (8 * hb), words[kt][3] = w.w >> (8 * hb);
+        } else {  // word 2 j + b of the lane's eight
+          const uint4 w0 = lds128(base + val_off + kt * 1024), w1 = lds128(base + val_off + kt * 1024 + 16);
+          words[kt][0] = hb ? w0.y : w0.x, words[kt][1] = hb ? w0.w : w0.z;
+          words[kt][2] = hb ? w1.y : w1.x, words[kt][3] = hb ? w1.w : w1.z;
+        }
         const uint4 ma = lds128(base + meta_off + kt * 512);        // j = 0, 1
         const uint4 mb = lds128(base + meta_off + kt * 512 + 128);  // j = 2, 3
         meta[kt][0] = ma.x, meta[kt][1] = ma.y, meta[kt][2] = ma.z, meta[kt][3] = ma.w;
@@ -281,8 +297,15 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
             constexpr uint32_t LO = 0x000f000f, HI = 0x00f000f0, EX = 0x64006400;
             constexpr uint32_t SUB = 0x64086408, MUL = 0x2c002c00, ADD = 0xd480d480;
             const uint32_t q = words[kt][j];
-            const uint32_t v_lo = mul2<__half>(h2_sub(lop3<kAndOr>(q, LO, EX), SUB), sc[j]);
-            const uint32_t v_hi = mul2<__half>(h2_fma(lop3<kAndOr>(q, HI, EX), MUL, ADD), sc[j]);
+            uint32_t v_lo, v_hi;  // kept pairs of groups r and r + 4, exact q - zp, x scale (one rounding)
+            if constexpr (BITS == 4) {
+              v_lo = mul2<__half>(h2_sub(lop3<kAndOr>(q, LO, EX), SUB), sc[j]);
+              v_hi = mul2<__half>(h2_fma(lop3<kAndOr>(q, HI, EX), MUL, ADD), sc[j]);
+            } else {
+              unpack8<__half>(q, v_lo, v_hi);
+              v_lo = mul2<__half>(v_lo, sc[j]);
+              v_hi = mul2<__half>(v_hi, sc[j]);
+            }
             const uint2 e_lo = lds64(lut_u32 + (((meta[kt][2 * j] >> msh) & 0xf) << 3));
             const uint2 e_hi = lds64(lut_u32 + (((meta[kt][2 * j + 1] >> msh) & 0xf) << 3));
             lo[u][0] = __byte_perm(v_lo, 0, e_lo.x), lo[u][1] = __byte_perm(v_lo, 0, e_lo.y);
@@ -355,14 +378,15 @@ __global__ void __launch_bounds__(256) splitk_sum24_kernel(__half* __restrict__ 
   }
 }
 
-template <int BM>
+template <int BM, int BITS>
 int launch24(const b200_gptq_marlin_24_gemm_params& p, cudaStream_t st) {
-  using P = Plan24<BM>;
+  using P = Plan24<BM, BITS>;
   CUtensorMap tm_x, tm_w, tm_m, tm_s;
   int rc = make_tmap_2d(&tm_x, p.a, (uint64_t)p.size_m, (uint64_t)p.size_k, (uint64_t)p.size_k * 2, 2, BM);
   if (rc != B200_OK) return rc;
   const uint64_t rows = (uint64_t)p.size_k / 32, cols = (uint64_t)p.size_n * 2;
-  rc = make_tmap_2d_ex(&tm_w, p.b_q_weight, rows, cols, cols * 4, CU_TENSOR_MAP_DATA_TYPE_INT32, 256, 2,
+  const uint64_t wcols = (uint64_t)p.size_n * (BITS / 2);
+  rc = make_tmap_2d_ex(&tm_w, p.b_q_weight, rows, wcols, wcols * 4, CU_TENSOR_MAP_DATA_TYPE_INT32, 256, 2,
                        CU_TENSOR_MAP_SWIZZLE_NONE);
   if (rc != B200_OK) return rc;
   rc = make_tmap_2d_ex(&tm_m, p.b_meta, rows, cols, cols * 2, CU_TENSOR_MAP_DATA_TYPE_UINT16, 256, 2,
@@ -390,7 +414,7 @@ int launch24(const b200_gptq_marlin_24_gemm_params& p, cudaStream_t st) {
   a.kb_per_split = (a.num_kb + splits - 1) / splits;
   splits = (a.num_kb + a.kb_per_split - 1) / a.kb_per_split;
   a.partial = splits > 1 ? reinterpret_cast<float*>(p.splitk_ws) : nullptr;
-  auto kern = marlin24_gemm_kernel<BM>;
+  auto kern = marlin24_gemm_kernel<BM, BITS>;
   static size_t smem_configured[kMaxDevices] = {};
   if (ensure_dyn_smem(kern, P::kBytes, smem_configured) != cudaSuccess) {
     cudaGetLastError();
@@ -419,21 +443,25 @@ extern "C" int b200_gptq_marlin_24_gemm(const b200_gptq_marlin_24_gemm_params* p
   const b200_gptq_marlin_24_gemm_params& p = *pp;
   // marlin_24_cuda_kernel.cu:1024-1116
   B200_REQUIRE(p.num_bits == 4 || p.num_bits == 8, B200_EINVAL, "num_bits must be 4 or 8. Got = %d", p.num_bits);
-  B200_REQUIRE(p.num_bits == 4, B200_ENOTSUP,
-               "gptq_marlin_24_gemm: 8-bit 2:4 weights are not implemented yet (4-bit only)");
   B200_REQUIRE(p.size_m >= 0 && p.size_n > 0 && p.size_k > 0, B200_EINVAL, "gptq_marlin_24_gemm: bad sizes");
   if (p.size_m == 0) return B200_OK;
   B200_REQUIRE(p.size_k % 128 == 0, B200_EINVAL, "size_k = %d is not divisible by 128", p.size_k);
   B200_REQUIRE(p.size_n % 128 == 0, B200_EINVAL, "size_n = %d is not divisible by 128", p.size_n);
   B200_REQUIRE(p.c && p.a && p.b_q_weight && p.b_meta && p.b_scales, B200_EINVAL,
                "gptq_marlin_24_gemm: null pointer");
+  B200_REQUIRE(p.num_groups >= 1, B200_EINVAL, "gptq_marlin_24_gemm: b_scales has no rows");
   B200_REQUIRE(p.num_groups == 1 || p.size_k / p.num_groups == 128, B200_EINVAL, "Unexpected groupsize = %d",
-               p.num_groups > 0 ? p.size_k / p.num_groups : -1);
+               p.size_k / p.num_groups);
   B200_REQUIRE(((uintptr_t)p.a & 15) == 0 && ((uintptr_t)p.b_q_weight & 15) == 0 &&
                    ((uintptr_t)p.b_meta & 15) == 0 && ((uintptr_t)p.b_scales & 15) == 0,
                B200_EINVAL, "gptq_marlin_24_gemm: operands must be 16-byte aligned");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (p.size_m <= 16) return launch24<16>(p, st);
-  if (p.size_m <= 32) return launch24<32>(p, st);
-  return launch24<64>(p, st);
+  if (p.num_bits == 4) {
+    if (p.size_m <= 16) return launch24<16, 4>(p, st);
+    if (p.size_m <= 32) return launch24<32, 4>(p, st);
+    return launch24<64, 4>(p, st);
+  }
+  if (p.size_m <= 16) return launch24<16, 8>(p, st);
+  if (p.size_m <= 32) return launch24<32, 8>(p, st);
+  return launch24<64, 8>(p, st);
 }

@@ -468,7 +468,7 @@ def test_marlin_gemm_rejects_bad_arguments(ops):
 
 
 # ------------------------------------------------------------------------------------------
-# gptq_marlin_24_gemm (test_marlin_gemm.py:182-229): 2:4 sparse + 4-bit
+# gptq_marlin_24_gemm (test_marlin_gemm.py:182-229): 2:4 sparse + 4-bit / 8-bit
 # ------------------------------------------------------------------------------------------
 def _marlin24_check(ops, a, mq, meta, ms, w_ref, bits, m, n, k):
     out = ops.gptq_marlin_24_gemm(a, mq.to(DEV), meta.to(DEV), ms.to(DEV), _ws(n, par=64, thread_n=128),
@@ -481,36 +481,42 @@ def _marlin24_check(ops, a, mq, meta, ms, w_ref, bits, m, n, k):
     assert bool((err <= tol).all()), f"max err {err.max()} vs scale {ref.abs().max()}"
 
 
+@pytest.mark.parametrize("bits", [4, 8])  # marlin_24_cuda_kernel.cu:1024 accepts both
 @pytest.mark.parametrize("group", [-1, 128])
 @pytest.mark.parametrize("mnk", MNK)
-def test_marlin_24_gemm(ops, group, mnk):
+def test_marlin_24_gemm(ops, bits, group, mnk):
     mf, nf, kf = mnk
+    if bits == 8 and mf > 26:
+        pytest.skip("8-bit: the small and medium factors cover the format; CPU quantisation budget")
     m, n, k = mf, 512 * nf, 128 * kf
     torch.manual_seed(0)
     a = torch.randn(m, k, dtype=torch.half, device=DEV)
     w = torch.randn(k, n, dtype=torch.half)
-    w_ref, mq, meta, ms = qr.marlin_24_quantize(w, 4, group)
-    _marlin24_check(ops, a, mq, meta, ms, w_ref, 4, m, n, k)
+    w_ref, mq, meta, ms = qr.marlin_24_quantize(w, bits, group)
+    _marlin24_check(ops, a, mq, meta, ms, w_ref, bits, m, n, k)
 
 
+@pytest.mark.parametrize("bits", [4, 8])
 @pytest.mark.parametrize("m", [1, 2, 16, 17, 32, 33, 64, 100, 128, 200])
-def test_marlin_24_gemm_m_sweep(ops, m):
+def test_marlin_24_gemm_m_sweep(ops, bits, m):
     torch.manual_seed(1)
     k, n = 1024, 384
     a = torch.randn(m, k, dtype=torch.half, device=DEV)
-    w_ref, mq, meta, ms = qr.marlin_24_quantize(torch.randn(k, n, dtype=torch.half), 4, 128)
-    _marlin24_check(ops, a, mq, meta, ms, w_ref, 4, m, n, k)
+    w_ref, mq, meta, ms = qr.marlin_24_quantize(torch.randn(k, n, dtype=torch.half), bits, 128)
+    _marlin24_check(ops, a, mq, meta, ms, w_ref, bits, m, n, k)
 
 
-@pytest.mark.parametrize("tag,k,n", [("s24_k128_n128_b4_g-1", 128, 128), ("s24_k256_n128_b4_g128", 256, 128)])
+@pytest.mark.parametrize("tag,k,n", [("s24_k128_n128_b4_g-1", 128, 128), ("s24_k256_n128_b4_g128", 256, 128),
+                                     ("s24_k128_n256_b8_g-1", 128, 256), ("s24_k256_n128_b8_g128", 256, 128)])
 def test_marlin_24_golden_dequant_exact(ops, tag, k, n):
     """a = identity: the GEMM returns the dequantised 2:4 weight itself, which must equal the
     reference's w_24_ref bit for bit (fixtures generated from the reference's own Python)."""
     g = np.load(os.path.join(os.path.dirname(__file__), "golden", "marlin_24.npz"))
     mq = torch.from_numpy(g[tag + "_marlin_q"]); meta = torch.from_numpy(g[tag + "_meta"])
     ms = torch.from_numpy(g[tag + "_marlin_s"]); w_ref = torch.from_numpy(g[tag + "_w_ref"])
+    bits = 8 if "_b8_" in tag else 4
     a = torch.eye(k, dtype=torch.half, device=DEV)
-    out = ops.gptq_marlin_24_gemm(a, mq.to(DEV), meta.to(DEV), ms.to(DEV), _ws(n, par=64, thread_n=128), 4, k, n, k)
+    out = ops.gptq_marlin_24_gemm(a, mq.to(DEV), meta.to(DEV), ms.to(DEV), _ws(n, par=64, thread_n=128), bits, k, n, k)
     assert torch.equal(out.cpu(), w_ref)
 
 
