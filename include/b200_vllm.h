@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define B200_VLLM_ABI_VERSION 1
+#define B200_VLLM_ABI_VERSION 2
 
 /* every entry point is exported with default visibility (the library is built -fvisibility=hidden) */
 #if defined(__GNUC__)
@@ -221,13 +221,11 @@ typedef struct {
   /* optional split-K scratch (fp32 partials) for the weight-streaming regime; NULL => no split-K */
   void* splitk_ws;
   int64_t splitk_ws_bytes;
+  int32_t weight_format; /* 0 = integers with zero point 2^(bits-1) (GPTQ); 1 = fp8 e4m3 (num_bits 8) */
 } b200_gptq_marlin_gemm_params;
 
 B200_API int b200_gptq_marlin_gemm(const b200_gptq_marlin_gemm_params* p, void* stream);
 B200_API int64_t b200_gptq_marlin_gemm_workspace_bytes(int32_t m, int32_t n, int32_t k);
-/* test hook: out [size_k, size_n] (dtype) = dequantised weights, produced by the same unpack /
- * scale device code the GEMM uses (bit-exact against the reference's w_ref,
- * quant_utils.py:73). No act-order. */
 /* test hook: which W4A16/W8A16 decode kernel gptq_marlin_gemm takes at M <= 64 (0 heuristic,
  * 1 first-generation split-K kernel, 2 stream-K kernel wherever eligible, -1 environment) */
 B200_API void b200_debug_set_marlin_decode_kernel(int32_t choice);
@@ -236,6 +234,14 @@ B200_API void b200_debug_set_marlin_decode_kernel(int32_t choice);
  * (0 unless built with -DB200_STREAM_PROF) */
 B200_API int b200_debug_stream_prof(unsigned long long* dst, int32_t n);
 
+/* fp8_marlin_gemm (csrc/quantization/fp8/fp8_marlin.cu:1212-1308): fp8 e4m3 weights repacked with
+ * gptq_marlin_repack(num_bits = 8), b_scales [1, size_n] in marlin_permute_scales order.  Takes the
+ * same parameter block (num_bits = 8, num_groups = 1, no act-order). */
+B200_API int b200_fp8_marlin_gemm(const b200_gptq_marlin_gemm_params* p, void* stream);
+
+/* test hook: out [size_k, size_n] (dtype) = dequantised weights, produced by the same unpack /
+ * scale device code the GEMM uses (bit-exact against the reference's w_ref,
+ * quant_utils.py:73). No act-order. */
 B200_API int b200_marlin_dequant(void* out, const uint32_t* b_q_weight, const void* b_scales,
                                  int32_t size_k, int32_t size_n, int32_t num_groups,
                                  int32_t num_bits, int32_t dtype, void* stream);

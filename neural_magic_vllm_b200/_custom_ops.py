@@ -140,6 +140,11 @@ def gptq_marlin_gemm(a, b_q_weight, b_scales, g_idx, perm, workspace, num_bits: 
                                size_n, size_k, is_k_full)
 
 
+def fp8_marlin_gemm(a, b_q_weight, b_scales, workspace, num_bits: int, size_m: int, size_n: int,
+                    size_k: int) -> torch.Tensor:  # :275-280
+    return _C.fp8_marlin_gemm(a, b_q_weight, b_scales, workspace, num_bits, size_m, size_n, size_k)
+
+
 def scaled_fp8_quant(input: torch.Tensor, scale: Optional[torch.Tensor] = None,
                      batch_dim_padding: Optional[int] = None
                      ) -> Tuple[torch.Tensor, torch.Tensor]:  # :284-320

@@ -97,6 +97,24 @@ __device__ __forceinline__ void unpack8(uint32_t q, uint32_t& lo, uint32_t& hi) 
   }
 }
 
+// fp8 e4m3 weights in the same 8-bit word (fp8_marlin_gemm, csrc/quantization/fp8/fp8_marlin.cu:
+// 120-192): sign and exponent/mantissa bits are moved to their fp16 / bf16 positions; the result is
+// the fp8 value times 2^-8 (fp16) or 2^-120 (bf16), exactly.  The missing power of two is folded
+// into the channel scale (fp8_scale_bias), so that ONE multiply rounds value x scale once.
+template <typename T>
+__device__ __forceinline__ void unpack8_fp8(uint32_t q, uint32_t& lo, uint32_t& hi) {
+  constexpr int SH = DT<T>::id == B200_F16 ? 1 : 4;                         // exponent 5 | 8 bits vs 4
+  constexpr uint32_t EM = DT<T>::id == B200_F16 ? 0x3F803F80u : 0x07F007F0u;  // (0x7F007F00 >> SH)
+  const uint32_t ql = q << 8;  // bytes 0, 2 -> the high byte of each half
+  hi = lop3<kAndOr>(q >> SH, EM, q & 0x80008000u);
+  lo = lop3<kAndOr>(ql >> SH, EM, ql & 0x80008000u);
+}
+template <typename T>
+__device__ __forceinline__ uint32_t fp8_scale_bias(uint32_t s2) {  // s2 x 2^8 | 2^120 (exact)
+  if constexpr (DT<T>::id == B200_F16) return mul2<T>(s2, 0x5C005C00u);  // 256.0
+  else return mul2<T>(s2, 0x7B807B80u);                                   // 2^120 in bf16
+}
+
 // position of column n inside a grouped-scale row (marlin_perms.py:41-43: 64-column chunks,
 // position 8*a + c holds column a + 8*c)
 __host__ __device__ __forceinline__ int scale_pos_grouped(int n) {

@@ -44,6 +44,7 @@ struct MarlinArgs {
   int s_rows;                  // scale rows fetched per stage (0: scales are not staged)
   int kb_per_split, num_kb;
   int w_evict_first;
+  int fp8;  // 8-bit words hold fp8 e4m3 values (fp8_marlin_gemm), channel-wise scales
   int32_t* locks;  // decode kernel, split-K: arrival counter per n tile (zero on entry, zero on exit)
 };
 
@@ -215,6 +216,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
           const int n = n0 + h * 128 + nt0 * 64 + 16 * (i >> 1) + a_row + 8 * (i & 1);
           const uint32_t v = s[scale_pos_single(n)];
           sc[h][i] = v | (v << 16);
+          if (BITS == 8 && args.fp8) sc[h][i] = fp8_scale_bias<T>(sc[h][i]);
         }
       }
     }
@@ -264,8 +266,13 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
           if constexpr (BITS == 4) {
             unpack4<T>(words[h][j], rg);
           } else {
-            unpack8<T>(words[h][2 * j], rg[0], rg[1]);
-            unpack8<T>(words[h][2 * j + 1], rg[2], rg[3]);
+            if (args.fp8) {
+              unpack8_fp8<T>(words[h][2 * j], rg[0], rg[1]);
+              unpack8_fp8<T>(words[h][2 * j + 1], rg[2], rg[3]);
+            } else {
+              unpack8<T>(words[h][2 * j], rg[0], rg[1]);
+              unpack8<T>(words[h][2 * j + 1], rg[2], rg[3]);
+            }
           }
           if constexpr (ACT_ORDER) {
             // every k row may belong to a different group: scale each element separately
@@ -514,6 +521,7 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
         const int n = n0 + nt * 64 + 16 * (j0 + (i >> 1)) + a_row + 8 * (i & 1);
         const uint32_t v = s[scale_pos_single(n)];
         sc[i] = v | (v << 16);
+        if (BITS == 8 && args.fp8) sc[i] = fp8_scale_bias<T>(sc[i]);
       }
     }
     // one group per 64-k stage (group_size >= 64; smaller groups take the shared-memory kernel)
@@ -570,8 +578,13 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
           if constexpr (BITS == 4) {
             unpack4<T>(words[kt][jj], rg);
           } else {
-            unpack8<T>(words[kt][2 * jj], rg[0], rg[1]);
-            unpack8<T>(words[kt][2 * jj + 1], rg[2], rg[3]);
+            if (args.fp8) {
+              unpack8_fp8<T>(words[kt][2 * jj], rg[0], rg[1]);
+              unpack8_fp8<T>(words[kt][2 * jj + 1], rg[2], rg[3]);
+            } else {
+              unpack8<T>(words[kt][2 * jj], rg[0], rg[1]);
+              unpack8<T>(words[kt][2 * jj + 1], rg[2], rg[3]);
+            }
           }
           rg[0] = mul2<T>(rg[0], sc[2 * jj]);
           rg[1] = mul2<T>(rg[1], sc[2 * jj]);
@@ -766,6 +779,7 @@ int launch(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64_t ld
   a.group_size = p.num_groups > 1 ? p.size_k / p.num_groups : p.size_k;
   a.group_shift = (a.group_size & (a.group_size - 1)) == 0 ? __builtin_ctz(a.group_size) : -1;
   a.num_kb = p.size_k / kStageK;
+  a.fp8 = p.weight_format == 1;
   CUtensorMap tm_w, tm_s;
   rc = make_weight_maps(p, p.num_groups > 1 && !ACT, P::kCtaN, &tm_w, &tm_s, &a);
   if (rc != B200_OK) return rc;
@@ -832,6 +846,7 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   a.group_size = p.num_groups > 1 ? p.size_k / p.num_groups : p.size_k;
   a.group_shift = (a.group_size & (a.group_size - 1)) == 0 ? __builtin_ctz(a.group_size) : -1;
   a.num_kb = p.size_k / kStageK;
+  a.fp8 = p.weight_format == 1;
   CUtensorMap tm_w, tm_s;
   rc = make_weight_maps(p, p.num_groups > 1, kTileN, &tm_w, &tm_s, &a);
   if (rc != B200_OK) return rc;
@@ -986,6 +1001,9 @@ int b200_gptq_marlin_gemm(const b200_gptq_marlin_gemm_params* pp, void* stream) 
   const b200_gptq_marlin_gemm_params& p = *pp;
   B200_REQUIRE(p.num_bits == 4 || p.num_bits == 8, B200_EINVAL, "num_bits must be 4 or 8. Got = %d",
                p.num_bits);
+  B200_REQUIRE(p.weight_format == 0 || (p.weight_format == 1 && p.num_bits == 8 && p.num_groups == 1 &&
+                                        p.g_idx == nullptr),
+               B200_EINVAL, "gptq_marlin_gemm: fp8 weights need num_bits 8, channel-wise scales, no act-order");
   B200_REQUIRE(p.size_m >= 0 && p.size_n > 0 && p.size_k > 0, B200_EINVAL, "gptq_marlin_gemm: bad sizes");
   if (p.size_m == 0) return B200_OK;
   B200_REQUIRE(p.size_n % 64 == 0, B200_EINVAL, "size_n = %d, is not divisible by min_thread_n = 64", p.size_n);
@@ -1025,6 +1043,20 @@ int b200_debug_stream_prof(unsigned long long* dst, int32_t n) {
   (void)n;
   return 0;
 #endif
+}
+
+// fp8_marlin_gemm (csrc/quantization/fp8/fp8_marlin.cu:1212-1308): fp8 e4m3 weights in the Marlin
+// 8-bit layout, channel-wise scales; same kernels, other unpack
+int b200_fp8_marlin_gemm(const b200_gptq_marlin_gemm_params* pp, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(pp != nullptr, B200_EINVAL, "fp8_marlin_gemm: null params");
+  B200_REQUIRE(pp->num_bits == 8, B200_EINVAL, "num_bits must be 8. Got = %d", pp->num_bits);
+  B200_REQUIRE(pp->num_groups == 1, B200_EINVAL, "fp8_marlin_gemm: b_scales must have one row");
+  b200_gptq_marlin_gemm_params p = *pp;
+  p.weight_format = 1;
+  p.g_idx = nullptr;
+  p.perm = nullptr;
+  return b200_gptq_marlin_gemm(&p, stream);
 }
 
 int b200_marlin_dequant(void* out, const uint32_t* b_q_weight, const void* b_scales, int32_t size_k,

@@ -316,6 +316,7 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
           const int n = tile * kSCtaN + h * kTileN + nt * 64 + 16 * (j0 + (e >> 1)) + a_row + 8 * (e & 1);
           const uint32_t v = n < args.n ? s[scale_pos_single(n)] : 0u;
           sc[e] = v | (v << 16);
+          if (BITS == 8 && args.fp8) sc[e] = fp8_scale_bias<T>(sc[e]);
         }
       }
       mbar_wait_bounded(&empty_a[aslot], ((job >> 3) & 1) ^ 1);
@@ -333,8 +334,13 @@ marlin_gemm_stream_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid
           if constexpr (BITS == 4) {
             unpack4<T>(cur[kt][jj], rg);
           } else {
-            unpack8<T>(cur[kt][2 * jj], rg[0], rg[1]);
-            unpack8<T>(cur[kt][2 * jj + 1], rg[2], rg[3]);
+            if (args.fp8) {
+              unpack8_fp8<T>(cur[kt][2 * jj], rg[0], rg[1]);
+              unpack8_fp8<T>(cur[kt][2 * jj + 1], rg[2], rg[3]);
+            } else {
+              unpack8<T>(cur[kt][2 * jj], rg[0], rg[1]);
+              unpack8<T>(cur[kt][2 * jj + 1], rg[2], rg[3]);
+            }
           }
           st[4 * kt + 0] = mul2<T>(rg[0], sc[2 * jj]);
           st[4 * kt + 2] = mul2<T>(rg[1], sc[2 * jj]);
@@ -535,6 +541,7 @@ int launch_stream(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   a.group_size = p.num_groups > 1 ? p.size_k / p.num_groups : p.size_k;
   a.group_shift = (a.group_size & (a.group_size - 1)) == 0 ? __builtin_ctz(a.group_size) : -1;
   a.num_kb = p.size_k / kStageK;
+  a.fp8 = p.weight_format == 1;
   CUtensorMap tm_w, tm_s;
   rc = make_weight_maps(p, p.num_groups > 1, kSCtaN, &tm_w, &tm_s, &a);
   if (rc != B200_OK) return rc;

@@ -153,6 +153,26 @@ def marlin_quantize(w, num_bits, group_size, act_order, generator=None):  # marl
     return w_ref, marlin_q_w, marlin_s, g_idx, sort_indices, rand_perm
 
 
+def fp8_marlin_quantize(w: torch.Tensor):
+    """fp8 weight-only Marlin operands as tests/kernels/test_marlin_gemm.py:256-283 of the reference
+    builds them: per-tensor dynamic fp8 quantisation (fp8/common.cu:129-165: scale = absmax / 448),
+    the fp8 bytes packed four k rows per int32 (marlin_utils.py:227-247 pack_fp8_to_int32) and
+    repacked to the 8-bit Marlin layout (gptq_marlin_repack == marlin_weights on the same bytes,
+    pinned by the repack golden test), the scale expanded to channel-wise and permuted
+    (marlin_permute_scales, group_size -1).  -> (w_ref [K, N] = fl(fp8 value x scale) in w.dtype,
+    marlin_q [K/16, 4N] int32, marlin_s [1, N])."""
+    size_k, size_n = w.shape
+    scale = (w.float().abs().max() / 448.0).clamp(min=1e-12)
+    w8 = (w.float() / scale).clamp(-448.0, 448.0).to(torch.float8_e4m3fn)
+    q = w8.view(torch.uint8).to(torch.int32)
+    perm, sp, sps = get_perms(8)
+    marlin_q = marlin_weights(q, size_k, size_n, 8, perm)
+    s = scale.to(w.dtype).reshape(1, 1).repeat(1, size_n)
+    marlin_s = marlin_permute_scales(s, size_k, size_n, -1, sp, sps)
+    w_ref = (w8.float() * s.float()).to(w.dtype)  # exact product, one rounding
+    return w_ref, marlin_q, marlin_s
+
+
 def marlin_unpack(marlin_q_w: torch.Tensor, size_k: int, size_n: int, num_bits: int) -> torch.Tensor:
     """inverse of marlin_weights: Marlin tiles [K/16, N*16/pack] int32 -> [K, N] ints."""
     perm, _, _ = get_perms(num_bits)

@@ -179,7 +179,7 @@ def test_c_abi_exports_every_declared_symbol():
     missing = [n for n in names if not hasattr(lib, n)]
     assert not missing, f"declared but not exported: {missing}"
     lib.b200_abi_version.restype = ctypes.c_int
-    assert lib.b200_abi_version() >= 1
+    assert lib.b200_abi_version() >= 2
     lib.b200_parse_kv_cache_dtype.argtypes = [ctypes.c_char_p]
     assert lib.b200_parse_kv_cache_dtype(b"fp8") == 1
     assert lib.b200_parse_kv_cache_dtype(b"auto") == 0
@@ -190,7 +190,7 @@ def test_c_abi_exports_every_declared_symbol():
 def test_torch_ops_registered_with_reference_schemas():
     import neural_magic_vllm_b200  # noqa: F401  loads _C.so (fails loudly when missing)
     want = ["_C::paged_attention_v1", "_C::paged_attention_v2", "_C::gptq_marlin_gemm",
-            "_C::gptq_marlin_repack", "_C::gptq_marlin_24_gemm", "_C::cutlass_scaled_mm",
+            "_C::gptq_marlin_repack", "_C::gptq_marlin_24_gemm", "_C::fp8_marlin_gemm", "_C::cutlass_scaled_mm",
             "_C::cutlass_scaled_mm_supports_fp8", "_C::static_scaled_fp8_quant",
             "_C::dynamic_scaled_fp8_quant", "_C::static_scaled_int8_quant",
             "_C::dynamic_scaled_int8_quant", "_C_cache_ops::reshape_and_cache",

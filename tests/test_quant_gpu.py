@@ -468,6 +468,55 @@ def test_marlin_gemm_rejects_bad_arguments(ops):
 
 
 # ------------------------------------------------------------------------------------------
+# fp8_marlin_gemm (test_marlin_gemm.py:232-304): fp8 e4m3 weights, channel-wise scales
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", [torch.half, torch.bfloat16])
+@pytest.mark.parametrize("k_chunk,n_chunk,mnk", [(128, 64, (1, 1, 1)), (128, 128, (1, 4, 8)), (128, 256, (1, 7, 5)),
+                                                 (128, 64, (13, 17, 67)), (128, 256, (26, 37, 13)),
+                                                 (128, 128, (67, 13, 11)), (128, 256, (300, 4, 16))])
+def test_fp8_marlin_gemm(ops, dtype, k_chunk, n_chunk, mnk):
+    mf, nf, kf = mnk
+    m, n, k = mf, n_chunk * nf, k_chunk * kf
+    torch.manual_seed(0)
+    a = torch.randn(m, k, dtype=dtype, device=DEV)
+    w = torch.randn(k, n, dtype=dtype)
+    w_ref, mq, ms = qr.fp8_marlin_quantize(w)
+    out = ops.fp8_marlin_gemm(a, mq.to(DEV), ms.to(DEV), _ws(n), 8, m, n, k)
+    # the reference's bar: against the UNQUANTISED product (test_marlin_gemm.py:297-304)
+    assert qr.compute_max_diff(out.float(), torch.matmul(a.float(), w.to(DEV).float())) < 0.04
+    # this repo's bar: against the same dequantised weights, fp32 accumulation
+    ref = torch.matmul(a.float(), w_ref.to(DEV).float())
+    err = (out.float() - ref).abs()
+    tol = 1e-2 * ref.abs() + 2e-3 * ref.abs().max() + 1e-3
+    if dtype == torch.bfloat16:
+        tol = tol * 8
+    assert bool((err <= tol).all()), f"max err {err.max()} vs scale {ref.abs().max()}"
+
+
+@pytest.mark.parametrize("dtype", [torch.half, torch.bfloat16])
+@pytest.mark.parametrize("k", [64, 256])  # the decode kernel (TMEM operand) / the shared-memory kernel (M > 64)
+def test_fp8_marlin_identity_a_is_the_dequantised_tile(ops, dtype, k):
+    torch.manual_seed(2)
+    n = 256
+    w = torch.randn(k, n, dtype=dtype) * 3
+    w[0, :8] = torch.tensor([0.0, 1e-4, -1e-4, 2e-3, -2e-3, 5.0, -5.0, 0.01], dtype=dtype)  # fp8 subnormals too
+    w_ref, mq, ms = qr.fp8_marlin_quantize(w)
+    a = torch.eye(k, dtype=dtype, device=DEV)
+    out = ops.fp8_marlin_gemm(a, mq.to(DEV), ms.to(DEV), _ws(n), 8, k, n, k)
+    assert torch.equal(out.cpu(), w_ref)
+
+
+def test_fp8_marlin_errors(ops):
+    a = torch.zeros(4, 128, dtype=torch.half, device=DEV)
+    q = torch.zeros(8, 64 * 4, dtype=torch.int32, device=DEV)
+    s = torch.ones(1, 64, dtype=torch.half, device=DEV)
+    with pytest.raises(RuntimeError):
+        ops.fp8_marlin_gemm(a, q, s, _ws(64), 4, 4, 64, 128)                     # num_bits must be 8
+    with pytest.raises(RuntimeError):
+        ops.fp8_marlin_gemm(a, q, torch.ones(2, 64, dtype=torch.half, device=DEV), _ws(64), 8, 4, 64, 128)
+
+
+# ------------------------------------------------------------------------------------------
 # gptq_marlin_24_gemm (test_marlin_gemm.py:182-229): 2:4 sparse + 4-bit / 8-bit
 # ------------------------------------------------------------------------------------------
 def _marlin24_check(ops, a, mq, meta, ms, w_ref, bits, m, n, k):
