@@ -275,6 +275,15 @@ B200_API int b200_gptq_marlin_24_gemm(const b200_gptq_marlin_24_gemm_params* p, 
 B200_API int b200_rms_norm(void* out, const void* input, const void* weight, float epsilon,
                            int32_t num_tokens, int32_t hidden, int32_t dtype, void* stream);
 
+/* (fused_add_)rms_norm + activation quantisation in one pass (extension):
+ * residual != NULL: residual += input first (rounded, stored back), as fused_add_rms_norm.
+ * quant_mode 0: int8 per-token dynamic, scales [num_tokens] written; 1: int8 static, *scales read;
+ * 2: fp8 e4m3 static, *scales read.  out [num_tokens, hidden] bytes.  Results are bit-identical to
+ * (fused_add_)rms_norm followed by scaled_int8_quant / scaled_fp8_quant. */
+B200_API int b200_rms_norm_quant(void* out, float* scales, const void* input, void* residual, const void* weight,
+                        float epsilon, int32_t num_tokens, int32_t hidden, int32_t dtype, int32_t quant_mode,
+                        void* stream);
+
 /* fused_add_rms_norm (csrc/layernorm_kernels.cu:199-287, 326-352), in place:
  * residual = input + residual; input = rms_norm(residual) * weight. */
 B200_API int b200_fused_add_rms_norm(void* input, void* residual, const void* weight, float epsilon,

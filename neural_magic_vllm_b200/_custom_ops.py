@@ -78,6 +78,21 @@ def rms_norm(out: torch.Tensor, input: torch.Tensor, weight: torch.Tensor,
     _C.rms_norm(out, input, weight, epsilon)
 
 
+def rms_norm_quant(input: torch.Tensor, weight: torch.Tensor, epsilon: float,
+                   residual: Optional[torch.Tensor] = None, scale: Optional[torch.Tensor] = None,
+                   out_dtype: torch.dtype = torch.int8) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Extension: (fused_add_)rms_norm followed by scaled_int8_quant /
+    scaled_fp8_quant in ONE launch, bit-identical to the two reference ops.  `residual` is updated
+    in place when given.  int8: scale=None -> per-token dynamic scales [tokens, 1]; a scalar tensor
+    -> static.  fp8: static only (scale required)."""
+    out = torch.empty(input.shape, dtype=out_dtype, device=input.device)
+    dynamic = scale is None
+    if dynamic:
+        scale = torch.empty((input.numel() // input.shape[-1], 1), dtype=torch.float32, device=input.device)
+    _C.rms_norm_quant(out, scale, input, residual, weight, epsilon, dynamic)
+    return out, scale
+
+
 def fused_add_rms_norm(input: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor,
                        epsilon: float) -> None:
     _C.fused_add_rms_norm(input, residual, weight, epsilon)

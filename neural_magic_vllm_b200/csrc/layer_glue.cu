@@ -154,6 +154,131 @@ int launch_rms(void* out, const void* in, void* residual, const void* weight, fl
 }
 
 // ---------------------------------------------------------------------------------------------
+// (fused_add_)rms_norm + activation quantisation in one pass: the W8A8
+// linears take int8 / fp8 activations, so the normalised row never goes to HBM in 16 bits.
+// Arithmetic = the two reference ops back to back: y = T(T(z * rstd) * w) exactly as
+// rms_norm_kernel stores it (layernorm_kernels.cu:21-45, 199-249), then
+//   QMODE 0  int8, per-token dynamic: scale = absmax(y) / 127, q = cvt.rni.sat(y * (127 / absmax))
+//   QMODE 1  int8, static:            q = cvt.rni.sat(y / *scale)   (int8_quant_kernels.cu:27-66)
+//   QMODE 2  fp8 e4m3, static:        q = e4m3(clamp(y * (1 / *scale), +-448))  (fp8/common.cu:18-76)
+// One CTA per token, the row parked in shared memory between the passes.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int8_t f2i8_rni_sat(float x) {
+  int32_t d;
+  asm("cvt.rni.sat.s8.f32 %0, %1;" : "=r"(d) : "f"(x));
+  return static_cast<int8_t>(d);
+}
+__device__ __forceinline__ float block_max_f(float v, float* red) {
+  v = warp_max(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = (blockDim.x + 31) >> 5;
+  __syncthreads();  // `red` may still be read by the previous reduction
+  if (l == 0) red[w] = v;
+  __syncthreads();
+  float r = (l < nw) ? red[l] : 0.f;
+  return warp_max(r);
+}
+
+template <typename T, bool FUSED, int QMODE>
+__global__ void __launch_bounds__(1024) rms_norm_quant_kernel(uint8_t* __restrict__ out, float* __restrict__ scales,
+                                                              const T* __restrict__ in, T* __restrict__ residual,
+                                                              const T* __restrict__ weight, const float eps,
+                                                              const int hidden) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ float red[32];
+  pdl_wait();
+  pdl_launch_dependents();
+  constexpr int N = V16<T>::N;
+  T* row = reinterpret_cast<T*>(smem_raw);
+  const int64_t base = (int64_t)blockIdx.x * hidden;
+  float ss = 0.f;
+  for (int i = threadIdx.x * N; i < hidden; i += blockDim.x * N) {
+    V16<T> a;
+    a.load(in + base + i);
+    if constexpr (FUSED) {
+      V16<T> r;
+      r.load(residual + base + i);
+#pragma unroll
+      for (int j = 0; j < N; ++j) a.set(j, __fadd_rn(a.f(j), r.f(j)));
+      a.store(residual + base + i);
+    }
+#pragma unroll
+    for (int j = 0; j < N; ++j) ss = fmaf(a.f(j), a.f(j), ss);
+    a.store(row + i);
+  }
+  ss = block_sum(ss, red);
+  const float rstd = rsqrtf(ss / hidden + eps);
+  float amax = 0.f;
+  // each thread re-reads exactly the vectors it staged: no barrier needed on `row`
+  for (int i = threadIdx.x * N; i < hidden; i += blockDim.x * N) {
+    V16<T> a, w;
+    a.load(row + i);
+    w.load(weight + i);
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+      a.set(j, __fmul_rn(rnd<T>(__fmul_rn(a.f(j), rstd)), w.f(j)));
+      if constexpr (QMODE == 0) amax = fmaxf(amax, fabsf(a.f(j)));
+    }
+    a.store(row + i);
+  }
+  float mul = 1.f, div = 1.f;
+  if constexpr (QMODE == 0) {
+    amax = block_max_f(amax, red);
+    if (threadIdx.x == 0) scales[blockIdx.x] = amax / 127.0f;
+    mul = 127.0f / amax;
+  } else if constexpr (QMODE == 1) {
+    div = *scales;
+  } else {
+    mul = 1.0f / (*scales);
+  }
+  for (int i = threadIdx.x * N; i < hidden; i += blockDim.x * N) {
+    V16<T> a;
+    a.load(row + i);
+    uint8_t q[N];
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+      const float y = a.f(j);
+      if constexpr (QMODE == 0) q[j] = (uint8_t)f2i8_rni_sat(y * mul);
+      else if constexpr (QMODE == 1) q[j] = (uint8_t)f2i8_rni_sat(y / div);
+      else q[j] = (uint8_t)__nv_cvt_float_to_fp8(fmaxf(-448.0f, fminf(y * mul, 448.0f)), __NV_SATFINITE, __NV_E4M3);
+    }
+    if constexpr (N == 8) *reinterpret_cast<uint2*>(out + base + i) = *reinterpret_cast<uint2*>(q);
+    else *reinterpret_cast<uint32_t*>(out + base + i) = *reinterpret_cast<uint32_t*>(q);
+  }
+}
+
+template <typename T, bool FUSED>
+int launch_rms_quant(uint8_t* out, float* scales, const void* in, void* residual, const void* weight, float eps,
+                     int tokens, int hidden, int qmode, cudaStream_t st) {
+  constexpr int N = V16<T>::N;
+  const size_t row_bytes = (size_t)hidden * sizeof(T);
+  B200_REQUIRE(hidden % N == 0 && aligned16(in) && aligned16(weight) && (!FUSED || aligned16(residual)) &&
+                   (reinterpret_cast<uintptr_t>(out) & 7) == 0 && row_bytes <= 200 * 1024,
+               B200_EINVAL, "rms_norm_quant: rows must be 16-byte aligned multiples of 16 bytes, <= 200 KiB");
+  int threads = ((hidden / N + 31) / 32) * 32;
+  threads = threads > 1024 ? 1024 : threads;
+  auto go = [&](auto kern) -> int {
+    if (row_bytes > 48 * 1024) {
+      static size_t configured[kMaxDevices] = {};
+      if (ensure_dyn_smem(kern, row_bytes, configured) != cudaSuccess) {
+        cudaGetLastError();
+        set_error("rms_norm_quant: cannot reserve %d B of shared memory", (int)row_bytes);
+        return B200_ECUDA;
+      }
+    }
+    launch_pdl(kern, dim3(tokens), dim3(threads), row_bytes, st, out, scales, (const T*)in, (T*)residual,
+               (const T*)weight, eps, hidden);
+    return check_launch("rms_norm_quant");
+  };
+  switch (qmode) {
+    case 0: return go(rms_norm_quant_kernel<T, FUSED, 0>);
+    case 1: return go(rms_norm_quant_kernel<T, FUSED, 1>);
+    case 2: return go(rms_norm_quant_kernel<T, FUSED, 2>);
+  }
+  set_error("rms_norm_quant: quant mode %d (0 int8 dynamic, 1 int8 static, 2 fp8 static)", qmode);
+  return B200_EINVAL;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Rotary embedding, in place on query / key (pos_encoding_kernels.cu:10-96).
 //   x' = x*cos - y*sin ; y' = y*cos + x*sin, every operator rounded to T.
 // One CTA per token; a work item is 16 bytes of x (NeoX: + the matching 16 bytes of y).
@@ -588,6 +713,30 @@ int b200_fused_add_rms_norm(void* input, void* residual, const void* weight, flo
     case B200_F32: return launch_rms<float, true>(input, input, residual, weight, epsilon, num_tokens, hidden, st);
   }
   set_error("fused_add_rms_norm: unsupported dtype %d", dtype);
+  return B200_EINVAL;
+}
+
+int b200_rms_norm_quant(void* out, float* scales, const void* input, void* residual, const void* weight,
+                        float epsilon, int32_t num_tokens, int32_t hidden, int32_t dtype, int32_t quant_mode,
+                        void* stream) {
+  using namespace b200;
+  B200_REQUIRE(num_tokens >= 0 && hidden >= 0, B200_EINVAL, "rms_norm_quant: negative size");
+  if (num_tokens == 0 || hidden == 0) return B200_OK;
+  B200_REQUIRE(out && scales && input && weight, B200_EINVAL, "rms_norm_quant: null pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  uint8_t* o = static_cast<uint8_t*>(out);
+  if (residual != nullptr) {
+    if (dtype == B200_F16)
+      return launch_rms_quant<__half, true>(o, scales, input, residual, weight, epsilon, num_tokens, hidden, quant_mode, st);
+    if (dtype == B200_BF16)
+      return launch_rms_quant<__nv_bfloat16, true>(o, scales, input, residual, weight, epsilon, num_tokens, hidden, quant_mode, st);
+  } else {
+    if (dtype == B200_F16)
+      return launch_rms_quant<__half, false>(o, scales, input, nullptr, weight, epsilon, num_tokens, hidden, quant_mode, st);
+    if (dtype == B200_BF16)
+      return launch_rms_quant<__nv_bfloat16, false>(o, scales, input, nullptr, weight, epsilon, num_tokens, hidden, quant_mode, st);
+  }
+  set_error("rms_norm_quant: unsupported dtype %d (fp16 / bf16)", dtype);
   return B200_EINVAL;
 }
 

@@ -82,6 +82,76 @@ def test_rms_norm_vs_reference_cpu_kernels(ops, dtype):
     _ref_cpu_close(xd, xi, dtype)
 
 
+@pytest.mark.parametrize("dtype", [torch.half, torch.bfloat16])
+@pytest.mark.parametrize("hidden", [8, 768, 4096, 8192, 28672])
+@pytest.mark.parametrize("tokens", [1, 7, 83, 2048])
+@pytest.mark.parametrize("add_residual", [False, True])
+@pytest.mark.parametrize("mode", ["int8_dynamic", "int8_static", "fp8_static"])
+def test_rms_norm_quant_is_the_two_ops_back_to_back(ops, dtype, hidden, tokens, add_residual, mode):
+    """(fused_add_)rms_norm + activation quant in one launch must be
+    bit-identical to the reference sequence layernorm_kernels.cu:21-45/199-249 followed by
+    int8_quant_kernels.cu:27-115 / fp8/common.cu:78-105, i.e. to this repo's two separately
+    parity-tested ops, and must match the oracle composition (scales exact, values +-1 LSB as
+    tests/kernels/test_int8_quant.py:25-71 allows)."""
+    from oracle import quant_ref as qr
+    if tokens * hidden > 2048 * 8192:
+        pytest.skip("size")
+    g = torch.Generator().manual_seed(tokens * 131 + hidden)
+    x = torch.randn(tokens, hidden, generator=g).to(dtype)
+    res = torch.randn(tokens, hidden, generator=g).to(dtype) if add_residual else None
+    w = (torch.randn(hidden, generator=g) * 0.1 + 1).to(dtype)
+    static_scale = torch.tensor([0.037], dtype=torch.float32)
+    # unfused: this repo's ops
+    xd = x.to(DEV)
+    rd = res.to(DEV) if add_residual else None
+    if add_residual:
+        ops.fused_add_rms_norm(xd, rd, w.to(DEV), 1e-5)
+        y = xd
+    else:
+        y = torch.empty_like(xd)
+        ops.rms_norm(y, xd, w.to(DEV), 1e-5)
+    if mode == "int8_dynamic":
+        q_ref, s_ref = ops.scaled_int8_quant(y)
+    elif mode == "int8_static":
+        q_ref, s_ref = ops.scaled_int8_quant(y, static_scale.to(DEV))
+    else:
+        q_ref, s_ref = ops.scaled_fp8_quant(y, static_scale.to(DEV))
+    # fused
+    r2 = res.to(DEV) if add_residual else None
+    q, s = ops.rms_norm_quant(x.to(DEV), w.to(DEV), 1e-5, residual=r2,
+                              scale=None if mode == "int8_dynamic" else static_scale.to(DEV),
+                              out_dtype=torch.float8_e4m3fn if mode == "fp8_static" else torch.int8)
+    assert torch.equal(q.view(torch.uint8), q_ref.view(torch.uint8))
+    assert torch.equal(s, s_ref)
+    if add_residual:
+        assert torch.equal(r2, rd)
+    # oracle composition on the CPU (small cases)
+    if tokens <= 83:
+        if add_residual:
+            y_o, _ = gr.fused_add_rms_norm(x, res, w, 1e-5)
+        else:
+            y_o = gr.rms_norm(x, w, 1e-5)
+        if mode == "fp8_static":
+            q_o, _ = qr.scaled_fp8_quant_ref(y_o, static_scale)
+            torch.testing.assert_close(q.cpu().float(), q_o.float(), rtol=0.13, atol=1e-3)  # <= 1 fp8 ulp
+        else:
+            q_o, s_o = qr.scaled_int8_quant_ref(y_o, None if mode == "int8_dynamic" else static_scale)
+            assert (q.cpu().int() - q_o.int()).abs().max() <= 1
+            if mode == "int8_dynamic":
+                torch.testing.assert_close(s.cpu().view(-1), s_o.view(-1).float(), rtol=2e-3, atol=0)
+
+
+def test_rms_norm_quant_rejects(ops):
+    x = torch.randn(4, 64, dtype=torch.half, device=DEV)
+    w = torch.ones(64, dtype=torch.half, device=DEV)
+    with pytest.raises(RuntimeError):
+        ops.rms_norm_quant(x, w, 1e-5, out_dtype=torch.float8_e4m3fn)            # dynamic fp8: not fused
+    with pytest.raises(RuntimeError):
+        ops.rms_norm_quant(x.float(), w.float(), 1e-5)                            # fp32 rows
+    with pytest.raises(RuntimeError):
+        ops.rms_norm_quant(x, w, 1e-5, residual=torch.zeros(4, 32, dtype=torch.half, device=DEV))
+
+
 def test_rms_norm_empty_and_errors(ops):
     x = torch.empty(0, 128, dtype=torch.half, device=DEV)
     ops.rms_norm(torch.empty_like(x), x, torch.ones(128, dtype=torch.half, device=DEV), 1e-6)
