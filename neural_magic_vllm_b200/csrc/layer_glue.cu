@@ -258,8 +258,9 @@ int launch_rms_quant(uint8_t* out, float* scales, const void* in, void* residual
   threads = threads > 1024 ? 1024 : threads;
   auto go = [&](auto kern) -> int {
     if (row_bytes > 48 * 1024) {
-      static size_t configured[kMaxDevices] = {};
-      if (ensure_dyn_smem(kern, row_bytes, configured) != cudaSuccess) {
+      // (the three quant modes share one function-pointer type: one cache row per mode)
+      static size_t configured[3][kMaxDevices] = {};
+      if (ensure_dyn_smem(kern, row_bytes, configured[qmode]) != cudaSuccess) {
         cudaGetLastError();
         set_error("rms_norm_quant: cannot reserve %d B of shared memory", (int)row_bytes);
         return B200_ECUDA;
