@@ -95,6 +95,32 @@ B200_API int b200_paged_attention_v1(const b200_paged_attention_params* p, void*
 B200_API int b200_paged_attention_v2(const b200_paged_attention_params* p, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Variable-length attention for prefill.  Stands in for the library call
+ * of the reference's prefill path: flash_attn_varlen_func (vllm/attention/backends/flash_attn.py:
+ * 320-346) / xformers (backends/xformers.py:340-424); semantics as backends/torch_sdpa.py:203-218.
+ *   q [total_q, num_heads, head_size], k / v [total_k, num_kv_heads, head_size] (token strides in
+ *   elements: q may be a slice of a fused qkv row), out [total_q, num_heads, head_size];
+ *   cu_seqlens_q / cu_seqlens_k [num_seqs + 1] int32 prefix sums; causal mask aligned bottom-right.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  void* out;
+  const void* q;
+  const void* k;
+  const void* v;
+  const int32_t* cu_seqlens_q;
+  const int32_t* cu_seqlens_k;
+  int32_t num_seqs, num_heads, num_kv_heads, head_size;
+  int32_t total_q, total_k, max_seqlen_q, max_seqlen_k;
+  int64_t q_stride, k_stride, v_stride, out_stride; /* elements between consecutive tokens */
+  float softmax_scale;
+  int32_t causal;
+  int32_t dtype; /* B200_F16 / B200_BF16 */
+} b200_varlen_attention_params;
+
+B200_API int b200_varlen_attention_fwd(const b200_varlen_attention_params* p, void* stream);
+
+
+/* ------------------------------------------------------------------------------------------
  * Cache ops.  Replace csrc/cache_kernels.cu (schemas csrc/torch_bindings.cpp:207-244).
  * ------------------------------------------------------------------------------------------ */
 typedef struct {

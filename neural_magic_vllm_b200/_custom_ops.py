@@ -125,6 +125,23 @@ def paged_attention_v2(out, exp_sum, max_logits, tmp_out, query, key_cache, valu
                           blocksparse_block_size, blocksparse_head_sliding_step)
 
 
+def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens_q: torch.Tensor,
+                           cu_seqlens_k: torch.Tensor, max_seqlen_q: int, max_seqlen_k: int,
+                           softmax_scale: Optional[float] = None, causal: bool = False,
+                           out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Prefill attention over packed variable-length sequences, with the call shape of the
+    flash_attn_varlen_func the reference's FlashAttention backend uses
+    (vllm/attention/backends/flash_attn.py:320-346): q [total_q, H, D], k / v [total_k, KVH, D],
+    int32 cu_seqlens.  Extension op: the reference calls a library here."""
+    if softmax_scale is None:
+        softmax_scale = q.shape[-1] ** -0.5
+    if out is None:
+        out = torch.empty_like(q)
+    _C.varlen_attention_fwd(out, q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k,
+                            softmax_scale, causal)
+    return out
+
+
 # ------------------------------------------------------------------ quantized linears (:208-352)
 def gptq_marlin_24_gemm(a, b_q_weight, b_meta, b_scales, workspace, num_bits: int, size_m: int,
                         size_n: int, size_k: int) -> torch.Tensor:  # :208-215

@@ -1,0 +1,391 @@
+// Variable-length causal attention for prefill on tcgen05 / TMEM (sm_100a) -- SURVEY.md 8(f) rank 3.
+// Stands in for the library call the reference's prefill path makes: flash_attn_varlen_func
+// (vllm/attention/backends/flash_attn.py:320-346) / xformers memory_efficient_attention_forward
+// (backends/xformers.py:340-424); semantics = per-sequence softmax(scale * Q K^T + causal mask) V as
+// the reference's CPU backend spells it out (backends/torch_sdpa.py:203-218).  GQA: query head h
+// reads kv head h / (H / KVH).  Causal alignment is bottom-right (query i of a sequence with
+// q_len <= k_len sees keys <= i + k_len - q_len), as flash-attn does.
+//
+// One CTA = 128 queries of one head.  Both GEMMs run on tcgen05 with fp32 accumulators in TMEM:
+//   S = Q K^T   A = Q tile (shared memory, K-major, TMA 128B swizzle), B = K tile (same layout)
+//   O_t = P V   A = P (fp16/bf16, written by the softmax warps straight into TMEM, over the S
+//               columns it came from), B = V tile in its natural [key][d] layout = MN-major operand
+//               (descriptor: 64-d column blocks LBO apart, 8-key groups 1 KiB apart)
+//   warp 0      TMA producer: Q once, then K / V tiles of 128 keys through two-stage rings
+//   warp 1      MMA issuer (one elected lane): QK of tile j + 1 is issued before PV of tile j, so
+//               the tensor pipe works while the softmax warps are on tile j + 1
+//   warps 2-5   softmax, one thread per query row (TMEM lane = row: row max / sum need no
+//               shuffles): two passes over the S row in 32-column chunks (max, then exp2 + pack),
+//               running (m, l) in registers, and the output accumulator o = o * alpha + O_t in
+//               registers (128 fp32 per thread) -- no TMEM correction pass.
+// TMEM: S0, S1 (2 x 128 columns, P aliased inside) + O_t (128 columns) of a 512-column allocation.
+#include "umma.cuh"
+
+namespace b200 {
+namespace {
+
+using namespace umma;
+
+constexpr int kBQ = 128;   // queries per CTA
+constexpr int kBK = 128;   // keys per tile
+constexpr int kFaThreads = 6 * 32;
+
+struct FaArgs {
+  void* out;
+  const int32_t* cu_q;
+  const int32_t* cu_k;
+  int num_heads, num_kv_heads;
+  int64_t out_stride;  // elements between consecutive tokens of out
+  float scale_log2;    // softmax scale * log2(e)
+  int causal;
+};
+
+template <int D>
+struct FaPlan {
+  static constexpr int kTileBytes = kBQ * D * 2;  // one Q / K / V tile: D / 64 boxes of 128 x 128 B
+  static constexpr int kBoxBytes = kBQ * 128;
+  static constexpr int kBytes = 5 * kTileBytes + 1024 + 256;  // Q + 2 K + 2 V
+};
+
+// MN-major operand tile (rows = k index, 128 bytes = 64 elements of the N dimension per row, 8-row
+// swizzle atoms 1 KiB apart, 64-element column blocks `lbo_bytes` apart), SWIZZLE_128B.
+// Canonical form ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units (cute/atom/mma_traits_sm100.hpp).
+__device__ __forceinline__ uint64_t smem_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((1024u >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+      "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <typename T, int D>
+__global__ void __launch_bounds__(kFaThreads, 1)
+varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                        const __grid_constant__ CUtensorMap tm_v, const FaArgs args) {
+  using P = FaPlan<D>;
+  constexpr int KIND = DT<T>::id == B200_F16 ? KIND_F16 : KIND_BF16;
+  constexpr int kBoxes = D / 64;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* q_s = smem;
+  uint8_t* k_s = q_s + P::kTileBytes;       // [2]
+  uint8_t* v_s = k_s + 2 * P::kTileBytes;   // [2]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(v_s + 2 * P::kTileBytes);
+  uint64_t* q_full = bars;
+  uint64_t* k_full = bars + 1;    // [2]
+  uint64_t* v_full = bars + 3;    // [2]
+  uint64_t* k_empty = bars + 5;   // [2]
+  uint64_t* v_empty = bars + 7;   // [2]
+  uint64_t* s_full = bars + 9;    // [2]
+  uint64_t* p_full = bars + 11;   // [2]
+  uint64_t* o_full = bars + 13;
+  uint64_t* o_empty = bars + 14;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+  const int seq = blockIdx.y, head = blockIdx.z;
+  const int q_begin = args.cu_q[seq], q_len = args.cu_q[seq + 1] - q_begin;
+  const int k_begin = args.cu_k[seq], k_len = args.cu_k[seq + 1] - k_begin;
+  const int q0 = blockIdx.x * kBQ;  // first query of this tile inside the sequence
+  if (q0 >= q_len) return;          // uniform over the CTA: nothing allocated yet
+  const int shift = k_len - q_len;  // bottom-right causal alignment
+  // keys this tile can see: [0, k_end)
+  const int k_end = args.causal ? max(0, min(k_len, min(q0 + kBQ, q_len) + shift)) : k_len;
+  const int nt = (k_end + kBK - 1) / kBK;
+  const int kv_head = head / (args.num_heads / args.num_kv_heads);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_q);
+    tma_prefetch_desc(&tm_k);
+    tma_prefetch_desc(&tm_v);
+    mbar_init(q_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_empty[i], 1);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_full[i], 4);
+    }
+    mbar_init(o_full, 1);
+    mbar_init(o_empty, 4);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  constexpr uint32_t kSCol = 0, kOCol = 256;  // S0 at 0, S1 at 128, O_t at 256
+
+  if (warp == 0) {
+    // ======================= TMA producer =======================
+    const bool leader = elect_one();
+    const uint64_t pol = l2_policy_evict_last();  // K / V are re-read by the other heads of the group
+    pdl_wait();
+    if (leader) {
+      mbar_arrive_expect_tx(q_full, P::kTileBytes);
+#pragma unroll
+      for (int b = 0; b < kBoxes; ++b)
+        tma_load_2d(q_s + b * P::kBoxBytes, &tm_q, head * D + b * 64, q_begin + q0, q_full, pol);
+    }
+    for (int j = 0; j < nt; ++j) {
+      const int st = j & 1;
+      const uint32_t ph = ((j >> 1) & 1) ^ 1;
+      mbar_wait_bounded(&k_empty[st], ph);
+      if (leader) {
+        mbar_arrive_expect_tx(&k_full[st], P::kTileBytes);
+#pragma unroll
+        for (int b = 0; b < kBoxes; ++b)
+          tma_load_2d(k_s + st * P::kTileBytes + b * P::kBoxBytes, &tm_k, kv_head * D + b * 64,
+                      k_begin + j * kBK, &k_full[st], pol);
+      }
+      mbar_wait_bounded(&v_empty[st], ph);
+      if (leader) {
+        mbar_arrive_expect_tx(&v_full[st], P::kTileBytes);
+#pragma unroll
+        for (int b = 0; b < kBoxes; ++b)
+          tma_load_2d(v_s + st * P::kTileBytes + b * P::kBoxBytes, &tm_v, kv_head * D + b * 64,
+                      k_begin + j * kBK, &v_full[st], pol);
+      }
+    }
+  } else if (warp == 1) {
+    // ======================= MMA issuer =======================
+    const bool leader = elect_one();
+    constexpr uint32_t idesc_qk = instr_desc<KIND>(kBQ, kBK);             // S[128 q, 128 keys]
+    constexpr uint32_t idesc_pv = instr_desc<KIND>(kBQ, D) | (1u << 16);  // O_t[128 q, D], B MN-major
+    auto issue_qk = [&](int j) {
+      const int st = j & 1;
+      mbar_wait_bounded(&k_full[st], (j >> 1) & 1);
+      fence_after_sync();
+      const uint32_t qa = smem_u32(q_s), ka = smem_u32(k_s + st * P::kTileBytes);
+      if (leader) {
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * P::kBoxBytes + (kk & 3) * 32;
+          mma_ss<KIND>(tmem_base + kSCol + st * kBK, smem_desc_sw128(qa + off), smem_desc_sw128(ka + off), idesc_qk,
+                       kk > 0 ? 1u : 0u);
+        }
+        mma_commit(&s_full[st]);
+        mma_commit(&k_empty[st]);
+      }
+    };
+    mbar_wait_bounded(q_full, 0);
+    if (nt > 0) issue_qk(0);
+    for (int j = 0; j < nt; ++j) {
+      const int st = j & 1;
+      if (j + 1 < nt) issue_qk(j + 1);  // the tensor pipe works on S_{j+1} while tile j is in softmax
+      mbar_wait_bounded(&p_full[st], (j >> 1) & 1);
+      mbar_wait_bounded(&v_full[st], (j >> 1) & 1);
+      mbar_wait_bounded(o_empty, (j & 1) ^ 1);
+      fence_after_sync();
+      const uint32_t va = smem_u32(v_s + st * P::kTileBytes);
+      if (leader) {
+#pragma unroll
+        for (int kk = 0; kk < kBK / 16; ++kk)  // 16 keys per MMA: 8 packed P columns, 16 V rows
+          mma_ts_f16(tmem_base + kOCol, tmem_base + kSCol + st * kBK + kk * 8,
+                     smem_desc_mn_sw128(va + kk * 2048, P::kBoxBytes), idesc_pv, kk > 0 ? 1u : 0u);
+        mma_commit(o_full);
+        mma_commit(&v_empty[st]);
+      }
+    }
+    pdl_launch_dependents();
+  } else {
+    // ======================= softmax + output accumulation (thread = query row) =======================
+    const int qd = warp & 3;
+    const int row = qd * 32 + lane;           // TMEM lane
+    const int qi = q0 + row;                  // query index inside the sequence
+    const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16);
+    const float c = args.scale_log2;
+    // keys this row may see: [0, row_end)
+    const int row_end = args.causal ? min(k_len, qi + shift + 1) : k_len;
+    float m = -1e30f, l = 0.f;
+    float o_acc[D];
+#pragma unroll
+    for (int i = 0; i < D; ++i) o_acc[i] = 0.f;
+    float alpha_prev = 1.f;
+    auto accumulate = [&](int j, float alpha) {  // o = o * alpha + O_t of tile j
+      mbar_wait_bounded(o_full, j & 1);
+      fence_after_sync();
+#pragma unroll
+      for (int cc = 0; cc < D / 32; ++cc) {
+        uint32_t r[32];
+        tmem_ld32(t_lane + kOCol + cc * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o_acc[cc * 32 + i] = fmaf(o_acc[cc * 32 + i], alpha, __uint_as_float(r[i]));
+      }
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(o_empty);
+    };
+    for (int j = 0; j < nt; ++j) {
+      const int st = j & 1;
+      const uint32_t s_addr = t_lane + kSCol + st * kBK;
+      const int lim = row_end - j * kBK;  // columns < lim are visible to this row
+      mbar_wait_bounded(&s_full[st], (j >> 1) & 1);
+      fence_after_sync();
+      // pass 1: row maximum
+      float mx = -1e30f;
+#pragma unroll 1
+      for (int cc = 0; cc < kBK / 32; ++cc) {
+        uint32_t r[32];
+        tmem_ld32(s_addr + cc * 32, r);
+        tmem_ld_wait();
+        if (lim >= (cc + 1) * 32) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (cc * 32 + i < lim) mx = fmaxf(mx, __uint_as_float(r[i]));
+        }
+      }
+      const float m_new = fmaxf(m, mx);
+      const float alpha = ex2((m - m_new) * c);
+      const float mc = m_new * c;
+      // pass 2: p = exp2(s c - m c), row sum, packed 16-bit P over the S columns already consumed
+      float sum = 0.f;
+#pragma unroll 1
+      for (int cc = 0; cc < kBK / 32; ++cc) {
+        uint32_t r[32];
+        tmem_ld32(s_addr + cc * 32, r);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float p0 = ex2(fmaf(__uint_as_float(r[i]), c, -mc));
+          float p1 = ex2(fmaf(__uint_as_float(r[i + 1]), c, -mc));
+          if (cc * 32 + i >= lim) p0 = 0.f;
+          if (cc * 32 + i + 1 >= lim) p1 = 0.f;
+          sum += p0 + p1;
+          pk[i >> 1] = DT<T>::pack2(p0, p1);
+        }
+        tmem_st16(s_addr + cc * 16, pk);
+      }
+      l = fmaf(l, alpha, sum);
+      m = m_new;
+      tmem_st_wait();
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[st]);
+      // the previous tile's P V finished while this tile was in softmax
+      if (j > 0) accumulate(j - 1, alpha_prev);
+      alpha_prev = alpha;
+    }
+    if (nt > 0) accumulate(nt - 1, alpha_prev);
+    // o / l -> out[token][head][:]
+    if (qi < q_len) {
+      const float inv = l > 0.f ? 1.f / l : 0.f;
+      T* dst = reinterpret_cast<T*>(args.out) + (int64_t)(q_begin + qi) * args.out_stride + (int64_t)head * D;
+#pragma unroll
+      for (int i = 0; i < D; i += 8) {
+        uint4 v;
+        v.x = DT<T>::pack2(o_acc[i] * inv, o_acc[i + 1] * inv);
+        v.y = DT<T>::pack2(o_acc[i + 2] * inv, o_acc[i + 3] * inv);
+        v.z = DT<T>::pack2(o_acc[i + 4] * inv, o_acc[i + 5] * inv);
+        v.w = DT<T>::pack2(o_acc[i + 6] * inv, o_acc[i + 7] * inv);
+        *reinterpret_cast<uint4*>(dst + i) = v;
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    fence_after_sync();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+template <typename T, int D>
+int launch_fa(const b200_varlen_attention_params& p, cudaStream_t st) {
+  using P = FaPlan<D>;
+  CUtensorMap tm_q, tm_k, tm_v;
+  const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_UINT16;
+  int rc = make_tmap_2d_ex(&tm_q, p.q, (uint64_t)p.total_q, (uint64_t)p.num_heads * D, (uint64_t)p.q_stride * 2, dt, 64,
+                           kBQ, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc != B200_OK) return rc;
+  rc = make_tmap_2d_ex(&tm_k, p.k, (uint64_t)p.total_k, (uint64_t)p.num_kv_heads * D, (uint64_t)p.k_stride * 2, dt, 64,
+                       kBK, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc != B200_OK) return rc;
+  rc = make_tmap_2d_ex(&tm_v, p.v, (uint64_t)p.total_k, (uint64_t)p.num_kv_heads * D, (uint64_t)p.v_stride * 2, dt, 64,
+                       kBK, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc != B200_OK) return rc;
+  FaArgs a{};
+  a.out = p.out;
+  a.cu_q = p.cu_seqlens_q;
+  a.cu_k = p.cu_seqlens_k;
+  a.num_heads = p.num_heads;
+  a.num_kv_heads = p.num_kv_heads;
+  a.out_stride = p.out_stride;
+  a.scale_log2 = p.softmax_scale * 1.4426950408889634f;
+  a.causal = p.causal;
+  auto kern = varlen_attention_kernel<T, D>;
+  static size_t configured[kMaxDevices] = {};
+  if (ensure_dyn_smem(kern, P::kBytes, configured) != cudaSuccess) {
+    cudaGetLastError();
+    set_error("varlen_attention_fwd: cannot reserve %d B of shared memory", (int)P::kBytes);
+    return B200_ECUDA;
+  }
+  const int q_tiles = (p.max_seqlen_q + kBQ - 1) / kBQ;
+  cudaError_t le = launch_pdl(kern, dim3(q_tiles, p.num_seqs, p.num_heads), dim3(kFaThreads), (size_t)P::kBytes, st,
+                              tm_q, tm_k, tm_v, a);
+  if (le != cudaSuccess) {
+    cudaGetLastError();
+    set_error("varlen_attention_fwd: launch failed: %s", cudaGetErrorString(le));
+    return B200_ECUDA;
+  }
+  return B200_OK;
+}
+
+}  // namespace
+}  // namespace b200
+
+extern "C" int b200_varlen_attention_fwd(const b200_varlen_attention_params* pp, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(pp != nullptr, B200_EINVAL, "varlen_attention_fwd: null params");
+  const b200_varlen_attention_params& p = *pp;
+  B200_REQUIRE(p.num_seqs >= 0 && p.total_q >= 0 && p.total_k >= 0, B200_EINVAL, "varlen_attention_fwd: negative size");
+  if (p.num_seqs == 0 || p.total_q == 0 || p.max_seqlen_q == 0) return B200_OK;
+  B200_REQUIRE(p.out && p.q && p.k && p.v && p.cu_seqlens_q && p.cu_seqlens_k, B200_EINVAL,
+               "varlen_attention_fwd: null pointer");
+  B200_REQUIRE(p.head_size == 128, B200_ENOTSUP, "varlen_attention_fwd: head_size %d (128 is built)", p.head_size);
+  B200_REQUIRE(p.num_kv_heads > 0 && p.num_heads % p.num_kv_heads == 0, B200_EINVAL,
+               "varlen_attention_fwd: num_heads must be a multiple of num_kv_heads");
+  B200_REQUIRE(((uintptr_t)p.q & 15) == 0 && ((uintptr_t)p.k & 15) == 0 && ((uintptr_t)p.v & 15) == 0 &&
+                   ((uintptr_t)p.out & 15) == 0 && p.q_stride % 8 == 0 && p.k_stride % 8 == 0 &&
+                   p.v_stride % 8 == 0 && p.out_stride % 8 == 0,
+               B200_EINVAL, "varlen_attention_fwd: tensors must be 16-byte aligned with 16-byte aligned token strides");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (p.dtype == B200_F16) return launch_fa<__half, 128>(p, st);
+  if (p.dtype == B200_BF16) return launch_fa<__nv_bfloat16, 128>(p, st);
+  set_error("varlen_attention_fwd: unsupported dtype %d (fp16 / bf16)", p.dtype);
+  return B200_EINVAL;
+}

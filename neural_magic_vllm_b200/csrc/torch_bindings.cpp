@@ -164,6 +164,52 @@ void paged_attention_v1(Tensor& out, Tensor& query, Tensor& key_cache, Tensor& v
   check_rc(b200_paged_attention_v1(&p, cur_stream()));
 }
 
+// extension: variable-length causal attention for prefill (stands in for flash_attn_varlen_func /
+// xformers of the reference's prefill path)
+void varlen_attention_fwd(Tensor& out, const Tensor& q, const Tensor& k, const Tensor& v,
+                          const Tensor& cu_seqlens_q, const Tensor& cu_seqlens_k, int64_t max_seqlen_q,
+                          int64_t max_seqlen_k, double softmax_scale, bool causal) {
+  B200_TCHECK(q.is_cuda() && k.is_cuda() && v.is_cuda() && out.is_cuda(), "varlen_attention_fwd: CUDA tensors");
+  B200_TCHECK(q.dim() == 3 && k.dim() == 3 && v.dim() == 3 && out.dim() == 3,
+              "varlen_attention_fwd: q / k / v / out must be [tokens, heads, head_size]");
+  B200_TCHECK(q.stride(2) == 1 && k.stride(2) == 1 && v.stride(2) == 1 && out.stride(2) == 1 &&
+                  q.stride(1) == q.size(2) && k.stride(1) == k.size(2) && v.stride(1) == v.size(2) &&
+                  out.stride(1) == out.size(2),
+              "varlen_attention_fwd: heads must be contiguous inside a token");
+  B200_TCHECK(k.sizes() == v.sizes() && q.size(2) == k.size(2) && out.sizes() == q.sizes(), "varlen_attention_fwd: shapes");
+  B200_TCHECK(q.scalar_type() == k.scalar_type() && q.scalar_type() == v.scalar_type() &&
+                  q.scalar_type() == out.scalar_type(), "varlen_attention_fwd: dtypes must match");
+  B200_TCHECK(cu_seqlens_q.scalar_type() == at::ScalarType::Int && cu_seqlens_k.scalar_type() == at::ScalarType::Int &&
+                  cu_seqlens_q.is_cuda() && cu_seqlens_k.is_cuda() && cu_seqlens_q.is_contiguous() &&
+                  cu_seqlens_k.is_contiguous() && cu_seqlens_q.numel() == cu_seqlens_k.numel() &&
+                  cu_seqlens_q.numel() >= 1,
+              "varlen_attention_fwd: cu_seqlens must be int32 CUDA vectors of num_seqs + 1 entries");
+  const at::cuda::OptionalCUDAGuard guard(device_of(q));
+  b200_varlen_attention_params p{};
+  p.out = out.data_ptr();
+  p.q = q.data_ptr();
+  p.k = k.data_ptr();
+  p.v = v.data_ptr();
+  p.cu_seqlens_q = cu_seqlens_q.data_ptr<int32_t>();
+  p.cu_seqlens_k = cu_seqlens_k.data_ptr<int32_t>();
+  p.num_seqs = (int32_t)cu_seqlens_q.numel() - 1;
+  p.num_heads = (int32_t)q.size(1);
+  p.num_kv_heads = (int32_t)k.size(1);
+  p.head_size = (int32_t)q.size(2);
+  p.total_q = (int32_t)q.size(0);
+  p.total_k = (int32_t)k.size(0);
+  p.max_seqlen_q = (int32_t)max_seqlen_q;
+  p.max_seqlen_k = (int32_t)max_seqlen_k;
+  p.q_stride = q.stride(0);
+  p.k_stride = k.stride(0);
+  p.v_stride = v.stride(0);
+  p.out_stride = out.stride(0);
+  p.softmax_scale = (float)softmax_scale;
+  p.causal = causal ? 1 : 0;
+  p.dtype = dtype_of(q, "varlen_attention_fwd");
+  check_rc(b200_varlen_attention_fwd(&p, cur_stream()));
+}
+
 void paged_attention_v2(Tensor& out, Tensor& exp_sums, Tensor& max_logits, Tensor& tmp_out,
                         Tensor& query, Tensor& key_cache, Tensor& value_cache, int64_t num_kv_heads,
                         double scale, Tensor& block_tables, Tensor& seq_lens, int64_t block_size,
@@ -366,6 +412,10 @@ B200_TORCH_LIBRARY(B200_TORCH_NS, ops) {
       "    int blocksparse_vert_stride, int blocksparse_block_size,"
       "    int blocksparse_head_sliding_step) -> ()");
   ops.impl("paged_attention_v2", c10::DispatchKey::CUDA, &paged_attention_v2);
+  ops.def(
+      "varlen_attention_fwd(Tensor! out, Tensor q, Tensor k, Tensor v, Tensor cu_seqlens_q, Tensor cu_seqlens_k, "
+      "int max_seqlen_q, int max_seqlen_k, float softmax_scale, bool causal) -> ()");
+  ops.impl("varlen_attention_fwd", c10::DispatchKey::CUDA, &varlen_attention_fwd);
   b200_register_quant_ops(ops);
   b200_register_glue_ops(ops);
 }

@@ -121,3 +121,28 @@ def gather_last_tokens(key_cache, value_cache, block_tables, seq_lens):
         ks.append(k[-1])
         vs.append(v[-1])
     return torch.stack(ks).contiguous(), torch.stack(vs).contiguous()
+
+
+def varlen_attention_ref(q, k, v, cu_seqlens_q, cu_seqlens_k, softmax_scale, causal):
+    """Per-sequence softmax(scale * Q K^T + mask) V in fp32, the arithmetic of the reference's CPU
+    prefill path (vllm/attention/backends/torch_sdpa.py:203-218: scaled_dot_product_attention per
+    sequence, K/V heads repeated for GQA) with the bottom-right aligned causal mask of
+    flash_attn_varlen_func (backends/flash_attn.py:320-346).  q [Tq, H, D], k / v [Tk, KVH, D]."""
+    out = torch.zeros(q.shape, dtype=torch.float32)
+    h, kvh = q.shape[1], k.shape[1]
+    cq, ck = cu_seqlens_q.tolist(), cu_seqlens_k.tolist()
+    for s in range(len(cq) - 1):
+        qs = q[cq[s]:cq[s + 1]].float().transpose(0, 1)                                   # [H, Lq, D]
+        ks = k[ck[s]:ck[s + 1]].float().transpose(0, 1).repeat_interleave(h // kvh, 0)    # [H, Lk, D]
+        vs = v[ck[s]:ck[s + 1]].float().transpose(0, 1).repeat_interleave(h // kvh, 0)
+        lq, lk = qs.shape[1], ks.shape[1]
+        if lq == 0:
+            continue
+        logits = torch.einsum("hqd,hkd->hqk", qs, ks) * softmax_scale
+        if causal:
+            mask = torch.ones(lq, lk, dtype=torch.bool).tril(diagonal=lk - lq)
+            logits = logits.masked_fill(~mask, float("-inf"))
+        p = torch.softmax(logits, dim=-1)
+        p = torch.nan_to_num(p, nan=0.0)  # rows with no visible key
+        out[cq[s]:cq[s + 1]] = torch.einsum("hqk,hkd->hqd", p, vs).transpose(0, 1)
+    return out
