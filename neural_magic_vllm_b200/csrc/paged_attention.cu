@@ -341,8 +341,24 @@ static int run_paged_attention(const b200_paged_attention_params* p, bool v2, cu
     B200_REQUIRE(stages <= kAttnMaxStages && stages * a.stage_bytes >= merge_bytes, B200_ENOTSUP,
                  "paged_attention: internal stage sizing");
     a.stages = stages;
-    const size_t smem = 256 + (size_t)kAttnWarps * stages * a.stage_bytes;
-    dim3 grid(p->num_kv_heads * a.q_tiles, p->num_seqs, a.max_num_partitions);
+    // Few CTAs (small batch, or v1's single partition per sequence): split every partition over a
+    // cluster of 2 / 4 / 8 CTAs, merged through distributed shared memory, until the grid holds
+    // >= 8 CTAs per SM or a CTA would get fewer than 128 tokens.
+    const int base_ctas = p->num_kv_heads * a.q_tiles * p->num_seqs * a.max_num_partitions;
+    const int part_tokens = v2 ? (p->max_seq_len < B200_PARTITION_SIZE ? p->max_seq_len : B200_PARTITION_SIZE)
+                               : p->max_seq_len;
+    int cluster = 1;
+    while (cluster < 8 && base_ctas * cluster < 8 * num_sms() && part_tokens / (cluster * 2) >= 128) cluster *= 2;
+    {  // tuning knob (bench sweeps), read once per process: 1 / 2 / 4 / 8 forces the cluster size
+      static int knob[2] = {0, 0};
+      const int v = env_int_once("B200_ATTN_CLUSTER", knob, 0);
+      if (v == 1 || v == 2 || v == 4 || v == 8) cluster = v;
+    }
+    a.cluster = cluster;
+    const int nh = 8 * nt;
+    const size_t smem = 256 + (size_t)kAttnWarps * stages * a.stage_bytes +
+                        (cluster > 1 ? (size_t)nh * (hs + 2) * sizeof(float) : 0);
+    dim3 grid(p->num_kv_heads * a.q_tiles, p->num_seqs, a.max_num_partitions * cluster);
     rc = p->dtype == B200_F16 ? launch_paged_attn_mma<__half>(a, p->kv_dtype, grid, smem, stream)
                               : launch_paged_attn_mma<__nv_bfloat16>(a, p->kv_dtype, grid, smem, stream);
   } else {

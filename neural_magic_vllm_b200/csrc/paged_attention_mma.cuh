@@ -88,7 +88,13 @@ __global__ void __launch_bounds__(kAttnThreads)
   const int kvh = blockIdx.x / a.q_tiles;
   const int qtile = blockIdx.x - kvh * a.q_tiles;
   const int seq = blockIdx.y;
-  const int part = blockIdx.z;
+  // a cluster of C CTAs (consecutive in z) shares one (kv head, sequence, partition): each takes a
+  // contiguous slice of the partition's 16-token items and the slices are merged through
+  // distributed shared memory at the end -- more CTAs per sequence without touching the
+  // caller-owned partition layout (paged_attn.py:145-156 fixes it at 512 tokens)
+  const int C = a.cluster;
+  const int part = C > 1 ? blockIdx.z / C : blockIdx.z;
+  const int crank = C > 1 ? blockIdx.z - part * C : 0;
   const int BS = FAST ? 16 : a.block_size;
   const int D = FAST ? HMAX : a.head_size;
   const int nks = D >> 4;
@@ -102,8 +108,13 @@ __global__ void __launch_bounds__(kAttnThreads)
   if (partitioned && tok_begin >= seq_len) return;  // attention_kernels.cu:128-131
 
   const int IT = BS < 16 ? 16 : BS;  // tokens per pipeline item (stage)
-  const int item_begin = tok_begin / IT;
-  const int item_end = (tok_end + IT - 1) / IT;
+  int item_begin = tok_begin / IT;
+  int item_end = (tok_end + IT - 1) / IT;
+  if (C > 1) {
+    const int per = (max(item_end - item_begin, 0) + C - 1) / C;
+    item_begin += crank * per;
+    item_end = min(item_end, item_begin + per);
+  }
   const int n_total = max(item_end - item_begin, 0);
   const int n_items = n_total > warp ? (n_total - warp + kAttnWarps - 1) / kAttnWarps : 0;
   const int num_seq_blocks = (seq_len + BS - 1) / BS;
@@ -482,26 +493,12 @@ __global__ void __launch_bounds__(kAttnThreads)
   const size_t wstride = (size_t)S * stage_bytes / sizeof(float);  // floats between warps' areas
   const float* base = reinterpret_cast<const float*>(smem + 256);
   const int half_d = D >> 1;
-  for (int idx = tid; idx < NH * half_d; idx += kAttnThreads) {
-    const int h = idx / half_d;
-    const int d2 = idx - h * half_d;
+  // cluster exchange area behind the rings: [NH][D] unnormalised output, then m[NH], l[NH]
+  float* xo = reinterpret_cast<float*>(smem + 256 + (size_t)kAttnWarps * S * stage_bytes);
+  float* xm = xo + NH * D;
+  float* xl = xm + NH;
+  auto finish = [&](int h, int d2, float M, float L, float o0, float o1) {
     const int hg = head_in_group0 + h;
-    if (hg >= G) continue;
-    float mw[kAttnWarps], M = -INFINITY;
-#pragma unroll
-    for (int w = 0; w < kAttnWarps; ++w) {
-      mw[w] = base[w * wstride + NH * DP + h];
-      M = fmaxf(M, mw[w]);
-    }
-    float L = 0.f, o0 = 0.f, o1 = 0.f;
-#pragma unroll
-    for (int w = 0; w < kAttnWarps; ++w) {
-      const float f = mw[w] == -INFINITY ? 0.f : exp2f(mw[w] - M);
-      L = fmaf(base[w * wstride + NH * DP + NH + h], f, L);
-      const float2 v = *reinterpret_cast<const float2*>(&base[w * wstride + h * DP + 2 * d2]);
-      o0 = fmaf(v.x, f, o0);
-      o1 = fmaf(v.y, f, o1);
-    }
     // attention_kernels.cu:342: inv_sum = 1 / (exp_sum + 1e-6)
     const float inv = a.v_scale * __fdividef(1.f, L + 1e-6f);
     const int head = kvh * G + hg;
@@ -519,6 +516,68 @@ __global__ void __launch_bounds__(kAttnThreads)
       T* dst = reinterpret_cast<T*>(a.out) + ((int64_t)seq * a.num_heads + head) * D;
       *reinterpret_cast<uint32_t*>(dst + 2 * d2) = packed;
     }
+  };
+  for (int idx = tid; idx < NH * half_d; idx += kAttnThreads) {
+    const int h = idx / half_d;
+    const int d2 = idx - h * half_d;
+    if (head_in_group0 + h >= G) continue;
+    float mw[kAttnWarps], M = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < kAttnWarps; ++w) {
+      mw[w] = base[w * wstride + NH * DP + h];
+      M = fmaxf(M, mw[w]);
+    }
+    float L = 0.f, o0 = 0.f, o1 = 0.f;
+#pragma unroll
+    for (int w = 0; w < kAttnWarps; ++w) {
+      const float f = mw[w] == -INFINITY ? 0.f : exp2f(mw[w] - M);
+      L = fmaf(base[w * wstride + NH * DP + NH + h], f, L);
+      const float2 v = *reinterpret_cast<const float2*>(&base[w * wstride + h * DP + 2 * d2]);
+      o0 = fmaf(v.x, f, o0);
+      o1 = fmaf(v.y, f, o1);
+    }
+    if (C == 1) {
+      finish(h, d2, M, L, o0, o1);
+    } else {
+      *reinterpret_cast<float2*>(&xo[h * D + 2 * d2]) = make_float2(o0, o1);
+      if (d2 == 0) xm[h] = M, xl[h] = L;
+    }
+  }
+  if (C > 1) {
+    // every CTA of the cluster has published its slice; rank 0 merges them in rank order
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (crank == 0) {
+      const uint32_t xo_s = smem_u32(xo), xm_s = smem_u32(xm), xl_s = smem_u32(xl);
+      auto remote = [](uint32_t local, int rank) {
+        uint32_t r;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+        return r;
+      };
+      auto ld_f = [](uint32_t addr) {
+        float v;
+        asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+        return v;
+      };
+      for (int idx = tid; idx < NH * half_d; idx += kAttnThreads) {
+        const int h = idx / half_d;
+        const int d2 = idx - h * half_d;
+        if (head_in_group0 + h >= G) continue;
+        float M = -INFINITY;
+        for (int c = 0; c < C; ++c) M = fmaxf(M, ld_f(remote(xm_s + h * 4, c)));
+        float L = 0.f, o0 = 0.f, o1 = 0.f;
+        for (int c = 0; c < C; ++c) {
+          const float mc = ld_f(remote(xm_s + h * 4, c));
+          const float f = mc == -INFINITY ? 0.f : exp2f(mc - M);
+          L = fmaf(ld_f(remote(xl_s + h * 4, c)), f, L);
+          const uint32_t oa = remote(xo_s + (h * D + 2 * d2) * 4, c);
+          o0 = fmaf(ld_f(oa), f, o0);
+          o1 = fmaf(ld_f(oa + 4), f, o1);
+        }
+        finish(h, d2, M, L, o0, o1);
+      }
+    }
+    // nobody leaves (and frees its shared memory) before rank 0 has read it
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
   }
 }
 
@@ -532,7 +591,28 @@ static int launch_one(const AttnArgs& a, dim3 grid, size_t smem, cudaStream_t st
     set_error("paged_attention: cannot reserve %zu B of shared memory: %s", smem, cudaGetErrorString(e));
     return B200_ECUDA;
   }
-  launch_pdl(kern, grid, dim3(kAttnThreads), smem, stream, a);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(kAttnThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (a.cluster > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 1;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = (unsigned)a.cluster;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  cudaLaunchKernelEx(&cfg, kern, a);
   return check_launch("paged_attention");
 }
 
