@@ -341,14 +341,16 @@ static int run_paged_attention(const b200_paged_attention_params* p, bool v2, cu
     B200_REQUIRE(stages <= kAttnMaxStages && stages * a.stage_bytes >= merge_bytes, B200_ENOTSUP,
                  "paged_attention: internal stage sizing");
     a.stages = stages;
-    // Few CTAs (small batch, or v1's single partition per sequence): split every partition over a
-    // cluster of 2 / 4 / 8 CTAs, merged through distributed shared memory, until the grid holds
-    // >= 8 CTAs per SM or a CTA would get fewer than 128 tokens.
+    // Fewer CTAs than SMs (batch 1-4 decode): split every partition over a cluster of 2 / 4 / 8 CTAs,
+    // merged through distributed shared memory, until the grid covers the SMs or a CTA would get
+    // fewer than 128 tokens.  (Measured, profiles/r2_decode_tokens.md: batch 1 2.43 -> 2.34 ms per
+    // step; with >= 1 CTA per SM already the split only adds cluster-launch and merge cost --
+    // batch 16 2.79 -> 3.33 ms when forced -- so it stops there.)
     const int base_ctas = p->num_kv_heads * a.q_tiles * p->num_seqs * a.max_num_partitions;
     const int part_tokens = v2 ? (p->max_seq_len < B200_PARTITION_SIZE ? p->max_seq_len : B200_PARTITION_SIZE)
                                : p->max_seq_len;
     int cluster = 1;
-    while (cluster < 8 && base_ctas * cluster < 8 * num_sms() && part_tokens / (cluster * 2) >= 128) cluster *= 2;
+    while (cluster < 8 && base_ctas * cluster < num_sms() && part_tokens / (cluster * 2) >= 128) cluster *= 2;
     {  // tuning knob (bench sweeps), read once per process: 1 / 2 / 4 / 8 forces the cluster size
       static int knob[2] = {0, 0};
       const int v = env_int_once("B200_ATTN_CLUSTER", knob, 0);
