@@ -66,6 +66,14 @@ __device__ __forceinline__ uint32_t fp8x2_to_T2(uint32_t v) {
   }
 }
 
+__device__ __forceinline__ bool umma_elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 template <typename T, int KV>
 __device__ __forceinline__ void fp8x4_to_frag(uint32_t w, uint32_t& lo, uint32_t& hi) {
   lo = fp8x2_to_T2<T, KV>(w);
@@ -151,6 +159,7 @@ __global__ void __launch_bounds__(kAttnThreads)
   const int64_t blk_bytes = a.kv_block_stride * ESZ;
 
   // producer state: item index -> ring slot, without divisions
+  const bool leader = umma_elect_one();
   int iss_i = 0, iss_s = 0;
   auto issue_next = [&]() {  // whole warp calls; lane 0 issues
     const int i = iss_i;
@@ -158,7 +167,7 @@ __global__ void __launch_bounds__(kAttnThreads)
     const int p0 = __shfl_sync(0xffffffffu, bt0, i & 31);
     int p1 = 0;
     if (!FAST && BS < 16) p1 = __shfl_sync(0xffffffffu, bt1, i & 31);
-    if (lane == 0) {
+    if (leader) {  // elect.sync: the copy's operands stay in uniform registers (no waterfall loop)
       uint8_t* dst = wbase + (size_t)iss_s * stage_bytes;
       uint64_t* bar = &wbar[iss_s];
       if (FAST || BS >= 16) {
