@@ -360,6 +360,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 constexpr int kTmemAStageCols = kStageK / 2;  // 32
 constexpr int kTDequantWarps = 4;          // one per TMEM quadrant
 constexpr int kTThreads = 64 + kTDequantWarps * 32;
+constexpr int kTmemDCol = kAStages * kTmemAStageCols;
 
 template <int BITS, int BM>
 struct PlanT {
@@ -367,14 +368,9 @@ struct PlanT {
   static constexpr int kScaleBytes = kMaxScaleRows * kTileN * 2;
   static constexpr int kXBytes = BM * 128;
   static constexpr int kStageBytes = kPackedBytes + kScaleBytes + kXBytes;
-  // BM = 64: a 4-stage ring and a 2-slot A ring keep the CTA at 128 TMEM columns / 55 KiB of shared
-  // memory, so four CTAs share an SM at every decode batch size (round 1: two at BM 64)
-  static constexpr int kStages = BM <= 32 ? 6 : 4;
-  static constexpr int kAS = BM <= 32 ? 3 : 2;            // TMEM A-ring slots
-  static constexpr int kDCol = kAS * kTmemAStageCols;     // accumulator behind the A ring
+  static constexpr int kStages = 6;
   static constexpr int kBytes = kStages * kStageBytes + 1024 + 512;
-  static constexpr uint32_t kTmemCols = kDCol + BM <= 128 ? 128 : 256;
-  static_assert(kDCol + BM <= 128, "four CTAs per SM need <= 128 TMEM columns each");
+  static constexpr uint32_t kTmemCols = kTmemDCol + BM <= 128 ? 128 : 256;
 };
 
 __device__ __forceinline__ uint2 lds64(uint32_t addr) {
@@ -384,13 +380,11 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
 }
 
 template <int BITS, int BM, typename T>
-__global__ void __launch_bounds__(kTThreads, 4)
+__global__ void __launch_bounds__(kTThreads, (BM <= 32 ? 4 : 2))
 marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                         const __grid_constant__ CUtensorMap tm_s, const MarlinArgs args) {
   using P = PlanT<BITS, BM>;
   constexpr int kStages = P::kStages;
-  constexpr int kAStages = P::kAS;
-  constexpr int kTmemDCol = P::kDCol;
   constexpr int KIND = DT<T>::id == B200_F16 ? KIND_F16 : KIND_BF16;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -751,10 +745,10 @@ inline int pick_splits(int m, int n, int num_kb, int64_t ws_bytes) {
   const int bm = pick_bm(m);
   const int cta_n = kTileN * pick_nt(bm);
   const int tiles = ((m + bm - 1) / bm) * ((n + cta_n - 1) / cta_n);
-  // CTAs that are resident at once: 4 per SM for the decode kernel (BM <= 64), 1 for
+  // CTAs that are resident at once: 4 per SM for the decode kernel at BM <= 32, 2 at BM = 64, 1 for
   // the large tiles.  Split K until one resident wave covers the grid (never past it: a second,
   // partial wave costs more than idle SM slots).
-  const int per_sm = bm <= 64 ? 4 : 1;
+  const int per_sm = bm <= 32 ? 4 : bm <= 64 ? 2 : 1;
   const int target = per_sm * num_sms();
   if (tiles >= target || tiles == 0) return 1;
   int splits = target / tiles;
