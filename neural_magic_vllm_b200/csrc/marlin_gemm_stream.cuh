@@ -12,19 +12,23 @@
 //   warp 0    TMA producer: per unit one activation tile [BM x 64] (128-byte swizzle), the packed
 //             weights (1 KiB rows of the Marlin tensor) and one group-scale row into a ring of
 //             ~20 stages (~210 KiB in flight per SM -- an epilogue never starves HBM)
-//   warp 1    MMA issuer: tcgen05.mma kind::f16, A = dequantised weights in TMEM, B = activations
-//             in shared memory, D = fp32 in TMEM, double-buffered per piece
+//   warps 1, 22  MMA issuers, one per 128-row sub-tile (each accumulator has ONE issuer: fixed
+//             summation order): tcgen05.mma kind::f16, A = dequantised weights in TMEM, B =
+//             activations in shared memory, D = fp32 in TMEM, double-buffered per piece
 //   warps 2-17  four dequant teams of four warps (one per TMEM quadrant).  A job is one 128 x 64
 //             sub-tile of a stage; jobs go round-robin to the teams, each team owns two 32-column
-//             A slots in TMEM, so four jobs are in flight while the MMA consumes in order.
-//             LDS.64 packed words -> lop3 / hsub2 / hfma2 exact (q - 8) -> x group scale (one
-//             rounding: bit-identical to the reference's w_ref) -> tcgen05.st straight to TMEM.
-//   warps 18-21 epilogue: tcgen05.ld the finished piece; a whole tile is rounded once and stored,
-//             a partial one goes to the fp32 workspace and bumps the tile's arrival counter.  After
-//             its last piece a CTA waits for the tiles it contributed to and sums ITS SLICE of each
-//             (fixed slot order: deterministic), so the split-K reduction is spread over all SMs
-//             and needs no second kernel.  The counters are the caller's `workspace` (zero on entry,
-//             zero on exit, as the reference requires: gptq_marlin.cu:329-332).
+//             A slots in TMEM, so four jobs are in flight while the MMAs consume in order.
+//             LDS.64 packed words (fetched one job ahead) -> lop3 / hsub2 / hfma2 exact (q - 8) ->
+//             x group scale (one rounding: bit-identical to the reference's w_ref) -> tcgen05.st
+//             16x128b.x8 straight to TMEM.
+//   warps 18-21 epilogue: tcgen05.ld the finished piece; a whole tile is rounded once and stored.
+//             A tile split over several CTAs is fixed up by the CTA that owns its lowest k range
+//             (that piece is the last of its range; the others' pieces come first in theirs):
+//             publishers store fp32 pieces to their slot and bump the tile's counter with one
+//             red.release.gpu; the fixer waits for parts - 1 arrivals, sums its own piece (from
+//             TMEM) and the slots in CTA order (deterministic), rounds once, stores.  The counters
+//             are the caller's `workspace` (zero on entry, zero on exit, as the reference
+//             requires: gptq_marlin.cu:329-332).
 // (no include guard / namespaces: this file is spliced into marlin_gemm.cu's b200::{anonymous})
 
 constexpr int kSNT = 2;                       // 128-row sub-tiles per n tile
