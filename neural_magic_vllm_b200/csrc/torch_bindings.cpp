@@ -10,6 +10,7 @@
 #include <ATen/ATen.h>
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
+#include <cstdlib>
 #include <torch/library.h>
 
 #include <optional>
@@ -161,6 +162,30 @@ void paged_attention_v1(Tensor& out, Tensor& query, Tensor& key_cache, Tensor& v
   fill_attention(p, out, query, key_cache, value_cache, num_kv_heads, scale, block_tables, seq_lens,
                  block_size, max_seq_len, alibi_slopes, kv_cache_dtype, kv_scale, tp_rank, bs_local,
                  bs_vert, bs_block, bs_step);
+  // v1 has no scratch in its signature, so one CTA per (kv head, sequence) walks the whole
+  // context.  When that grid is only a few CTAs per SM (one partial wave of long CTAs), the op is
+  // served by the partitioned kernel instead, with scratch from the torch caching allocator
+  // (stream-ordered, CUDA-graph safe): same arithmetic as paged_attention_v2 on the same inputs.
+  // Measured (decode step, ctx 1024): batch 64 4.24 -> 4.18 ms; at batch 256 (2048 CTAs) it loses
+  // (11.2 -> 11.8 ms), hence the bound of four CTAs per SM.  B200_ATTN_V1_SPLIT = 0 / 1 forces it.
+  const int64_t parts = (max_seq_len + B200_PARTITION_SIZE - 1) / B200_PARTITION_SIZE;
+  static const int split_knob = [] {
+    const char* e = std::getenv("B200_ATTN_V1_SPLIT");
+    return e ? std::atoi(e) : -1;
+  }();
+  const int64_t v1_ctas = (int64_t)num_kv_heads * query.size(0);
+  const bool split = split_knob >= 0 ? split_knob != 0 && parts > 1
+                                     : parts > 1 && v1_ctas <= 4 * 148 && query.scalar_type() != at::ScalarType::Float;
+  if (split) {
+    Tensor tmp_out = at::empty({query.size(0), query.size(1), parts, query.size(2)}, query.options());
+    Tensor exp_sums = at::empty({query.size(0), query.size(1), parts}, query.options().dtype(at::ScalarType::Float));
+    Tensor max_logits = at::empty_like(exp_sums);
+    p.exp_sums = exp_sums.data_ptr<float>();
+    p.max_logits = max_logits.data_ptr<float>();
+    p.tmp_out = tmp_out.data_ptr();
+    check_rc(b200_paged_attention_v2(&p, cur_stream()));
+    return;
+  }
   check_rc(b200_paged_attention_v1(&p, cur_stream()));
 }
 
