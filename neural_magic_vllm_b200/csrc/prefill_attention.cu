@@ -6,19 +6,21 @@
 // reads kv head h / (H / KVH).  Causal alignment is bottom-right (query i of a sequence with
 // q_len <= k_len sees keys <= i + k_len - q_len), as flash-attn does.
 //
-// One CTA = 128 queries of one head.  Both GEMMs run on tcgen05 with fp32 accumulators in TMEM:
+// One CTA = 256 queries of one head: two 128-row query tiles (A, B) that share every K / V tile and
+// ping-pong on the tensor pipe.  Both GEMMs run on tcgen05 with fp32 accumulators in TMEM:
 //   S = Q K^T   A = Q tile (shared memory, K-major, TMA 128B swizzle), B = K tile (same layout)
 //   O_t = P V   A = P (fp16/bf16, written by the softmax warps straight into TMEM, over the S
 //               columns it came from), B = V tile in its natural [key][d] layout = MN-major operand
 //               (descriptor: 64-d column blocks LBO apart, 8-key groups 1 KiB apart)
-//   warp 0      TMA producer: Q once, then K / V tiles of 128 keys through two-stage rings
-//   warp 1      MMA issuer (one elected lane): QK of tile j + 1 is issued before PV of tile j, so
-//               the tensor pipe works while the softmax warps are on tile j + 1
-//   warps 2-5   softmax, one thread per query row (TMEM lane = row: row max / sum need no
-//               shuffles): two passes over the S row in 32-column chunks (max, then exp2 + pack),
-//               running (m, l) in registers, and the output accumulator o = o * alpha + O_t in
-//               registers (128 fp32 per thread) -- no TMEM correction pass.
-// TMEM: S0, S1 (2 x 128 columns, P aliased inside) + O_t (128 columns) of a 512-column allocation.
+//   warp 0      TMA producer: both Q tiles once, then K / V tiles of 128 keys through two-stage rings
+//   warp 1      MMA issuer (one elected lane), per step j: P V of tile A, Q K^T of tile A for step
+//               j + 1, then the same for tile B -- the tensor pipe works for one tile while the
+//               other tile's softmax warps are busy
+//   warps 2-5 / 6-9  softmax of tile A / B, one thread per query row (TMEM lane = row: row max /
+//               sum need no shuffles): two passes over the S row (max, then exp2 + pack), running
+//               (m, l) in registers, and the output accumulator o = o * alpha + O_t in registers
+//               (128 fp32 per thread) -- no TMEM correction pass.
+// TMEM: S_A, S_B (2 x 128 columns, P aliased inside) + O_t of A and B (2 x 128) = 512 columns.
 #include "umma.cuh"
 
 namespace b200 {
@@ -28,7 +30,7 @@ using namespace umma;
 
 constexpr int kBQ = 128;   // queries per CTA
 constexpr int kBK = 128;   // keys per tile
-constexpr int kFaThreads = 6 * 32;
+constexpr int kFaThreads = 10 * 32;  // producer, MMA issuer, 2 x 4 softmax warps
 
 struct FaArgs {
   void* out;
@@ -44,7 +46,7 @@ template <int D>
 struct FaPlan {
   static constexpr int kTileBytes = kBQ * D * 2;  // one Q / K / V tile: D / 64 boxes of 128 x 128 B
   static constexpr int kBoxBytes = kBQ * 128;
-  static constexpr int kBytes = 5 * kTileBytes + 1024 + 256;  // Q + 2 K + 2 V
+  static constexpr int kBytes = 6 * kTileBytes + 1024 + 256;  // 2 Q + 2 K + 2 V
 };
 
 // MN-major operand tile (rows = k index, 128 bytes = 64 elements of the N dimension per row, 8-row
@@ -80,6 +82,11 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16
       "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
       : "memory");
 }
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(r[0]),
+               "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
 __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -95,31 +102,37 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
   constexpr int kBoxes = D / 64;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* q_s = smem;
-  uint8_t* k_s = q_s + P::kTileBytes;       // [2]
-  uint8_t* v_s = k_s + 2 * P::kTileBytes;   // [2]
+  uint8_t* q_s = smem;                      // [2] query tiles A, B
+  uint8_t* k_s = q_s + 2 * P::kTileBytes;   // [2] stages
+  uint8_t* v_s = k_s + 2 * P::kTileBytes;   // [2] stages
   uint64_t* bars = reinterpret_cast<uint64_t*>(v_s + 2 * P::kTileBytes);
   uint64_t* q_full = bars;
-  uint64_t* k_full = bars + 1;    // [2]
-  uint64_t* v_full = bars + 3;    // [2]
-  uint64_t* k_empty = bars + 5;   // [2]
-  uint64_t* v_empty = bars + 7;   // [2]
-  uint64_t* s_full = bars + 9;    // [2]
-  uint64_t* p_full = bars + 11;   // [2]
-  uint64_t* o_full = bars + 13;
-  uint64_t* o_empty = bars + 14;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+  uint64_t* k_full = bars + 1;    // [2] stage
+  uint64_t* v_full = bars + 3;    // [2] stage
+  uint64_t* k_empty = bars + 5;   // [2] stage
+  uint64_t* v_empty = bars + 7;   // [2] stage
+  uint64_t* s_full = bars + 9;    // [2] query tile
+  uint64_t* p_full = bars + 11;   // [2] query tile
+  uint64_t* o_full = bars + 13;   // [2] query tile
+  uint64_t* o_empty = bars + 15;  // [2] query tile
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int seq = blockIdx.y, head = blockIdx.z;
   const int q_begin = args.cu_q[seq], q_len = args.cu_q[seq + 1] - q_begin;
   const int k_begin = args.cu_k[seq], k_len = args.cu_k[seq + 1] - k_begin;
-  const int q0 = blockIdx.x * kBQ;  // first query of this tile inside the sequence
-  if (q0 >= q_len) return;          // uniform over the CTA: nothing allocated yet
-  const int shift = k_len - q_len;  // bottom-right causal alignment
-  // keys this tile can see: [0, k_end)
-  const int k_end = args.causal ? max(0, min(k_len, min(q0 + kBQ, q_len) + shift)) : k_len;
-  const int nt = (k_end + kBK - 1) / kBK;
+  const int q0 = blockIdx.x * (2 * kBQ);  // first query of tile A inside the sequence; tile B = q0 + 128
+  if (q0 >= q_len) return;                // uniform over the CTA: nothing allocated yet
+  const int shift = k_len - q_len;        // bottom-right causal alignment
+  // kv tiles each query tile walks: keys [0, k_end_t)
+  int nt[2];
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    const int qt = q0 + t * kBQ;
+    const int k_end = qt >= q_len ? 0 : (args.causal ? max(0, min(k_len, min(qt + kBQ, q_len) + shift)) : k_len);
+    nt[t] = (k_end + kBK - 1) / kBK;
+  }
+  const int ntmax = max(nt[0], nt[1]);
   const int kv_head = head / (args.num_heads / args.num_kv_heads);
 
   if (warp == 0 && lane == 0) {
@@ -134,9 +147,9 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       mbar_init(&v_empty[i], 1);
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 4);
+      mbar_init(&o_full[i], 1);
+      mbar_init(&o_empty[i], 4);
     }
-    mbar_init(o_full, 1);
-    mbar_init(o_empty, 4);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -144,7 +157,8 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
   __syncthreads();
   fence_after_sync();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
-  constexpr uint32_t kSCol = 0, kOCol = 256;  // S0 at 0, S1 at 128, O_t at 256
+  // TMEM columns: S of tile t (P aliased inside) at 128 t, O_t of tile t at 256 + 128 t
+  constexpr uint32_t kOCol = 256;
 
   if (warp == 0) {
     // ======================= TMA producer =======================
@@ -152,12 +166,15 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
     const uint64_t pol = l2_policy_evict_last();  // K / V are re-read by the other heads of the group
     pdl_wait();
     if (leader) {
-      mbar_arrive_expect_tx(q_full, P::kTileBytes);
+      mbar_arrive_expect_tx(q_full, 2 * P::kTileBytes);  // rows past the tensor end arrive as zeros
 #pragma unroll
-      for (int b = 0; b < kBoxes; ++b)
-        tma_load_2d(q_s + b * P::kBoxBytes, &tm_q, head * D + b * 64, q_begin + q0, q_full, pol);
+      for (int t = 0; t < 2; ++t)
+#pragma unroll
+        for (int b = 0; b < kBoxes; ++b)
+          tma_load_2d(q_s + t * P::kTileBytes + b * P::kBoxBytes, &tm_q, head * D + b * 64,
+                      q_begin + q0 + t * kBQ, q_full, pol);
     }
-    for (int j = 0; j < nt; ++j) {
+    for (int j = 0; j < ntmax; ++j) {
       const int st = j & 1;
       const uint32_t ph = ((j >> 1) & 1) ^ 1;
       mbar_wait_bounded(&k_empty[st], ph);
@@ -179,52 +196,70 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
     }
   } else if (warp == 1) {
     // ======================= MMA issuer =======================
+    // Ping-pong over the two query tiles: while the softmax warps of one tile work on S_t(j), the
+    // tensor pipe runs P V of the other tile's step j and its Q K^T of step j + 1.
     const bool leader = elect_one();
     constexpr uint32_t idesc_qk = instr_desc<KIND>(kBQ, kBK);             // S[128 q, 128 keys]
     constexpr uint32_t idesc_pv = instr_desc<KIND>(kBQ, D) | (1u << 16);  // O_t[128 q, D], B MN-major
-    auto issue_qk = [&](int j) {
+    auto issue_qk = [&](int t, int j) {
       const int st = j & 1;
       mbar_wait_bounded(&k_full[st], (j >> 1) & 1);
       fence_after_sync();
-      const uint32_t qa = smem_u32(q_s), ka = smem_u32(k_s + st * P::kTileBytes);
+      const uint32_t qa = smem_u32(q_s + t * P::kTileBytes), ka = smem_u32(k_s + st * P::kTileBytes);
       if (leader) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t off = (kk >> 2) * P::kBoxBytes + (kk & 3) * 32;
-          mma_ss<KIND>(tmem_base + kSCol + st * kBK, smem_desc_sw128(qa + off), smem_desc_sw128(ka + off), idesc_qk,
+          mma_ss<KIND>(tmem_base + t * kBK, smem_desc_sw128(qa + off), smem_desc_sw128(ka + off), idesc_qk,
                        kk > 0 ? 1u : 0u);
         }
-        mma_commit(&s_full[st]);
-        mma_commit(&k_empty[st]);
+        mma_commit(&s_full[t]);
       }
     };
-    mbar_wait_bounded(q_full, 0);
-    if (nt > 0) issue_qk(0);
-    for (int j = 0; j < nt; ++j) {
+    auto issue_pv = [&](int t, int j) {
       const int st = j & 1;
-      if (j + 1 < nt) issue_qk(j + 1);  // the tensor pipe works on S_{j+1} while tile j is in softmax
-      mbar_wait_bounded(&p_full[st], (j >> 1) & 1);
+      mbar_wait_bounded(&p_full[t], j & 1);
       mbar_wait_bounded(&v_full[st], (j >> 1) & 1);
-      mbar_wait_bounded(o_empty, (j & 1) ^ 1);
+      mbar_wait_bounded(&o_empty[t], (j & 1) ^ 1);
       fence_after_sync();
       const uint32_t va = smem_u32(v_s + st * P::kTileBytes);
       if (leader) {
 #pragma unroll
         for (int kk = 0; kk < kBK / 16; ++kk)  // 16 keys per MMA: 8 packed P columns, 16 V rows
-          mma_ts_f16(tmem_base + kOCol, tmem_base + kSCol + st * kBK + kk * 8,
+          mma_ts_f16(tmem_base + kOCol + t * D, tmem_base + t * kBK + kk * 8,
                      smem_desc_mn_sw128(va + kk * 2048, P::kBoxBytes), idesc_pv, kk > 0 ? 1u : 0u);
-        mma_commit(o_full);
-        mma_commit(&v_empty[st]);
+        mma_commit(&o_full[t]);
+      }
+    };
+    mbar_wait_bounded(q_full, 0);
+    // the key tile of step j is free once BOTH tiles' Q K^T of step j are issued (commit covers
+    // every MMA issued before it); likewise the value tile after both P V
+    for (int t = 0; t < 2; ++t)
+      if (nt[t] > 0) issue_qk(t, 0);
+    if (ntmax > 0 && leader) mma_commit(&k_empty[0]);
+    for (int j = 0; j < ntmax; ++j) {
+      for (int t = 0; t < 2; ++t) {
+        if (j < nt[t]) issue_pv(t, j);
+        if (j + 1 < nt[t]) issue_qk(t, j + 1);
+      }
+      if (leader) {
+        mma_commit(&v_empty[j & 1]);
+        if (j + 1 < ntmax) mma_commit(&k_empty[(j + 1) & 1]);
       }
     }
     pdl_launch_dependents();
   } else {
     // ======================= softmax + output accumulation (thread = query row) =======================
+    // warps 2-5 own query tile A, warps 6-9 tile B; a warp reaches the TMEM lanes of quadrant warp % 4
+    const int t = (warp - 2) >> 2;
     const int qd = warp & 3;
     const int row = qd * 32 + lane;           // TMEM lane
-    const int qi = q0 + row;                  // query index inside the sequence
+    const int qi = q0 + t * kBQ + row;        // query index inside the sequence
     const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16);
+    const uint32_t s_addr = t_lane + t * kBK;
+    const uint32_t o_addr = t_lane + kOCol + t * D;
     const float c = args.scale_log2;
+    const int my_nt = nt[t];
     // keys this row may see: [0, row_end)
     const int row_end = args.causal ? min(k_len, qi + shift + 1) : k_len;
     float m = -1e30f, l = 0.f;
@@ -232,26 +267,24 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
 #pragma unroll
     for (int i = 0; i < D; ++i) o_acc[i] = 0.f;
     float alpha_prev = 1.f;
-    auto accumulate = [&](int j, float alpha) {  // o = o * alpha + O_t of tile j
-      mbar_wait_bounded(o_full, j & 1);
+    auto accumulate = [&](int j, float alpha) {  // o = o * alpha + O_t of step j
+      mbar_wait_bounded(&o_full[t], j & 1);
       fence_after_sync();
 #pragma unroll
-      for (int cc = 0; cc < D / 32; ++cc) {
-        uint32_t r[32];
-        tmem_ld32(t_lane + kOCol + cc * 32, r);
+      for (int cc = 0; cc < D / 16; ++cc) {
+        uint32_t r[16];
+        tmem_ld16(o_addr + cc * 16, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o_acc[cc * 32 + i] = fmaf(o_acc[cc * 32 + i], alpha, __uint_as_float(r[i]));
+        for (int i = 0; i < 16; ++i) o_acc[cc * 16 + i] = fmaf(o_acc[cc * 16 + i], alpha, __uint_as_float(r[i]));
       }
       fence_before_sync();
       __syncwarp();
-      if (lane == 0) mbar_arrive(o_empty);
+      if (lane == 0) mbar_arrive(&o_empty[t]);
     };
-    for (int j = 0; j < nt; ++j) {
-      const int st = j & 1;
-      const uint32_t s_addr = t_lane + kSCol + st * kBK;
+    for (int j = 0; j < my_nt; ++j) {
       const int lim = row_end - j * kBK;  // columns < lim are visible to this row
-      mbar_wait_bounded(&s_full[st], (j >> 1) & 1);
+      mbar_wait_bounded(&s_full[t], j & 1);
       fence_after_sync();
       // pass 1: row maximum
       float mx = -1e30f;
@@ -275,33 +308,33 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       // pass 2: p = exp2(s c - m c), row sum, packed 16-bit P over the S columns already consumed
       float sum = 0.f;
 #pragma unroll 1
-      for (int cc = 0; cc < kBK / 32; ++cc) {
-        uint32_t r[32];
-        tmem_ld32(s_addr + cc * 32, r);
+      for (int cc = 0; cc < kBK / 16; ++cc) {
+        uint32_t r[16];
+        tmem_ld16(s_addr + cc * 16, r);
         tmem_ld_wait();
-        uint32_t pk[16];
+        uint32_t pk[8];
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
+        for (int i = 0; i < 16; i += 2) {
           float p0 = ex2(fmaf(__uint_as_float(r[i]), c, -mc));
           float p1 = ex2(fmaf(__uint_as_float(r[i + 1]), c, -mc));
-          if (cc * 32 + i >= lim) p0 = 0.f;
-          if (cc * 32 + i + 1 >= lim) p1 = 0.f;
+          if (cc * 16 + i >= lim) p0 = 0.f;
+          if (cc * 16 + i + 1 >= lim) p1 = 0.f;
           sum += p0 + p1;
           pk[i >> 1] = DT<T>::pack2(p0, p1);
         }
-        tmem_st16(s_addr + cc * 16, pk);
+        tmem_st8(s_addr + cc * 8, pk);
       }
       l = fmaf(l, alpha, sum);
       m = m_new;
       tmem_st_wait();
       fence_before_sync();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&p_full[st]);
-      // the previous tile's P V finished while this tile was in softmax
+      if (lane == 0) mbar_arrive(&p_full[t]);
+      // the previous step's P V finished while this step was in softmax
       if (j > 0) accumulate(j - 1, alpha_prev);
       alpha_prev = alpha;
     }
-    if (nt > 0) accumulate(nt - 1, alpha_prev);
+    if (my_nt > 0) accumulate(my_nt - 1, alpha_prev);
     // o / l -> out[token][head][:]
     if (qi < q_len) {
       const float inv = l > 0.f ? 1.f / l : 0.f;
@@ -354,7 +387,7 @@ int launch_fa(const b200_varlen_attention_params& p, cudaStream_t st) {
     set_error("varlen_attention_fwd: cannot reserve %d B of shared memory", (int)P::kBytes);
     return B200_ECUDA;
   }
-  const int q_tiles = (p.max_seqlen_q + kBQ - 1) / kBQ;
+  const int q_tiles = (p.max_seqlen_q + 2 * kBQ - 1) / (2 * kBQ);  // a CTA owns two query tiles
   cudaError_t le = launch_pdl(kern, dim3(q_tiles, p.num_seqs, p.num_heads), dim3(kFaThreads), (size_t)P::kBytes, st,
                               tm_q, tm_k, tm_v, a);
   if (le != cudaSuccess) {
