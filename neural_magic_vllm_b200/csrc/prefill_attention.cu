@@ -94,7 +94,7 @@ __device__ __forceinline__ float ex2(float x) {
 }
 
 template <typename T, int D>
-__global__ void __launch_bounds__(kFaThreads, 1)
+__global__ void __maxnreg__(200)
 varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                         const __grid_constant__ CUtensorMap tm_v, const FaArgs args) {
   using P = FaPlan<D>;
@@ -270,13 +270,16 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
     auto accumulate = [&](int j, float alpha) {  // o = o * alpha + O_t of step j
       mbar_wait_bounded(&o_full[t], j & 1);
       fence_after_sync();
+      uint32_t ra[16], rb[16];
+      tmem_ld16(o_addr, ra);
 #pragma unroll
       for (int cc = 0; cc < D / 16; ++cc) {
-        uint32_t r[16];
-        tmem_ld16(o_addr + cc * 16, r);
+        uint32_t (&cur)[16] = (cc & 1) ? rb : ra;
+        uint32_t (&nxt)[16] = (cc & 1) ? ra : rb;
         tmem_ld_wait();
+        if (cc + 1 < D / 16) tmem_ld16(o_addr + (cc + 1) * 16, nxt);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) o_acc[cc * 16 + i] = fmaf(o_acc[cc * 16 + i], alpha, __uint_as_float(r[i]));
+        for (int i = 0; i < 16; ++i) o_acc[cc * 16 + i] = fmaf(o_acc[cc * 16 + i], alpha, __uint_as_float(cur[i]));
       }
       fence_before_sync();
       __syncwarp();
@@ -286,20 +289,25 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       const int lim = row_end - j * kBK;  // columns < lim are visible to this row
       mbar_wait_bounded(&s_full[t], j & 1);
       fence_after_sync();
-      // pass 1: row maximum
+      // pass 1: row maximum (the next chunk's tcgen05.ld is in flight while this one is reduced)
       float mx = -1e30f;
-#pragma unroll 1
-      for (int cc = 0; cc < kBK / 32; ++cc) {
-        uint32_t r[32];
-        tmem_ld32(s_addr + cc * 32, r);
-        tmem_ld_wait();
-        if (lim >= (cc + 1) * 32) {
+      {
+        uint32_t ra[32], rb[32];
+        tmem_ld32(s_addr, ra);
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
-        } else {
+        for (int cc = 0; cc < kBK / 32; ++cc) {
+          uint32_t (&cur)[32] = (cc & 1) ? rb : ra;
+          uint32_t (&nxt)[32] = (cc & 1) ? ra : rb;
+          tmem_ld_wait();
+          if (cc + 1 < kBK / 32) tmem_ld32(s_addr + (cc + 1) * 32, nxt);
+          if (lim >= (cc + 1) * 32) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (cc * 32 + i < lim) mx = fmaxf(mx, __uint_as_float(r[i]));
+            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(cur[i]));
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (cc * 32 + i < lim) mx = fmaxf(mx, __uint_as_float(cur[i]));
+          }
         }
       }
       const float m_new = fmaxf(m, mx);
@@ -307,22 +315,30 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       const float mc = m_new * c;
       // pass 2: p = exp2(s c - m c), row sum, packed 16-bit P over the S columns already consumed
       float sum = 0.f;
-#pragma unroll 1
-      for (int cc = 0; cc < kBK / 16; ++cc) {
-        uint32_t r[16];
-        tmem_ld16(s_addr + cc * 16, r);
-        tmem_ld_wait();
-        uint32_t pk[8];
+      {
+        uint32_t ra[16], rb[16];
+        tmem_ld16(s_addr, ra);
+        const bool full = lim >= kBK;  // no masked column in this tile (all but the diagonal / tail tiles)
 #pragma unroll
-        for (int i = 0; i < 16; i += 2) {
-          float p0 = ex2(fmaf(__uint_as_float(r[i]), c, -mc));
-          float p1 = ex2(fmaf(__uint_as_float(r[i + 1]), c, -mc));
-          if (cc * 16 + i >= lim) p0 = 0.f;
-          if (cc * 16 + i + 1 >= lim) p1 = 0.f;
-          sum += p0 + p1;
-          pk[i >> 1] = DT<T>::pack2(p0, p1);
+        for (int cc = 0; cc < kBK / 16; ++cc) {
+          uint32_t (&cur)[16] = (cc & 1) ? rb : ra;
+          uint32_t (&nxt)[16] = (cc & 1) ? ra : rb;
+          tmem_ld_wait();
+          if (cc + 1 < kBK / 16) tmem_ld16(s_addr + (cc + 1) * 16, nxt);
+          uint32_t pk[8];
+#pragma unroll
+          for (int i = 0; i < 16; i += 2) {
+            float p0 = ex2(fmaf(__uint_as_float(cur[i]), c, -mc));
+            float p1 = ex2(fmaf(__uint_as_float(cur[i + 1]), c, -mc));
+            if (!full) {
+              if (cc * 16 + i >= lim) p0 = 0.f;
+              if (cc * 16 + i + 1 >= lim) p1 = 0.f;
+            }
+            sum += p0 + p1;
+            pk[i >> 1] = DT<T>::pack2(p0, p1);
+          }
+          tmem_st8(s_addr + cc * 8, pk);
         }
-        tmem_st8(s_addr + cc * 8, pk);
       }
       l = fmaf(l, alpha, sum);
       m = m_new;
