@@ -87,6 +87,25 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8])
                "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
                : "memory");
 }
+// tcgen05.wait::ld that also names the destination registers of the load it waits for: with the
+// next chunk's load already in flight, nothing but a data dependency keeps the compiler from
+// scheduling a consumer of these registers above the wait
+__device__ __forceinline__ void tmem_ld_wait_on(uint32_t (&r)[16]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                 "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+               :
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait_on(uint32_t (&r)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                 "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                 "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]),
+                 "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+               :
+               : "memory");
+}
 __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -94,7 +113,8 @@ __device__ __forceinline__ float ex2(float x) {
 }
 
 template <typename T, int D>
-__global__ void __maxnreg__(200)
+// (10 warps are allocated as 12: 168 registers per thread is the ceiling for this block size)
+__global__ void __launch_bounds__(kFaThreads, 1)
 varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                         const __grid_constant__ CUtensorMap tm_v, const FaArgs args) {
   using P = FaPlan<D>;
@@ -121,7 +141,9 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
   const int seq = blockIdx.y, head = blockIdx.z;
   const int q_begin = args.cu_q[seq], q_len = args.cu_q[seq + 1] - q_begin;
   const int k_begin = args.cu_k[seq], k_len = args.cu_k[seq + 1] - k_begin;
-  const int q0 = blockIdx.x * (2 * kBQ);  // first query of tile A inside the sequence; tile B = q0 + 128
+  // first query of tile A inside the sequence (tile B = q0 + 128).  Causal work grows with q0, and
+  // CTAs are dispatched in blockIdx order: the longest tiles go first (longest-processing-time order)
+  const int q0 = (int)(gridDim.x - 1 - blockIdx.x) * (2 * kBQ);
   if (q0 >= q_len) return;                // uniform over the CTA: nothing allocated yet
   const int shift = k_len - q_len;        // bottom-right causal alignment
   // kv tiles each query tile walks: keys [0, k_end_t)
@@ -276,7 +298,7 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       for (int cc = 0; cc < D / 16; ++cc) {
         uint32_t (&cur)[16] = (cc & 1) ? rb : ra;
         uint32_t (&nxt)[16] = (cc & 1) ? ra : rb;
-        tmem_ld_wait();
+        tmem_ld_wait_on(cur);
         if (cc + 1 < D / 16) tmem_ld16(o_addr + (cc + 1) * 16, nxt);
 #pragma unroll
         for (int i = 0; i < 16; ++i) o_acc[cc * 16 + i] = fmaf(o_acc[cc * 16 + i], alpha, __uint_as_float(cur[i]));
@@ -292,21 +314,21 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       // pass 1: row maximum (the next chunk's tcgen05.ld is in flight while this one is reduced)
       float mx = -1e30f;
       {
-        uint32_t ra[32], rb[32];
-        tmem_ld32(s_addr, ra);
+        uint32_t ra[16], rb[16];
+        tmem_ld16(s_addr, ra);
 #pragma unroll
-        for (int cc = 0; cc < kBK / 32; ++cc) {
-          uint32_t (&cur)[32] = (cc & 1) ? rb : ra;
-          uint32_t (&nxt)[32] = (cc & 1) ? ra : rb;
-          tmem_ld_wait();
-          if (cc + 1 < kBK / 32) tmem_ld32(s_addr + (cc + 1) * 32, nxt);
-          if (lim >= (cc + 1) * 32) {
+        for (int cc = 0; cc < kBK / 16; ++cc) {
+          uint32_t (&cur)[16] = (cc & 1) ? rb : ra;
+          uint32_t (&nxt)[16] = (cc & 1) ? ra : rb;
+          tmem_ld_wait_on(cur);
+          if (cc + 1 < kBK / 16) tmem_ld16(s_addr + (cc + 1) * 16, nxt);
+          if (lim >= (cc + 1) * 16) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(cur[i]));
+            for (int i = 0; i < 16; ++i) mx = fmaxf(mx, __uint_as_float(cur[i]));
           } else {
 #pragma unroll
-            for (int i = 0; i < 32; ++i)
-              if (cc * 32 + i < lim) mx = fmaxf(mx, __uint_as_float(cur[i]));
+            for (int i = 0; i < 16; ++i)
+              if (cc * 16 + i < lim) mx = fmaxf(mx, __uint_as_float(cur[i]));
           }
         }
       }
@@ -323,7 +345,7 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
         for (int cc = 0; cc < kBK / 16; ++cc) {
           uint32_t (&cur)[16] = (cc & 1) ? rb : ra;
           uint32_t (&nxt)[16] = (cc & 1) ? ra : rb;
-          tmem_ld_wait();
+          tmem_ld_wait_on(cur);
           if (cc + 1 < kBK / 16) tmem_ld16(s_addr + (cc + 1) * 16, nxt);
           uint32_t pk[8];
 #pragma unroll
