@@ -9,7 +9,7 @@
 // One CTA = 256 queries of one head: two 128-row query tiles (A, B) that share every K / V tile and
 // ping-pong on the tensor pipe.  Both GEMMs run on tcgen05 with fp32 accumulators in TMEM:
 //   S = Q K^T   A = Q tile (shared memory, K-major, TMA 128B swizzle), B = K tile (same layout)
-//   O_t = P V   A = P (fp16/bf16, written by the softmax warps straight into TMEM, over the S
+//   O += P V    A = P (fp16/bf16, written by the softmax warps straight into TMEM, over the S
 //               columns it came from), B = V tile in its natural [key][d] layout = MN-major operand
 //               (descriptor: 64-d column blocks LBO apart, 8-key groups 1 KiB apart)
 //   warp 0      TMA producer: both Q tiles once, then K / V tiles of 128 keys through two-stage rings
@@ -17,10 +17,11 @@
 //               j + 1, then the same for tile B -- the tensor pipe works for one tile while the
 //               other tile's softmax warps are busy
 //   warps 2-5 / 6-9  softmax of tile A / B, one thread per query row (TMEM lane = row: row max /
-//               sum need no shuffles): two passes over the S row (max, then exp2 + pack), running
-//               (m, l) in registers, and the output accumulator o = o * alpha + O_t in registers
-//               (128 fp32 per thread) -- no TMEM correction pass.
-// TMEM: S_A, S_B (2 x 128 columns, P aliased inside) + O_t of A and B (2 x 128) = 512 columns.
+//               sum need no shuffles): the S row is read once into registers (max, then exp2 +
+//               pack into P).  O accumulates in TMEM over the kv tiles; it is rescaled -- by these
+//               same warps, between two P V of their tile -- only when a row maximum has grown
+//               by more than 2^8 (lazy rescale), which after the first tiles is rare.
+// TMEM: S_A, S_B (2 x 128 columns, P aliased inside) + O of A and B (2 x 128) = 512 columns.
 #include "umma.cuh"
 
 namespace b200 {
@@ -134,8 +135,7 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
   uint64_t* s_full = bars + 9;    // [2] query tile
   uint64_t* p_full = bars + 11;   // [2] query tile
   uint64_t* o_full = bars + 13;   // [2] query tile
-  uint64_t* o_empty = bars + 15;  // [2] query tile
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int seq = blockIdx.y, head = blockIdx.z;
@@ -170,7 +170,6 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 4);
       mbar_init(&o_full[i], 1);
-      mbar_init(&o_empty[i], 4);
     }
     fence_mbar_init();
   }
@@ -240,17 +239,16 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
     };
     auto issue_pv = [&](int t, int j) {
       const int st = j & 1;
-      mbar_wait_bounded(&p_full[t], j & 1);
+      mbar_wait_bounded(&p_full[t], j & 1);  // P of step j stored (and O rescaled, when the row maxima moved)
       mbar_wait_bounded(&v_full[st], (j >> 1) & 1);
-      mbar_wait_bounded(&o_empty[t], (j & 1) ^ 1);
       fence_after_sync();
       const uint32_t va = smem_u32(v_s + st * P::kTileBytes);
       if (leader) {
 #pragma unroll
         for (int kk = 0; kk < kBK / 16; ++kk)  // 16 keys per MMA: 8 packed P columns, 16 V rows
           mma_ts_f16(tmem_base + kOCol + t * D, tmem_base + t * kBK + kk * 8,
-                     smem_desc_mn_sw128(va + kk * 2048, P::kBoxBytes), idesc_pv, kk > 0 ? 1u : 0u);
-        mma_commit(&o_full[t]);
+                     smem_desc_mn_sw128(va + kk * 2048, P::kBoxBytes), idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+        if (j + 1 == nt[t]) mma_commit(&o_full[t]);
       }
     };
     mbar_wait_bounded(q_full, 0);
@@ -284,14 +282,88 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
     const int my_nt = nt[t];
     // keys this row may see: [0, row_end)
     const int row_end = args.causal ? min(k_len, qi + shift + 1) : k_len;
-    float m = -1e30f, l = 0.f;
-    float o_acc[D];
-#pragma unroll
-    for (int i = 0; i < D; ++i) o_acc[i] = 0.f;
-    float alpha_prev = 1.f;
-    auto accumulate = [&](int j, float alpha) {  // o = o * alpha + O_t of step j
-      mbar_wait_bounded(&o_full[t], j & 1);
+    // O accumulates in TMEM across the kv tiles (P V with the accumulate flag).  The exponent
+    // reference m_ref follows the running row maximum lazily: it moves only when the maximum has
+    // grown by more than 2^8 in the exp2 domain, and only then is O (and l) rescaled -- p stays
+    // <= 256, exact enough for fp16 / bf16 P and fp32 sums, and o / l is the same quotient.
+    // S_t(j) arriving implies P V of step j - 1 has finished (the tensor pipe runs in issue order and
+    // the commit covers everything issued before it), so O may be touched right after s_full.
+    float m_ref = -1e30f, l = 0.f;
+    for (int j = 0; j < my_nt; ++j) {
+      const int lim = row_end - j * kBK;  // columns < lim are visible to this row
+      const bool full = lim >= kBK;       // no masked column in this tile (all but the diagonal / tail tiles)
+      mbar_wait_bounded(&s_full[t], j & 1);
       fence_after_sync();
+      // the S row in registers (one TMEM read), the next chunk's tcgen05.ld in flight during the max
+      uint32_t sr[4][32];
+      float mx0 = -1e30f, mx1 = -1e30f;
+      tmem_ld32(s_addr, sr[0]);
+#pragma unroll
+      for (int cc = 0; cc < 4; ++cc) {
+        tmem_ld_wait_on(sr[cc]);
+        if (cc + 1 < 4) tmem_ld32(s_addr + (cc + 1) * 32, sr[cc + 1]);
+        if (full) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            mx0 = fmaxf(mx0, __uint_as_float(sr[cc][i]));
+            mx1 = fmaxf(mx1, __uint_as_float(sr[cc][i + 1]));
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (cc * 32 + i < lim) mx0 = fmaxf(mx0, __uint_as_float(sr[cc][i]));
+        }
+      }
+      const float m_new = fmaxf(m_ref, fmaxf(mx0, mx1));
+      const bool moved = (m_new - m_ref) * c > 8.f;
+      if (__any_sync(0xffffffffu, moved)) {
+        const float alpha = moved ? ex2((m_ref - m_new) * c) : 1.f;
+        if (moved) m_ref = m_new;
+        l *= alpha;
+        if (j > 0) {  // at j = 0 the first P V overwrites O
+#pragma unroll 1
+          for (int cc = 0; cc < D / 16; ++cc) {
+            uint32_t r[16];
+            tmem_ld16(o_addr + cc * 16, r);
+            tmem_ld_wait_on(r);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+            tmem_st16(o_addr + cc * 16, r);
+          }
+        }
+      }
+      const float mc = m_ref * c;
+      // p = exp2(s c - m_ref c), row sum, packed 16-bit P over the S columns
+      float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+      for (int cc = 0; cc < 4; ++cc) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float p0 = ex2(fmaf(__uint_as_float(sr[cc][i]), c, -mc));
+          float p1 = ex2(fmaf(__uint_as_float(sr[cc][i + 1]), c, -mc));
+          if (!full) {
+            if (cc * 32 + i >= lim) p0 = 0.f;
+            if (cc * 32 + i + 1 >= lim) p1 = 0.f;
+          }
+          sum0 += p0;
+          sum1 += p1;
+          pk[i >> 1] = DT<T>::pack2(p0, p1);
+        }
+        tmem_st16(s_addr + cc * 16, pk);
+      }
+      l += sum0 + sum1;
+      tmem_st_wait();
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[t]);
+    }
+    // o / l -> out[token][head][:]
+    if (my_nt > 0) {
+      mbar_wait_bounded(&o_full[t], 0);
+      fence_after_sync();
+      const float inv = l > 0.f ? 1.f / l : 0.f;
+      T* dst = reinterpret_cast<T*>(args.out) + (int64_t)(q_begin + qi) * args.out_stride + (int64_t)head * D;
       uint32_t ra[16], rb[16];
       tmem_ld16(o_addr, ra);
 #pragma unroll
@@ -300,92 +372,22 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
         uint32_t (&nxt)[16] = (cc & 1) ? ra : rb;
         tmem_ld_wait_on(cur);
         if (cc + 1 < D / 16) tmem_ld16(o_addr + (cc + 1) * 16, nxt);
+        if (qi < q_len) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) o_acc[cc * 16 + i] = fmaf(o_acc[cc * 16 + i], alpha, __uint_as_float(cur[i]));
-      }
-      fence_before_sync();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&o_empty[t]);
-    };
-    for (int j = 0; j < my_nt; ++j) {
-      const int lim = row_end - j * kBK;  // columns < lim are visible to this row
-      mbar_wait_bounded(&s_full[t], j & 1);
-      fence_after_sync();
-      // pass 1: row maximum (the next chunk's tcgen05.ld is in flight while this one is reduced)
-      float mx = -1e30f;
-      {
-        uint32_t ra[16], rb[16];
-        tmem_ld16(s_addr, ra);
-#pragma unroll
-        for (int cc = 0; cc < kBK / 16; ++cc) {
-          uint32_t (&cur)[16] = (cc & 1) ? rb : ra;
-          uint32_t (&nxt)[16] = (cc & 1) ? ra : rb;
-          tmem_ld_wait_on(cur);
-          if (cc + 1 < kBK / 16) tmem_ld16(s_addr + (cc + 1) * 16, nxt);
-          if (lim >= (cc + 1) * 16) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) mx = fmaxf(mx, __uint_as_float(cur[i]));
-          } else {
-#pragma unroll
-            for (int i = 0; i < 16; ++i)
-              if (cc * 16 + i < lim) mx = fmaxf(mx, __uint_as_float(cur[i]));
+          for (int i = 0; i < 16; i += 8) {
+            uint4 v;
+            v.x = DT<T>::pack2(__uint_as_float(cur[i]) * inv, __uint_as_float(cur[i + 1]) * inv);
+            v.y = DT<T>::pack2(__uint_as_float(cur[i + 2]) * inv, __uint_as_float(cur[i + 3]) * inv);
+            v.z = DT<T>::pack2(__uint_as_float(cur[i + 4]) * inv, __uint_as_float(cur[i + 5]) * inv);
+            v.w = DT<T>::pack2(__uint_as_float(cur[i + 6]) * inv, __uint_as_float(cur[i + 7]) * inv);
+            *reinterpret_cast<uint4*>(dst + cc * 16 + i) = v;
           }
         }
       }
-      const float m_new = fmaxf(m, mx);
-      const float alpha = ex2((m - m_new) * c);
-      const float mc = m_new * c;
-      // pass 2: p = exp2(s c - m c), row sum, packed 16-bit P over the S columns already consumed
-      float sum = 0.f;
-      {
-        uint32_t ra[16], rb[16];
-        tmem_ld16(s_addr, ra);
-        const bool full = lim >= kBK;  // no masked column in this tile (all but the diagonal / tail tiles)
-#pragma unroll
-        for (int cc = 0; cc < kBK / 16; ++cc) {
-          uint32_t (&cur)[16] = (cc & 1) ? rb : ra;
-          uint32_t (&nxt)[16] = (cc & 1) ? ra : rb;
-          tmem_ld_wait_on(cur);
-          if (cc + 1 < kBK / 16) tmem_ld16(s_addr + (cc + 1) * 16, nxt);
-          uint32_t pk[8];
-#pragma unroll
-          for (int i = 0; i < 16; i += 2) {
-            float p0 = ex2(fmaf(__uint_as_float(cur[i]), c, -mc));
-            float p1 = ex2(fmaf(__uint_as_float(cur[i + 1]), c, -mc));
-            if (!full) {
-              if (cc * 16 + i >= lim) p0 = 0.f;
-              if (cc * 16 + i + 1 >= lim) p1 = 0.f;
-            }
-            sum += p0 + p1;
-            pk[i >> 1] = DT<T>::pack2(p0, p1);
-          }
-          tmem_st8(s_addr + cc * 8, pk);
-        }
-      }
-      l = fmaf(l, alpha, sum);
-      m = m_new;
-      tmem_st_wait();
-      fence_before_sync();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&p_full[t]);
-      // the previous step's P V finished while this step was in softmax
-      if (j > 0) accumulate(j - 1, alpha_prev);
-      alpha_prev = alpha;
-    }
-    if (my_nt > 0) accumulate(my_nt - 1, alpha_prev);
-    // o / l -> out[token][head][:]
-    if (qi < q_len) {
-      const float inv = l > 0.f ? 1.f / l : 0.f;
+    } else if (qi < q_len) {  // a query row that sees no key: zeros
       T* dst = reinterpret_cast<T*>(args.out) + (int64_t)(q_begin + qi) * args.out_stride + (int64_t)head * D;
 #pragma unroll
-      for (int i = 0; i < D; i += 8) {
-        uint4 v;
-        v.x = DT<T>::pack2(o_acc[i] * inv, o_acc[i + 1] * inv);
-        v.y = DT<T>::pack2(o_acc[i + 2] * inv, o_acc[i + 3] * inv);
-        v.z = DT<T>::pack2(o_acc[i + 4] * inv, o_acc[i + 5] * inv);
-        v.w = DT<T>::pack2(o_acc[i + 6] * inv, o_acc[i + 7] * inv);
-        *reinterpret_cast<uint4*>(dst + i) = v;
-      }
+      for (int i = 0; i < D; i += 8) *reinterpret_cast<uint4*>(dst + i) = make_uint4(0, 0, 0, 0);
     }
   }
   __syncthreads();
