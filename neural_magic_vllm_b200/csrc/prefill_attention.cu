@@ -107,6 +107,21 @@ __device__ __forceinline__ void tmem_ld_wait_on(uint32_t (&r)[32]) {
                :
                : "memory");
 }
+// packed fp32 pairs (FFMA2 / FADD2): one issue slot for two elements
+__device__ __forceinline__ void fma2(float& d0, float& d1, float a0, float a1, float b, float c) {
+  asm("{\n.reg .b64 ra, rb, rc, rd;\n"
+      "mov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %4};\nmov.b64 rc, {%5, %5};\n"
+      "fma.rn.ftz.f32x2 rd, ra, rb, rc;\nmov.b64 {%0, %1}, rd;\n}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b), "f"(c));
+}
+__device__ __forceinline__ void add2(float& d0, float& d1, float a0, float a1) {  // (d0, d1) += (a0, a1)
+  asm("{\n.reg .b64 ra, rd;\n"
+      "mov.b64 ra, {%2, %3};\nmov.b64 rd, {%0, %1};\n"
+      "add.rn.ftz.f32x2 rd, rd, ra;\nmov.b64 {%0, %1}, rd;\n}"
+      : "+f"(d0), "+f"(d1)
+      : "f"(a0), "f"(a1));
+}
 __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -291,7 +306,9 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
     float m_ref = -1e30f, l = 0.f;
     for (int j = 0; j < my_nt; ++j) {
       const int lim = row_end - j * kBK;  // columns < lim are visible to this row
-      const bool full = lim >= kBK;       // no masked column in this tile (all but the diagonal / tail tiles)
+      // no masked column in this tile for any row of the warp (all but the diagonal / tail tiles);
+      // warp-uniform, because the TMEM loads / stores below are warp-collective
+      const bool warp_full = __all_sync(0xffffffffu, lim >= kBK);
       mbar_wait_bounded(&s_full[t], j & 1);
       fence_after_sync();
       // the S row in registers (one TMEM read), the next chunk's tcgen05.ld in flight during the max
@@ -302,7 +319,7 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       for (int cc = 0; cc < 4; ++cc) {
         tmem_ld_wait_on(sr[cc]);
         if (cc + 1 < 4) tmem_ld32(s_addr + (cc + 1) * 32, sr[cc + 1]);
-        if (full) {
+        if (warp_full) {
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
             mx0 = fmaxf(mx0, __uint_as_float(sr[cc][i]));
@@ -335,22 +352,36 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       const float mc = m_ref * c;
       // p = exp2(s c - m_ref c), row sum, packed 16-bit P over the S columns
       float sum0 = 0.f, sum1 = 0.f;
+      if (warp_full) {
 #pragma unroll
-      for (int cc = 0; cc < 4; ++cc) {
-        uint32_t pk[16];
+        for (int cc = 0; cc < 4; ++cc) {
+          uint32_t pk[16];
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float p0 = ex2(fmaf(__uint_as_float(sr[cc][i]), c, -mc));
-          float p1 = ex2(fmaf(__uint_as_float(sr[cc][i + 1]), c, -mc));
-          if (!full) {
+          for (int i = 0; i < 32; i += 2) {
+            float x0, x1;
+            fma2(x0, x1, __uint_as_float(sr[cc][i]), __uint_as_float(sr[cc][i + 1]), c, -mc);
+            const float p0 = ex2(x0), p1 = ex2(x1);
+            add2(sum0, sum1, p0, p1);
+            pk[i >> 1] = DT<T>::pack2(p0, p1);
+          }
+          tmem_st16(s_addr + cc * 16, pk);
+        }
+      } else {
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            float p0 = ex2(fmaf(__uint_as_float(sr[cc][i]), c, -mc));
+            float p1 = ex2(fmaf(__uint_as_float(sr[cc][i + 1]), c, -mc));
             if (cc * 32 + i >= lim) p0 = 0.f;
             if (cc * 32 + i + 1 >= lim) p1 = 0.f;
+            sum0 += p0;
+            sum1 += p1;
+            pk[i >> 1] = DT<T>::pack2(p0, p1);
           }
-          sum0 += p0;
-          sum1 += p1;
-          pk[i >> 1] = DT<T>::pack2(p0, p1);
+          tmem_st16(s_addr + cc * 16, pk);
         }
-        tmem_st16(s_addr + cc * 16, pk);
       }
       l += sum0 + sum1;
       tmem_st_wait();
