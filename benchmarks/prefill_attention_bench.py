@@ -42,6 +42,7 @@ def timeit(fn, iters):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=30)
+    ap.add_argument("--shape", default=None, help="BATCHxSEQLEN: only this shape, only our kernel (for ncu)")
     args = ap.parse_args()
     import neural_magic_vllm_b200 as pkg
     ops = pkg.ops
@@ -50,8 +51,12 @@ def main():
         from flash_attn import flash_attn_varlen_func as fa_lib
     except Exception:
         fa_lib = None
-    for dtype in (torch.half, torch.bfloat16):
-        for batch, seqlen in ((1, 2048), (8, 2048), (1, 8192), (4, 512)):
+    shapes = ((1, 2048), (8, 2048), (1, 8192), (4, 512))
+    if args.shape:
+        shapes = (tuple(int(x) for x in args.shape.split("x")),)
+        fa_lib = None
+    for dtype in (torch.half, torch.bfloat16) if not args.shape else (torch.bfloat16,):
+        for batch, seqlen in shapes:
             t = batch * seqlen
             q = torch.randn(t, H, D, dtype=dtype, device="cuda")
             k = torch.randn(t, KVH, D, dtype=dtype, device="cuda")
@@ -63,6 +68,9 @@ def main():
             r = {"op": "varlen_attention_fwd", "dtype": str(dtype).split(".")[-1], "batch": batch, "seqlen": seqlen,
                  "heads": H, "kv_heads": KVH, "head_size": D, "causal": True, "us": ours * 1e6,
                  "TFLOPs": flops / ours / 1e12, "tensor_frac": flops / ours / 1e12 / peak}
+            if args.shape:
+                print(json.dumps(r), flush=True)
+                continue
             q4 = q.view(batch, seqlen, H, D).transpose(1, 2)
             k4 = k.view(batch, seqlen, KVH, D).transpose(1, 2)
             v4 = v.view(batch, seqlen, KVH, D).transpose(1, 2)

@@ -259,6 +259,9 @@ B200_API void b200_debug_set_marlin_decode_kernel(int32_t choice);
 /* debug only: cycle accounting of the stream-K decode kernel; returns the number of uint64 copied
  * (0 unless built with -DB200_STREAM_PROF) */
 B200_API int b200_debug_stream_prof(unsigned long long* dst, int32_t n);
+/* debug only: cycle totals of the prefill attention kernel's MMA issuer [0..7] and of one softmax
+ * warp of query tile A [8..15] / B [16..23]; 0 unless built with -DB200_FA_PROF */
+B200_API int b200_debug_fa_prof(unsigned long long* dst, int32_t n, int32_t reset);
 
 /* fp8_marlin_gemm (csrc/quantization/fp8/fp8_marlin.cu:1212-1308): fp8 e4m3 weights repacked with
  * gptq_marlin_repack(num_bits = 8), b_scales [1, size_n] in marlin_permute_scales order.  Takes the

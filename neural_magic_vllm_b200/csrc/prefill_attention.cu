@@ -29,6 +29,22 @@ namespace {
 
 using namespace umma;
 
+// Per-role cycle accounting (debug builds with -DB200_FA_PROF, read back through b200_debug_fa_prof):
+// totals over all CTAs of where the MMA issuer and one softmax warp of tile A spend their time.
+#ifdef B200_FA_PROF
+__device__ unsigned long long g_fa_prof[32];
+#define FPROF_DECL long long fp_t = clock64(), fp_n; unsigned long long fp_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}
+#define FPROF(i) (fp_n = clock64(), fp_acc[i] += (unsigned long long)(fp_n - fp_t), fp_t = fp_n)
+#define FPROF_FLUSH(base)                                                             \
+  do {                                                                                \
+    for (int fp_i = 0; fp_i < 8; ++fp_i) atomicAdd(&g_fa_prof[(base) + fp_i], fp_acc[fp_i]); \
+  } while (0)
+#else
+#define FPROF_DECL
+#define FPROF(i)
+#define FPROF_FLUSH(base)
+#endif
+
 constexpr int kBQ = 128;   // queries per CTA
 constexpr int kBK = 128;   // keys per tile
 constexpr int kFaThreads = 10 * 32;  // producer, MMA issuer, 2 x 4 softmax warps
@@ -116,19 +132,61 @@ __device__ __forceinline__ void fma2(float& d0, float& d1, float a0, float a1, f
       : "f"(a0), "f"(a1), "f"(b), "f"(c));
 }
 __device__ __forceinline__ void add2(float& d0, float& d1, float a0, float a1) {  // (d0, d1) += (a0, a1)
-  asm("{\n.reg .b64 ra, rd;\n"
+  asm volatile("{\n.reg .b64 ra, rd;\n"
       "mov.b64 ra, {%2, %3};\nmov.b64 rd, {%0, %1};\n"
       "add.rn.ftz.f32x2 rd, rd, ra;\nmov.b64 {%0, %1}, rd;\n}"
       : "+f"(d0), "+f"(d1)
       : "f"(a0), "f"(a1));
 }
+__device__ __forceinline__ void fma2v(float& d0, float& d1, float a0, float a1, float b0, float b1, float c0, float c1) {
+  asm("{\n.reg .b64 ra, rb, rc, rd;\n"
+      "mov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %5};\nmov.b64 rc, {%6, %7};\n"
+      "fma.rn.ftz.f32x2 rd, ra, rb, rc;\nmov.b64 {%0, %1}, rd;\n}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1), "f"(c0), "f"(c1));
+}
+__device__ __forceinline__ void add2v(float& d0, float& d1, float a0, float a1, float b) {
+  asm("{\n.reg .b64 ra, rb, rd;\n"
+      "mov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %4};\n"
+      "add.rn.ftz.f32x2 rd, ra, rb;\nmov.b64 {%0, %1}, rd;\n}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b));
+}
+// exp2 of a pair on the FMA / ALU pipes (the MUFU unit does 4 lanes per clock per sub-partition and
+// is the softmax bottleneck): round-to-nearest split x = n + f through the 1.5 * 2^23 magic add,
+// degree-3 minimax polynomial for 2^f on [-0.5, 0.5] (max relative error 7.5e-5, below the fp16 /
+// bf16 rounding of P), n added into the exponent field.  x <= 8 by construction (lazy rescale).
+__device__ __forceinline__ void ex2_poly2(float& p0, float& p1, float x0, float x1) {
+  constexpr float kMagic = 12582912.f;
+  x0 = fmaxf(x0, -125.f);
+  x1 = fmaxf(x1, -125.f);
+  float t0, t1, n0, n1, f0, f1, r0, r1;
+  add2v(t0, t1, x0, x1, kMagic);
+  add2v(n0, n1, t0, t1, -kMagic);
+  fma2v(f0, f1, n0, n1, -1.f, -1.f, x0, x1);
+  fma2v(r0, r1, f0, f1, 0.0551716685f, 0.0551716685f, 0.2426111251f, 0.2426111251f);
+  fma2v(r0, r1, r0, r1, f0, f1, 0.6932609677f, 0.6932609677f);
+  fma2v(r0, r1, r0, r1, f0, f1, 0.9999280572f, 0.9999280572f);
+  p0 = __int_as_float(__float_as_int(r0) + (__float_as_int(t0) << 23));
+  p1 = __int_as_float(__float_as_int(r1) + (__float_as_int(t1) << 23));
+}
+#ifndef B200_FA_POLY_PAIRS
+#define B200_FA_POLY_PAIRS 6  // of every 16 column pairs, this many take the polynomial instead of MUFU
+#endif
+// volatile twins: keep the hand-staged order of the unmasked softmax pass
+__device__ __forceinline__ float ex2v(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ void tmem_st16v(uint32_t taddr, const uint32_t (&r)[16]) { tmem_st16(taddr, r); }
 __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
 
-template <typename T, int D>
+template <typename T, int D, int POLY>
 // (10 warps are allocated as 12: 168 registers per thread is the ceiling for this block size)
 __global__ void __launch_bounds__(kFaThreads, 1)
 varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
@@ -235,11 +293,14 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
     // Ping-pong over the two query tiles: while the softmax warps of one tile work on S_t(j), the
     // tensor pipe runs P V of the other tile's step j and its Q K^T of step j + 1.
     const bool leader = elect_one();
+    FPROF_DECL;
     constexpr uint32_t idesc_qk = instr_desc<KIND>(kBQ, kBK);             // S[128 q, 128 keys]
     constexpr uint32_t idesc_pv = instr_desc<KIND>(kBQ, D) | (1u << 16);  // O_t[128 q, D], B MN-major
     auto issue_qk = [&](int t, int j) {
       const int st = j & 1;
+      FPROF(0);
       mbar_wait_bounded(&k_full[st], (j >> 1) & 1);
+      FPROF(1);
       fence_after_sync();
       const uint32_t qa = smem_u32(q_s + t * P::kTileBytes), ka = smem_u32(k_s + st * P::kTileBytes);
       if (leader) {
@@ -254,8 +315,11 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
     };
     auto issue_pv = [&](int t, int j) {
       const int st = j & 1;
+      FPROF(0);
       mbar_wait_bounded(&p_full[t], j & 1);  // P of step j stored (and O rescaled, when the row maxima moved)
+      FPROF(2 + t);
       mbar_wait_bounded(&v_full[st], (j >> 1) & 1);
+      FPROF(1);
       fence_after_sync();
       const uint32_t va = smem_u32(v_s + st * P::kTileBytes);
       if (leader) {
@@ -282,6 +346,8 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
         if (j + 1 < ntmax) mma_commit(&k_empty[(j + 1) & 1]);
       }
     }
+    FPROF(0);
+    if (lane == 0) FPROF_FLUSH(0);
     pdl_launch_dependents();
   } else {
     // ======================= softmax + output accumulation (thread = query row) =======================
@@ -304,16 +370,19 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
     // S_t(j) arriving implies P V of step j - 1 has finished (the tensor pipe runs in issue order and
     // the commit covers everything issued before it), so O may be touched right after s_full.
     float m_ref = -1e30f, l = 0.f;
+    FPROF_DECL;
     for (int j = 0; j < my_nt; ++j) {
       const int lim = row_end - j * kBK;  // columns < lim are visible to this row
       // no masked column in this tile for any row of the warp (all but the diagonal / tail tiles);
       // warp-uniform, because the TMEM loads / stores below are warp-collective
       const bool warp_full = __all_sync(0xffffffffu, lim >= kBK);
+      FPROF(0);
       mbar_wait_bounded(&s_full[t], j & 1);
+      FPROF(1);
       fence_after_sync();
       // the S row in registers (one TMEM read), the next chunk's tcgen05.ld in flight during the max
       uint32_t sr[4][32];
-      float mx0 = -1e30f, mx1 = -1e30f;
+      float mx0 = -1e30f, mx1 = -1e30f, mx2 = -1e30f, mx3 = -1e30f;
       tmem_ld32(s_addr, sr[0]);
 #pragma unroll
       for (int cc = 0; cc < 4; ++cc) {
@@ -321,9 +390,11 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
         if (cc + 1 < 4) tmem_ld32(s_addr + (cc + 1) * 32, sr[cc + 1]);
         if (warp_full) {
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            mx0 = fmaxf(mx0, __uint_as_float(sr[cc][i]));
-            mx1 = fmaxf(mx1, __uint_as_float(sr[cc][i + 1]));
+          for (int i = 0; i < 32; i += 8) {  // four chains of 3-input max
+            mx0 = fmaxf(mx0, fmaxf(__uint_as_float(sr[cc][i]), __uint_as_float(sr[cc][i + 1])));
+            mx1 = fmaxf(mx1, fmaxf(__uint_as_float(sr[cc][i + 2]), __uint_as_float(sr[cc][i + 3])));
+            mx2 = fmaxf(mx2, fmaxf(__uint_as_float(sr[cc][i + 4]), __uint_as_float(sr[cc][i + 5])));
+            mx3 = fmaxf(mx3, fmaxf(__uint_as_float(sr[cc][i + 6]), __uint_as_float(sr[cc][i + 7])));
           }
         } else {
 #pragma unroll
@@ -331,7 +402,8 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
             if (cc * 32 + i < lim) mx0 = fmaxf(mx0, __uint_as_float(sr[cc][i]));
         }
       }
-      const float m_new = fmaxf(m_ref, fmaxf(mx0, mx1));
+      FPROF(2);
+      const float m_new = fmaxf(fmaxf(m_ref, mx0), fmaxf(mx1, fmaxf(mx2, mx3)));
       const bool moved = (m_new - m_ref) * c > 8.f;
       if (__any_sync(0xffffffffu, moved)) {
         const float alpha = moved ? ex2((m_ref - m_new) * c) : 1.f;
@@ -349,23 +421,51 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
           }
         }
       }
+      FPROF(3);
       const float mc = m_ref * c;
       // p = exp2(s c - m_ref c), row sum, packed 16-bit P over the S columns
       float sum0 = 0.f, sum1 = 0.f;
       if (warp_full) {
-#pragma unroll
-        for (int cc = 0; cc < 4; ++cc) {
-          uint32_t pk[16];
+        // Staged by hand so that a MUFU result is consumed a whole 32-column chunk (>= 256 MUFU
+        // cycles) after it was issued: with one softmax warp per tile on a sub-partition, a
+        // consumer right behind its ex2 stalls for the MUFU latency on every pair.
+        float sumv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        auto exps = [&](int cc) {  // sr[cc] <- exp2(sr[cc] * c - mc), in place
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
             float x0, x1;
             fma2(x0, x1, __uint_as_float(sr[cc][i]), __uint_as_float(sr[cc][i + 1]), c, -mc);
-            const float p0 = ex2(x0), p1 = ex2(x1);
-            add2(sum0, sum1, p0, p1);
+            if (POLY < 0) {
+            } else if ((i >> 1) * POLY % 16 < POLY) {  // evenly spread over the chunk
+              ex2_poly2(x0, x1, x0, x1);
+            } else {
+              x0 = ex2v(x0);
+              x1 = ex2v(x1);
+            }
+            sr[cc][i] = __float_as_uint(x0);
+            sr[cc][i + 1] = __float_as_uint(x1);
+          }
+        };
+        auto pack_store = [&](int cc) {  // row sum, 16-bit P over the S columns
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            const float p0 = __uint_as_float(sr[cc][i]), p1 = __uint_as_float(sr[cc][i + 1]);
+            add2(sumv[i & 6], sumv[(i & 6) + 1], p0, p1);  // four independent chains: FADD2 latency is ~8 cycles
             pk[i >> 1] = DT<T>::pack2(p0, p1);
           }
-          tmem_st16(s_addr + cc * 16, pk);
-        }
+          tmem_st16v(s_addr + cc * 16, pk);
+        };
+        exps(0);
+        exps(1);
+        pack_store(0);
+        exps(2);
+        pack_store(1);
+        exps(3);
+        pack_store(2);
+        pack_store(3);
+        sum0 = (sumv[0] + sumv[2]) + (sumv[4] + sumv[6]);
+        sum1 = (sumv[1] + sumv[3]) + (sumv[5] + sumv[7]);
       } else {
 #pragma unroll
         for (int cc = 0; cc < 4; ++cc) {
@@ -384,10 +484,12 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
         }
       }
       l += sum0 + sum1;
+      FPROF(4);
       tmem_st_wait();
       fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[t]);
+      FPROF(5);
     }
     // o / l -> out[token][head][:]
     if (my_nt > 0) {
@@ -415,11 +517,15 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
           }
         }
       }
+      FPROF(6);
     } else if (qi < q_len) {  // a query row that sees no key: zeros
       T* dst = reinterpret_cast<T*>(args.out) + (int64_t)(q_begin + qi) * args.out_stride + (int64_t)head * D;
 #pragma unroll
       for (int i = 0; i < D; i += 8) *reinterpret_cast<uint4*>(dst + i) = make_uint4(0, 0, 0, 0);
     }
+#ifdef B200_FA_PROF
+    if ((warp == 2 || warp == 6) && lane == 0) FPROF_FLUSH(warp == 2 ? 8 : 16);
+#endif
   }
   __syncthreads();
   if (warp == 1) {
@@ -428,8 +534,8 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
   }
 }
 
-template <typename T, int D>
-int launch_fa(const b200_varlen_attention_params& p, cudaStream_t st) {
+template <typename T, int D, int POLY>
+int launch_fa_poly(const b200_varlen_attention_params& p, cudaStream_t st) {
   using P = FaPlan<D>;
   CUtensorMap tm_q, tm_k, tm_v;
   const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_UINT16;
@@ -451,7 +557,7 @@ int launch_fa(const b200_varlen_attention_params& p, cudaStream_t st) {
   a.out_stride = p.out_stride;
   a.scale_log2 = p.softmax_scale * 1.4426950408889634f;
   a.causal = p.causal;
-  auto kern = varlen_attention_kernel<T, D>;
+  auto kern = varlen_attention_kernel<T, D, POLY>;
   static size_t configured[kMaxDevices] = {};
   if (ensure_dyn_smem(kern, P::kBytes, configured) != cudaSuccess) {
     cudaGetLastError();
@@ -469,8 +575,43 @@ int launch_fa(const b200_varlen_attention_params& p, cudaStream_t st) {
   return B200_OK;
 }
 
+template <typename T, int D>
+int launch_fa(const b200_varlen_attention_params& p, cudaStream_t st) {
+  static const int poly = [] {
+    const char* e = getenv("B200_FA_POLY");
+    return e ? atoi(e) : B200_FA_POLY_PAIRS;
+  }();
+  switch (poly) {
+    case 0: return launch_fa_poly<T, D, 0>(p, st);
+    case 4: return launch_fa_poly<T, D, 4>(p, st);
+    case 8: return launch_fa_poly<T, D, 8>(p, st);
+#ifdef B200_FA_PROF
+    case 16: return launch_fa_poly<T, D, 16>(p, st);
+    case -1: return launch_fa_poly<T, D, -1>(p, st);  // no exp2 at all (wrong results): the floor of the rest
+#endif
+    default: return launch_fa_poly<T, D, 6>(p, st);
+  }
+}
+
 }  // namespace
 }  // namespace b200
+
+extern "C" int b200_debug_fa_prof(unsigned long long* dst, int32_t n, int32_t reset) {
+#ifdef B200_FA_PROF
+  if (n > 32) n = 32;
+  if (cudaMemcpyFromSymbol(dst, b200::g_fa_prof, (size_t)n * 8) != cudaSuccess) return -1;
+  if (reset) {
+    unsigned long long z[32] = {};
+    cudaMemcpyToSymbol(b200::g_fa_prof, z, sizeof(z));
+  }
+  return n;
+#else
+  (void)dst;
+  (void)n;
+  (void)reset;
+  return 0;
+#endif
+}
 
 extern "C" int b200_varlen_attention_fwd(const b200_varlen_attention_params* pp, void* stream) {
   using namespace b200;
