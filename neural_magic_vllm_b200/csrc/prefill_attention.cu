@@ -171,7 +171,7 @@ __device__ __forceinline__ void ex2_poly2(float& p0, float& p1, float x0, float 
   p1 = __int_as_float(__float_as_int(r1) + (__float_as_int(t1) << 23));
 }
 #ifndef B200_FA_POLY_PAIRS
-#define B200_FA_POLY_PAIRS 6  // of every 16 column pairs, this many take the polynomial instead of MUFU
+#define B200_FA_POLY_PAIRS 0  // of every 16 column pairs, this many take the polynomial instead of MUFU
 #endif
 // volatile twins: keep the hand-staged order of the unmasked softmax pass
 __device__ __forceinline__ float ex2v(float x) {
@@ -206,9 +206,9 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
   uint64_t* k_empty = bars + 5;   // [2] stage
   uint64_t* v_empty = bars + 7;   // [2] stage
   uint64_t* s_full = bars + 9;    // [2] query tile
-  uint64_t* p_full = bars + 11;   // [2] query tile
-  uint64_t* o_full = bars + 13;   // [2] query tile
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+  uint64_t* p_full = bars + 11;   // [2][2] query tile, half of the P row (keys 0-63 / 64-127)
+  uint64_t* o_full = bars + 15;   // [2] query tile
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int seq = blockIdx.y, head = blockIdx.z;
@@ -241,7 +241,8 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       mbar_init(&k_empty[i], 1);
       mbar_init(&v_empty[i], 1);
       mbar_init(&s_full[i], 1);
-      mbar_init(&p_full[i], 4);
+      mbar_init(&p_full[2 * i], 4);
+      mbar_init(&p_full[2 * i + 1], 4);
       mbar_init(&o_full[i], 1);
     }
     fence_mbar_init();
@@ -316,7 +317,9 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
     auto issue_pv = [&](int t, int j) {
       const int st = j & 1;
       FPROF(0);
-      mbar_wait_bounded(&p_full[t], j & 1);  // P of step j stored (and O rescaled, when the row maxima moved)
+      // P arrives in two halves: the P V MMAs of keys 0-63 run while the softmax warps are still
+      // in the exponentials of keys 64-127 (the O rescale, when the row maxima moved, precedes both)
+      mbar_wait_bounded(&p_full[2 * t], j & 1);
       FPROF(2 + t);
       mbar_wait_bounded(&v_full[st], (j >> 1) & 1);
       FPROF(1);
@@ -324,9 +327,19 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       const uint32_t va = smem_u32(v_s + st * P::kTileBytes);
       if (leader) {
 #pragma unroll
-        for (int kk = 0; kk < kBK / 16; ++kk)  // 16 keys per MMA: 8 packed P columns, 16 V rows
+        for (int kk = 0; kk < kBK / 32; ++kk)  // 16 keys per MMA: 8 packed P columns, 16 V rows
           mma_ts_f16(tmem_base + kOCol + t * D, tmem_base + t * kBK + kk * 8,
                      smem_desc_mn_sw128(va + kk * 2048, P::kBoxBytes), idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+      }
+      FPROF(0);
+      mbar_wait_bounded(&p_full[2 * t + 1], j & 1);
+      FPROF(2 + t);
+      fence_after_sync();
+      if (leader) {
+#pragma unroll
+        for (int kk = kBK / 32; kk < kBK / 16; ++kk)
+          mma_ts_f16(tmem_base + kOCol + t * D, tmem_base + t * kBK + kk * 8,
+                     smem_desc_mn_sw128(va + kk * 2048, P::kBoxBytes), idesc_pv, 1u);
         if (j + 1 == nt[t]) mma_commit(&o_full[t]);
       }
     };
@@ -380,14 +393,14 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       mbar_wait_bounded(&s_full[t], j & 1);
       FPROF(1);
       fence_after_sync();
-      // the S row in registers (one TMEM read), the next chunk's tcgen05.ld in flight during the max
+      // the S row in registers (one TMEM read)
       uint32_t sr[4][32];
       float mx0 = -1e30f, mx1 = -1e30f, mx2 = -1e30f, mx3 = -1e30f;
-      tmem_ld32(s_addr, sr[0]);
+#pragma unroll
+      for (int cc = 0; cc < 4; ++cc) tmem_ld32(s_addr + cc * 32, sr[cc]);
 #pragma unroll
       for (int cc = 0; cc < 4; ++cc) {
-        tmem_ld_wait_on(sr[cc]);
-        if (cc + 1 < 4) tmem_ld32(s_addr + (cc + 1) * 32, sr[cc + 1]);
+        tmem_ld_wait_on(sr[cc]);  // the first one waits for all four loads
         if (warp_full) {
 #pragma unroll
           for (int i = 0; i < 32; i += 8) {  // four chains of 3-input max
@@ -423,6 +436,12 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       }
       FPROF(3);
       const float mc = m_ref * c;
+      auto p_arrive = [&](int half) {  // this warp's P columns of one half are in TMEM
+        tmem_st_wait();
+        fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_full[2 * t + half]);
+      };
       // p = exp2(s c - m_ref c), row sum, packed 16-bit P over the S columns
       float sum0 = 0.f, sum1 = 0.f;
       if (warp_full) {
@@ -459,8 +478,9 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
         exps(0);
         exps(1);
         pack_store(0);
-        exps(2);
         pack_store(1);
+        p_arrive(0);
+        exps(2);
         exps(3);
         pack_store(2);
         pack_store(3);
@@ -485,10 +505,8 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
       }
       l += sum0 + sum1;
       FPROF(4);
-      tmem_st_wait();
-      fence_before_sync();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&p_full[t]);
+      if (!warp_full) p_arrive(0);
+      p_arrive(1);
       FPROF(5);
     }
     // o / l -> out[token][head][:]
