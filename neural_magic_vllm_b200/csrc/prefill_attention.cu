@@ -599,16 +599,18 @@ int launch_fa(const b200_varlen_attention_params& p, cudaStream_t st) {
     const char* e = getenv("B200_FA_POLY");
     return e ? atoi(e) : B200_FA_POLY_PAIRS;
   }();
-  switch (poly) {
-    case 0: return launch_fa_poly<T, D, 0>(p, st);
-    case 4: return launch_fa_poly<T, D, 4>(p, st);
-    case 8: return launch_fa_poly<T, D, 8>(p, st);
+  if constexpr (D == 128) {
+    switch (poly) {
+      case 4: return launch_fa_poly<T, D, 4>(p, st);
+      case 8: return launch_fa_poly<T, D, 8>(p, st);
 #ifdef B200_FA_PROF
-    case 16: return launch_fa_poly<T, D, 16>(p, st);
-    case -1: return launch_fa_poly<T, D, -1>(p, st);  // no exp2 at all (wrong results): the floor of the rest
+      case 16: return launch_fa_poly<T, D, 16>(p, st);
+      case -1: return launch_fa_poly<T, D, -1>(p, st);  // no exp2 at all (wrong results): the floor of the rest
 #endif
-    default: return launch_fa_poly<T, D, 6>(p, st);
+      default: break;
+    }
   }
+  return launch_fa_poly<T, D, 0>(p, st);
 }
 
 }  // namespace
@@ -639,7 +641,8 @@ extern "C" int b200_varlen_attention_fwd(const b200_varlen_attention_params* pp,
   if (p.num_seqs == 0 || p.total_q == 0 || p.max_seqlen_q == 0) return B200_OK;
   B200_REQUIRE(p.out && p.q && p.k && p.v && p.cu_seqlens_q && p.cu_seqlens_k, B200_EINVAL,
                "varlen_attention_fwd: null pointer");
-  B200_REQUIRE(p.head_size == 128, B200_ENOTSUP, "varlen_attention_fwd: head_size %d (128 is built)", p.head_size);
+  B200_REQUIRE(p.head_size == 128 || p.head_size == 64, B200_ENOTSUP,
+               "varlen_attention_fwd: head_size %d (64 and 128 are built)", p.head_size);
   B200_REQUIRE(p.num_kv_heads > 0 && p.num_heads % p.num_kv_heads == 0, B200_EINVAL,
                "varlen_attention_fwd: num_heads must be a multiple of num_kv_heads");
   B200_REQUIRE(((uintptr_t)p.q & 15) == 0 && ((uintptr_t)p.k & 15) == 0 && ((uintptr_t)p.v & 15) == 0 &&
@@ -647,8 +650,9 @@ extern "C" int b200_varlen_attention_fwd(const b200_varlen_attention_params* pp,
                    p.v_stride % 8 == 0 && p.out_stride % 8 == 0,
                B200_EINVAL, "varlen_attention_fwd: tensors must be 16-byte aligned with 16-byte aligned token strides");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (p.dtype == B200_F16) return launch_fa<__half, 128>(p, st);
-  if (p.dtype == B200_BF16) return launch_fa<__nv_bfloat16, 128>(p, st);
+  if (p.dtype == B200_F16) return p.head_size == 128 ? launch_fa<__half, 128>(p, st) : launch_fa<__half, 64>(p, st);
+  if (p.dtype == B200_BF16)
+    return p.head_size == 128 ? launch_fa<__nv_bfloat16, 128>(p, st) : launch_fa<__nv_bfloat16, 64>(p, st);
   set_error("varlen_attention_fwd: unsupported dtype %d (fp16 / bf16)", p.dtype);
   return B200_EINVAL;
 }

@@ -16,9 +16,8 @@ def ops():
     return pkg.ops
 
 
-def _run(ops, lens_q, lens_k, heads, kv_heads, dtype, causal, seed=0, scale_in=1.0, qkv_packed=False):
+def _run(ops, lens_q, lens_k, heads, kv_heads, dtype, causal, seed=0, scale_in=1.0, qkv_packed=False, d=128):
     from oracle import attention_ref as ar
-    d = 128
     g = torch.Generator().manual_seed(seed)
     tq, tk = sum(lens_q), sum(lens_k)
     if qkv_packed:  # q / k / v are column slices of one fused qkv row, as the model produces them
@@ -57,6 +56,13 @@ def test_varlen_attention_gqa(ops, heads, kv_heads):
     _run(ops, [200, 77], [200, 77], heads, kv_heads, torch.half, True, seed=3)
 
 
+@pytest.mark.parametrize("dtype", [torch.half, torch.bfloat16])
+@pytest.mark.parametrize("causal", [True, False])
+def test_varlen_attention_head_size_64(ops, dtype, causal):
+    _run(ops, [1, 100, 513, 31], [1, 100, 513, 31], 8, 2, dtype, causal, seed=9, d=64)
+    _run(ops, [5, 130], [300, 130], 4, 4, dtype, causal, seed=10, d=64)
+
+
 def test_varlen_attention_q_shorter_than_k(ops):
     # chunked prefill / prefix: the causal diagonal is aligned to the END of the keys
     _run(ops, [5, 130, 1], [300, 130, 64], 8, 2, torch.half, True, seed=4)
@@ -88,10 +94,10 @@ def test_varlen_attention_baseline_prefill_shape(ops):
 
 
 def test_varlen_attention_rejects(ops):
-    q = torch.zeros(4, 2, 64, dtype=torch.half, device=DEV)
+    q = torch.zeros(4, 2, 96, dtype=torch.half, device=DEV)
     cu = torch.tensor([0, 4], dtype=torch.int32, device=DEV)
     with pytest.raises(NotImplementedError):
-        ops.flash_attn_varlen_func(q, q, q, cu, cu, 4, 4, 0.1, True)             # head_size 64 is not built
+        ops.flash_attn_varlen_func(q, q, q, cu, cu, 4, 4, 0.1, True)             # head_size 96 is not built
     q = torch.zeros(4, 3, 128, dtype=torch.half, device=DEV)
     k = torch.zeros(4, 2, 128, dtype=torch.half, device=DEV)
     with pytest.raises(RuntimeError):
