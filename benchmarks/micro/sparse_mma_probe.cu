@@ -37,7 +37,19 @@ __device__ __forceinline__ void mma_sp_ss_f16(uint32_t tmem_d, uint64_t desc_a, 
       : "memory");
 }
 
-__global__ void __launch_bounds__(128, 1) probe_kernel(float* out, int n_exp, int col, uint32_t base_word, uint32_t flip16) {
+__device__ __forceinline__ void mma_sp_ts_f16(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t tmem_e,
+                                              uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+      "tcgen05.mma.sp.cta_group::1.kind::f16 [%0], [%1], %2, [%3], %4, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(tmem_e), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// ts = 1: the compressed A operand comes from TMEM (row m in lane m, two fp16 per 32-bit column,
+// 8 columns per MMA) instead of shared memory
+__global__ void __launch_bounds__(128, 1) probe_kernel(float* out, int n_exp, int col, uint32_t base_word, uint32_t flip16,
+                                                       int ts) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* a_s = smem;              // 128 x 128 B
@@ -65,7 +77,20 @@ __global__ void __launch_bounds__(128, 1) probe_kernel(float* out, int n_exp, in
   fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
-  constexpr uint32_t kECol = 128;
+  constexpr uint32_t kECol = 128, kACol = 160;
+  if (ts) {  // compressed A into TMEM: column j of lane m = values 1 + 2j, 2 + 2j
+    for (int j = 0; j < 32; j += 4) {
+      uint32_t w[4];
+      for (int i = 0; i < 4; ++i) {
+        const __half2 h = __floats2half2_rn((float)(1 + 2 * (j + i)), (float)(2 + 2 * (j + i)));
+        w[i] = *reinterpret_cast<const uint32_t*>(&h);
+      }
+      asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%2,%3,%4};" ::"r"(lane_addr + kACol + j), "r"(w[0]),
+                   "r"(w[1]), "r"(w[2]), "r"(w[3])
+                   : "memory");
+    }
+    tmem_st_wait();
+  }
   // M = 128, N = 128, F16 x F16 -> F32, K-major both, sparse flag (bit 2)
   const uint32_t idesc = instr_desc<KIND_F16>(kM, kN) | (1u << 2);
   for (int e = 0; e < n_exp; ++e) {
@@ -88,7 +113,11 @@ __global__ void __launch_bounds__(128, 1) probe_kernel(float* out, int n_exp, in
         // the metadata address is an even column; the odd one is selected through sparse_id2
         // (instruction-descriptor bits [0, 2)), as cute's MMA_Traits<..._SS_SPARSE> does
         const uint32_t e_col = kECol + kk;
-        mma_sp_ss_f16(tmem_base, da, db, tmem_base + (e_col & ~1u), idesc | (e_col & 1u), kk > 0 ? 1u : 0u);
+        if (ts)
+          mma_sp_ts_f16(tmem_base, tmem_base + kACol + kk * 8, db, tmem_base + (e_col & ~1u), idesc | (e_col & 1u),
+                        kk > 0 ? 1u : 0u);
+        else
+          mma_sp_ss_f16(tmem_base, da, db, tmem_base + (e_col & ~1u), idesc | (e_col & 1u), kk > 0 ? 1u : 0u);
       }
       mma_commit(bar);
     }
@@ -109,11 +138,12 @@ __global__ void __launch_bounds__(128, 1) probe_kernel(float* out, int n_exp, in
 
 int main(int argc, char** argv) {
   const int col = argc > 1 ? atoi(argv[1]) : 0;
+  const int ts = argc > 2 ? atoi(argv[2]) : 0;
   const int n_exp = 1 + 2 * 128;
   float* d_out;
   cudaMalloc(&d_out, (size_t)n_exp * kM * kN * 4);
   cudaFuncSetAttribute(probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384 + 32768 + 2048);
-  probe_kernel<<<1, 128, 16384 + 32768 + 2048>>>(d_out, n_exp, col, 0x44444444u, 0xEEEEu);
+  probe_kernel<<<1, 128, 16384 + 32768 + 2048>>>(d_out, n_exp, col, 0x44444444u, 0xEEEEu, ts);
   cudaError_t err = cudaDeviceSynchronize();
   if (err != cudaSuccess) {
     printf("error: %s\n", cudaGetErrorString(err));
@@ -146,7 +176,7 @@ int main(int argc, char** argv) {
           ++cnt;
           rmin = r < rmin ? r : rmin, rmax = r > rmax ? r : rmax, kmin = k < kmin ? k : kmin, kmax = k > kmax ? k : kmax;
         }
-    if (lane < 20 || lane % 16 == 0 || lane == 127)
+    if (lane < 2 || lane == 8 || lane == 127)
       printf("{\"col\": %d, \"lane\": %d, \"half\": %d, \"changed\": %d, \"rows\": [%d, %d], \"k\": [%d, %d]}\n", col, lane, half,
              cnt, rmin, rmax, kmin, kmax);
   }

@@ -4,15 +4,20 @@
 // (mma.sp.m16n8k32).  fp16 only, like the reference (:1100-1103: group 128 or channelwise).
 //
 // HBM traffic is the compressed stream (0.375 B per dense weight) read once, through three 2-D TMA
-// boxes per 64-k stage (values, metadata, scales) plus the activation tile.  Four dequant warps (one
-// per TMEM quadrant) unpack q - 8 with the lop3/hfma2 trick, apply the group scale (one rounding,
-// bit-identical to the reference's w_24_ref), scatter each kept pair to its two of four k positions
-// with two PRMTs whose selectors come from a 16-entry shared-memory table indexed by the 4-bit
-// metadata, and write the dense fragment straight into TMEM (tcgen05.st 16x256b); the MMA
-// (kind::f16, A from TMEM, B = activations in shared memory, fp32 accumulate in TMEM) is issued by
-// one thread.  The dense MMA spends 2x the tensor work of mma.sp, which is irrelevant at the
-// decode sizes this op serves (M <= 128 in C5: weight streaming); a tcgen05.mma.sp variant is the
-// next step for prefill.
+// boxes per 64-k stage (values, metadata, scales) plus the activation tile.  The tensor core takes
+// the weights as they are stored -- 2:4 compressed -- through tcgen05.mma.sp (kind::f16):
+//   A  = the kept values: four dequant warps (one per TMEM quadrant) unpack q - 8 with the
+//        lop3 / hfma2 trick, apply the group scale (one rounding, bit-identical to the reference's
+//        w_24_ref) and write the compressed fragment straight into TMEM (tcgen05.st 16x128b.x2: the
+//        Marlin-24 value order IS that shape's register order); row = output column n
+//   E  = the 2-bit position metadata, one 32-bit TMEM column per MMA of 32 dense k: lane
+//        m%8 + 8 khalf + 16 (m/16) holds the 16 metadata bits of rows m (low half) and m + 8 (high
+//        half) for dense k 16 khalf .. 16 khalf + 15 (read off the hardware with
+//        benchmarks/micro/sparse_mma_probe.cu; cute's tmem_e_frg says the same).  One LDS.128 and
+//        one PRMT per thread turn the Marlin-24 metadata words into that column.
+//   B  = activations in shared memory (K-major, 128-byte swizzle), N = the token tile
+//   D  = fp32 in TMEM, issued by one thread: two sparse MMAs per 64-k stage
+// No expansion to dense anywhere: half the dequant stores and half the tensor work of a dense MMA.
 //
 // Layout facts used below (re-derived from marlin_24_perms.py:16-48 and format_24.py:22-49, and
 // checked bit-exactly against tests/golden/marlin_24.npz):
@@ -42,8 +47,10 @@ constexpr int kTileN = 128;
 constexpr int kStageK = 64;
 constexpr int kStages = 6;
 constexpr int kAStages = 3;
-constexpr int kACols = kStageK / 2;          // 32 TMEM columns per dense 64-k stage
-constexpr int kDCol = kAStages * kACols;     // accumulator behind the A ring
+constexpr int kACols = kStageK / 4;          // 16 TMEM columns per stage: 32 kept fp16 per row
+constexpr int kECol = kAStages * kACols;     // 48: metadata ring, two columns (even, odd) per stage
+constexpr int kDCol = 64;                    // accumulator behind the A and metadata rings
+static_assert(kECol % 2 == 0 && kECol + 2 * kAStages <= kDCol, "TMEM layout");
 constexpr int kWarps = 4;                    // dequant warps
 constexpr int kThreads = 64 + kWarps * 32;
 constexpr int kMetaBytes = 2 * 512;
@@ -79,21 +86,19 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
   asm volatile("ld.shared.v2.b32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
   return v;
 }
-__device__ __forceinline__ void tmem_st_16x256b(uint32_t taddr, uint32_t r0, uint32_t r1, uint32_t r2,
-                                                uint32_t r3) {
-  // thread t: r0,r1 = (lane t/4, columns 2(t%4), 2(t%4)+1), r2,r3 = (lane t/4 + 8, same columns)
-  asm volatile("tcgen05.st.sync.aligned.16x256b.x1.b32 [%0], {%1,%2,%3,%4};" ::"r"(taddr), "r"(r0),
-               "r"(r1), "r"(r2), "r"(r3)
-               : "memory");
+// D[tmem] (+)= A_sparse[tmem] * B[smem]: A holds the kept half of a 2:4 sparse M x 32 slab (8 columns
+// of packed fp16 pairs), `tmem_e` (an even column; sparse_id2 = idesc bit 0 selects the odd one) the
+// position metadata
+__device__ __forceinline__ void mma_sp_ts_f16(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t tmem_e,
+                                              uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+      "tcgen05.mma.sp.cta_group::1.kind::f16 [%0], [%1], %2, [%3], %4, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(tmem_e), "r"(idesc), "r"(accumulate)
+      : "memory");
 }
-
-// PRMT selectors that place the kept pair (v0 = bytes 1:0, v1 = bytes 3:2 of the source, zero =
-// bytes of the second operand) at positions idx0, idx1 of a 4-group: .x builds k positions 0,1,
-// .y builds positions 2,3
-__device__ __forceinline__ uint2 expand_selectors(int m4) {
-  const int i0 = m4 & 3, i1 = m4 >> 2;
-  auto sel = [&](int pos) -> uint32_t { return i0 == pos ? 0x10u : (i1 == pos ? 0x32u : 0x44u); };
-  return make_uint2(sel(0) | (sel(1) << 8), sel(2) | (sel(3) << 8));
+__device__ __forceinline__ void tmem_st_32x32b_x2(uint32_t taddr, uint32_t r0, uint32_t r1) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1,%2};" ::"r"(taddr), "r"(r0), "r"(r1) : "memory");
 }
 
 template <int BM, int BITS>
@@ -113,7 +118,6 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
   uint64_t* empty_a = full_a + kAStages;
   uint64_t* tmem_full = empty_a + kAStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
-  uint2* lut = reinterpret_cast<uint2*>(bars + 32);  // 16 x 8 bytes, 256 bytes into the barrier block
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * BM;
@@ -138,7 +142,6 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
     mbar_init(tmem_full, 1);
     fence_mbar_init();
   }
-  if (threadIdx.x < 16) lut[threadIdx.x] = expand_selectors(threadIdx.x);
   if (warp == 1) tmem_alloc(tmem_slot, P::kTmemCols);
   fence_before_sync();
   __syncthreads();
@@ -197,7 +200,7 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
     // whole warp runs the loop (uniform operands); one elected lane issues (see scaled_mm.cu)
     const bool leader = elect_one();
     {
-      constexpr uint32_t idesc = instr_desc<KIND_F16>(kTileN, BM);
+      constexpr uint32_t idesc = instr_desc<KIND_F16>(kTileN, BM) | (1u << 2);  // sparse A
       int stage = 0, as = 0;
       uint32_t aphase = 0;
       for (int kb = kb_begin; kb < kb_end; ++kb) {
@@ -207,9 +210,9 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
         const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
         if (leader) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            mma_ts_f16(tmem_base + kDCol, tmem_base + as * kACols + k * 8, desc_advance(dx, k * 32), idesc,
-                       (kb > kb_begin || k > 0) ? 1u : 0u);
+          for (int kt = 0; kt < 2; ++kt)  // 32 dense k per MMA: 8 columns of kept pairs, 64 bytes of B per row
+            mma_sp_ts_f16(tmem_base + kDCol, tmem_base + as * kACols + kt * 8, desc_advance(dx, kt * 64),
+                          tmem_base + kECol + as * 2, idesc | (uint32_t)kt, (kb > kb_begin || kt > 0) ? 1u : 0u);
           mma_commit(&empty_a[as]);
           mma_commit(&empty_p[stage]);
         }
@@ -223,8 +226,7 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
     const int qd = warp & 3;  // TMEM quadrant
     const int nt = qd >> 1, hb = qd & 1;
     const int c = lane >> 2, r = lane & 3;
-    const uint32_t lut_u32 = smem_u32(lut);
-    const uint32_t msh = 16 * hb + 4 * r;  // this thread's metadata nibble inside each 32-bit word
+    (void)r;
     uint32_t sc[4];                        // sc[j]: scale of n = 64 nt + 8c + 4 hb + j, both halves
 #pragma unroll
     for (int j = 0; j < 4; ++j) sc[j] = 0x3c003c00u;
@@ -239,7 +241,12 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
     const uint32_t stage0 = smem_u32(stages) + P::kXBytes;
     // 4-bit: one 128-column box, rows 1 KiB, chunk nt at +512; 8-bit: one 64-column box per chunk
     const uint32_t val_off = BITS == 4 ? nt * 512 + lane * 16 : nt * 2048 + lane * 32;
-    const uint32_t meta_off = kValBytes + nt * 256 + c * 16;
+    // metadata column: this thread writes TMEM lane `lane` of its quadrant = rows (c' , j = 2 bb'),
+    // (c', j = 2 bb' + 1) with c' = lane % 8, bb' = lane / 16, k half (lane / 8) % 2; the two 8-byte
+    // units of those rows are adjacent: 16 bytes at unit 16 bb' + 2 c'
+    const uint32_t meta_off = kValBytes + nt * 256 + (lane >> 4) * 128 + (lane & 7) * 16;
+    const int khalf = (lane >> 3) & 1;
+    const uint32_t meta_sel = hb ? 0x7632u : 0x5410u;  // the int16 of this quadrant's b from both rows
     const uint32_t scale_off = kValBytes + kMetaBytes + (nt * 64 + 8 * c) * 2;
     const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16);
     int cur_group = -1;
@@ -256,7 +263,7 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
       const uint32_t aphase = (us / kAStages) & 1;
       mbar_wait_bounded(&full_p[stage], phase);
       const uint32_t base = stage0 + stage * P::kStageBytes;
-      uint32_t words[2][4], meta[2][8];
+      uint32_t words[2][4], mword[2];
 #pragma unroll
       for (int kt = 0; kt < 2; ++kt) {
         if constexpr (BITS == 4) {
@@ -268,10 +275,9 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
           words[kt][0] = hb ? w0.y : w0.x, words[kt][1] = hb ? w0.w : w0.z;
           words[kt][2] = hb ? w1.y : w1.x, words[kt][3] = hb ? w1.w : w1.z;
         }
-        const uint4 ma = lds128(base + meta_off + kt * 512);        // j = 0, 1
-        const uint4 mb = lds128(base + meta_off + kt * 512 + 128);  // j = 2, 3
-        meta[kt][0] = ma.x, meta[kt][1] = ma.y, meta[kt][2] = ma.z, meta[kt][3] = ma.w;
-        meta[kt][4] = mb.x, meta[kt][5] = mb.y, meta[kt][6] = mb.z, meta[kt][7] = mb.w;
+        // [row j = 2 bb': k half 0, k half 1][row j = 2 bb' + 1: k half 0, k half 1], each word = b0 | b1 << 16
+        const uint4 mw = lds128(base + meta_off + kt * 512);
+        mword[kt] = __byte_perm(khalf ? mw.y : mw.x, khalf ? mw.w : mw.z, meta_sel);
       }
       if (grouped) {
         const int g = (kb * kStageK) >> args.group_shift;
@@ -290,32 +296,28 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
       for (int kt = 0; kt < 2; ++kt) {
 #pragma unroll
         for (int bb = 0; bb < 2; ++bb) {
-          uint32_t lo[2][2], hi[2][2];  // [row c | row c+8][k pair]: groups r (lo) and r + 4 (hi)
+          uint32_t lo[2], hi[2];  // [row c | row c + 8]: kept pairs of groups r (lo) and r + 4 (hi)
 #pragma unroll
           for (int u = 0; u < 2; ++u) {
             const int j = 2 * bb + u;
             constexpr uint32_t LO = 0x000f000f, HI = 0x00f000f0, EX = 0x64006400;
             constexpr uint32_t SUB = 0x64086408, MUL = 0x2c002c00, ADD = 0xd480d480;
             const uint32_t q = words[kt][j];
-            uint32_t v_lo, v_hi;  // kept pairs of groups r and r + 4, exact q - zp, x scale (one rounding)
+            // exact q - zp, x scale (one rounding)
             if constexpr (BITS == 4) {
-              v_lo = mul2<__half>(h2_sub(lop3<kAndOr>(q, LO, EX), SUB), sc[j]);
-              v_hi = mul2<__half>(h2_fma(lop3<kAndOr>(q, HI, EX), MUL, ADD), sc[j]);
+              lo[u] = mul2<__half>(h2_sub(lop3<kAndOr>(q, LO, EX), SUB), sc[j]);
+              hi[u] = mul2<__half>(h2_fma(lop3<kAndOr>(q, HI, EX), MUL, ADD), sc[j]);
             } else {
-              unpack8<__half>(q, v_lo, v_hi);
-              v_lo = mul2<__half>(v_lo, sc[j]);
-              v_hi = mul2<__half>(v_hi, sc[j]);
+              unpack8<__half>(q, lo[u], hi[u]);
+              lo[u] = mul2<__half>(lo[u], sc[j]);
+              hi[u] = mul2<__half>(hi[u], sc[j]);
             }
-            const uint2 e_lo = lds64(lut_u32 + (((meta[kt][2 * j] >> msh) & 0xf) << 3));
-            const uint2 e_hi = lds64(lut_u32 + (((meta[kt][2 * j + 1] >> msh) & 0xf) << 3));
-            lo[u][0] = __byte_perm(v_lo, 0, e_lo.x), lo[u][1] = __byte_perm(v_lo, 0, e_lo.y);
-            hi[u][0] = __byte_perm(v_hi, 0, e_hi.x), hi[u][1] = __byte_perm(v_hi, 0, e_hi.y);
           }
-          const uint32_t t = t_dst + ((uint32_t)(16 * bb) << 16) + kt * 16;
-          tmem_st_16x256b(t, lo[0][0], lo[0][1], lo[1][0], lo[1][1]);          // dense k 4r .. 4r+3
-          tmem_st_16x256b(t + 8, hi[0][0], hi[0][1], hi[1][0], hi[1][1]);      // dense k 16+4r ..
+          // kept-pair column g of row kt: groups r and r + 4 = columns r and 4 + r of the 8
+          tmem_st_16x128b_x2(t_dst + ((uint32_t)(16 * bb) << 16) + kt * 8, lo[0], lo[1], hi[0], hi[1]);
         }
       }
+      tmem_st_32x32b_x2(t_lane + kECol + as * 2, mword[0], mword[1]);
       tmem_st_wait();
       fence_before_sync();
       __syncwarp();
