@@ -45,11 +45,17 @@ using namespace marlin;
 
 constexpr int kTileN = 128;
 constexpr int kStageK = 64;
-constexpr int kStages = 6;
-constexpr int kAStages = 3;
+#ifndef B200_M24_STAGES
+#define B200_M24_STAGES 6
+#endif
+#ifndef B200_M24_ASTAGES
+#define B200_M24_ASTAGES 3
+#endif
+constexpr int kStages = B200_M24_STAGES;
+constexpr int kAStages = B200_M24_ASTAGES;
 constexpr int kACols = kStageK / 4;          // 16 TMEM columns per stage: 32 kept fp16 per row
 constexpr int kECol = kAStages * kACols;     // 48: metadata ring, two columns (even, odd) per stage
-constexpr int kDCol = 64;                    // accumulator behind the A and metadata rings
+constexpr int kDCol = (kECol + 2 * kAStages + 15) / 16 * 16;  // 64: accumulator behind the A and metadata rings
 static_assert(kECol % 2 == 0 && kECol + 2 * kAStages <= kDCol, "TMEM layout");
 constexpr int kWarps = 4;                    // dequant warps
 constexpr int kThreads = 64 + kWarps * 32;
@@ -408,6 +414,11 @@ int launch24(const b200_gptq_marlin_24_gemm_params& p, cudaStream_t st) {
   const int tiles = m_tiles * n_tiles;
   const int target = (BM <= 32 ? 4 : 2) * num_sms();
   int splits = tiles >= target ? 1 : target / tiles;
+  static const int forced_splits = [] {  // debug knob: B200_M24_SPLITS
+    const char* e = getenv("B200_M24_SPLITS");
+    return e ? atoi(e) : 0;
+  }();
+  if (forced_splits > 0) splits = forced_splits;
   if (splits > a.num_kb / 4) splits = a.num_kb / 4;
   const int64_t per = (int64_t)p.size_m * p.size_n * 4;
   if (p.splitk_ws == nullptr) splits = 1;
