@@ -94,6 +94,22 @@ typedef struct {
 B200_API int b200_paged_attention_v1(const b200_paged_attention_params* p, void* stream);
 B200_API int b200_paged_attention_v2(const b200_paged_attention_params* p, void* stream);
 
+/* paged_attention_v2 that allocates nothing and needs no caller scratch.  No counterpart in the
+ * reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs,
+ * outputs and arithmetic as b200_paged_attention_v2; p->exp_sums / max_logits / tmp_out are
+ * ignored and the partition scratch lives in a device array built into the library
+ * (b200_paged_attention_v2_static_scratch_max_bytes() = 16 MiB, held by every GPU that loads the
+ * library until exit).  A shape whose scratch (b200_paged_attention_v2_static_scratch_bytes)
+ * exceeds that returns B200_EINVAL with a message.  All calls on a device share the array: calls
+ * that overlap on the GPU (different streams without ordering) race; calls ordered on one stream
+ * are safe.  Nothing in the array has to be zero on entry. */
+B200_API int b200_paged_attention_v2_static(const b200_paged_attention_params* p, void* stream);
+B200_API int64_t b200_paged_attention_v2_static_scratch_max_bytes(void);
+B200_API int64_t b200_paged_attention_v2_static_scratch_bytes(int32_t num_seqs, int32_t num_heads,
+                                                              int32_t head_size, int32_t max_seq_len,
+                                                              int32_t dtype);
+
 /* ------------------------------------------------------------------------------------------
  * Variable-length attention for prefill.  Stands in for the library call
  * of the reference's prefill path: flash_attn_varlen_func (vllm/attention/backends/flash_attn.py:
