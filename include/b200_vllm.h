@@ -279,6 +279,33 @@ B200_API int b200_debug_stream_prof(unsigned long long* dst, int32_t n);
  * warp of query tile A [8..15] / B [16..23]; 0 unless built with -DB200_FA_PROF */
 B200_API int b200_debug_fa_prof(unsigned long long* dst, int32_t n, int32_t reset);
 
+/* ------------------------------------------------------------------------------------------
+ * AWQ.  Replaces awq_gemm / awq_dequantize
+ * (csrc/quantization/awq/gemm_kernels.cu:437-549; ops csrc/torch_bindings.cpp:117-122).  fp16.
+ *   qweight [size_k, size_n / 8] int32, qzeros [size_k / group_size, size_n / 8] int32 (nibble j
+ *   of a word = channel 8 c + {0,2,4,6,1,3,5,7}[j]), scales [size_k / group_size, size_n] fp16;
+ *   w = (q - z) * s rounded to fp16 once.  size_n % 64 == 0, group_size % 32 == 0.
+ * awq_gemm: c [size_m, size_n] = a [size_m, size_k] (row stride lda elements) x w.  splitk_ws
+ * (optional, b200_awq_gemm_workspace_bytes) lets small size_m fill the GPU by splitting K; the
+ * reference's split_k_iters argument only sizes ITS scratch and has no meaning here.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  void* c;
+  const void* a;
+  const void* qweight;
+  const void* scales;
+  const void* qzeros;
+  int32_t size_m, size_n, size_k, group_size;
+  int64_t lda;
+  void* splitk_ws;
+  int64_t splitk_ws_bytes;
+} b200_awq_gemm_params;
+
+B200_API int b200_awq_gemm(const b200_awq_gemm_params* p, void* stream);
+B200_API int64_t b200_awq_gemm_workspace_bytes(int32_t m, int32_t n, int32_t k);
+B200_API int b200_awq_dequantize(void* out, const void* qweight, const void* scales, const void* qzeros,
+                                 int32_t size_k, int32_t size_n, int32_t group_size, void* stream);
+
 /* fp8_marlin_gemm (csrc/quantization/fp8/fp8_marlin.cu:1212-1308): fp8 e4m3 weights repacked with
  * gptq_marlin_repack(num_bits = 8), b_scales [1, size_n] in marlin_permute_scales order.  Takes the
  * same parameter block (num_bits = 8, num_groups = 1, no act-order). */

@@ -172,6 +172,18 @@ def gptq_marlin_gemm(a, b_q_weight, b_scales, g_idx, perm, workspace, num_bits: 
                                size_n, size_k, is_k_full)
 
 
+# awq (vllm/_custom_ops.py:167-177; the parameter NAMES of awq_gemm are swapped there, the positional
+# order -- input, qweight, scales, qzeros -- is what awq.py:172 passes and what the C++ op takes)
+def awq_dequantize(qweight: torch.Tensor, scales: torch.Tensor, zeros: torch.Tensor, split_k_iters: int,
+                   thx: int, thy: int) -> torch.Tensor:
+    return _C.awq_dequantize(qweight, scales, zeros, split_k_iters, thx, thy)
+
+
+def awq_gemm(input: torch.Tensor, qweight: torch.Tensor, qzeros: torch.Tensor, scales: torch.Tensor,
+             split_k_iters: int) -> torch.Tensor:
+    return _C.awq_gemm(input, qweight, qzeros, scales, split_k_iters)
+
+
 def fp8_marlin_gemm(a, b_q_weight, b_scales, workspace, num_bits: int, size_m: int, size_n: int,
                     size_k: int) -> torch.Tensor:  # :275-280
     return _C.fp8_marlin_gemm(a, b_q_weight, b_scales, workspace, num_bits, size_m, size_n, size_k)

@@ -336,3 +336,60 @@ def scaled_fp8_quant_ref(x: torch.Tensor, scale: torch.Tensor | None = None):
         scale = (xf.abs().max() / 448.0).reshape(1)
     q = (xf * (1.0 / scale.float())).clamp(-448.0, 448.0).to(torch.float8_e4m3fn)
     return q, scale
+
+
+# ---- AWQ ------------------------------------------------------------------
+# Format restated from the reference's device code, the only place it is written down:
+# csrc/quantization/awq/dequantize.cuh:17-101 (a 32-bit word holds eight 4-bit values of ONE k row;
+# the lop3 pairs nibbles (0,4) (1,5) (2,6) (3,7) and the results are eight consecutive output
+# channels, i.e. nibble j holds channel AWQ_ORDER[j]) and gemm_kernels.cu:369-435
+# (dequantize_weights: w = (q - z) * s in fp16, sub.f16x2 then fma.rn.f16x2 with 0: (q - z) is an
+# exact integer, so the product is rounded once).  No test or golden vector for AWQ exists in the
+# reference tree; the GPU tests pin this restatement against the reference's own kernels compiled
+# for sm_100 (oracle/_ref/_C_refcuda.so).
+AWQ_ORDER = [0, 2, 4, 6, 1, 3, 5, 7]
+
+
+def awq_pack(q: torch.Tensor) -> torch.Tensor:
+    """q [R, C] integers in [0, 16) -> int32 [R, C / 8]: nibble j of a word = column 8 c + AWQ_ORDER[j]."""
+    r, c = q.shape
+    assert c % 8 == 0
+    q = q.to(torch.int64).view(r, c // 8, 8)
+    word = torch.zeros(r, c // 8, dtype=torch.int64)
+    for j, col in enumerate(AWQ_ORDER):
+        word |= q[:, :, col] << (4 * j)
+    return _wrap_i32(word)
+
+
+def awq_unpack(packed: torch.Tensor) -> torch.Tensor:
+    """int32 [R, C / 8] -> int64 [R, C] in [0, 16)."""
+    r, c8 = packed.shape
+    w = packed.to(torch.int64) & 0xFFFFFFFF
+    out = torch.zeros(r, c8, 8, dtype=torch.int64)
+    for j, col in enumerate(AWQ_ORDER):
+        out[:, :, col] = (w >> (4 * j)) & 0xF
+    return out.view(r, c8 * 8)
+
+
+def awq_quantize(w: torch.Tensor, group_size: int):
+    """Asymmetric 4-bit quantisation of w [K, N] per (group of K, column), as AutoAWQ checkpoints
+    hold it -> (w_ref fp16 [K, N], qweight int32 [K, N/8], scales fp16 [K/G, N], qzeros int32 [K/G, N/8])."""
+    k, n = w.shape
+    g = k // group_size
+    wg = w.float().view(g, group_size, n)
+    lo, hi = wg.amin(1), wg.amax(1)
+    scales = ((hi - lo).clamp(min=1e-5) / 15).half()
+    zeros = (-lo / scales.float()).round().clamp(0, 15).to(torch.int64)
+    q = (wg / scales.float().unsqueeze(1) + zeros.unsqueeze(1)).round().clamp(0, 15).to(torch.int64).view(k, n)
+    qweight, qzeros = awq_pack(q), awq_pack(zeros)
+    return awq_dequantize_ref(qweight, scales, qzeros), qweight, scales, qzeros
+
+
+def awq_dequantize_ref(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> torch.Tensor:
+    """-> fp16 [K, N]: (q - z) exactly, times the group scale, rounded to fp16 once."""
+    k = qweight.shape[0]
+    group_size = k // scales.shape[0]
+    q = awq_unpack(qweight)
+    z = awq_unpack(qzeros).repeat_interleave(group_size, 0)
+    s = scales.float().repeat_interleave(group_size, 0)
+    return ((q - z).float() * s).half()  # fp32 product of an integer |.| <= 15 and an fp16 value is exact

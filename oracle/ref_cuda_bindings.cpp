@@ -44,6 +44,8 @@ TORCH_LIBRARY(_C_refcuda, ops) {
   ops.def("gptq_marlin_24_gemm", &gptq_marlin_24_gemm);
   ops.def("gptq_marlin_gemm", &gptq_marlin_gemm);
   ops.def("gptq_marlin_repack", &gptq_marlin_repack);
+  ops.def("awq_gemm", &awq_gemm);            // csrc/torch_bindings.cpp:117-118
+  ops.def("awq_dequantize", &awq_dequantize);  // :121-122
 
   ops.def("static_scaled_int8_quant(Tensor! out, Tensor input, Tensor scale) -> ()");
   ops.impl("static_scaled_int8_quant", torch::kCUDA, &static_scaled_int8_quant);
