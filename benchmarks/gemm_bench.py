@@ -131,6 +131,40 @@ def bench_marlin_24(ops, ms, iters):
         del qs, mt, ss
 
 
+def bench_awq(ops, ms, iters, with_ref):
+    """AWQ W4A16 g128 at the Llama-3-8B layer shapes (random words / zeros: timing only); with
+    --awq-ref the reference's own kernel (oracle/_ref/_C_refcuda.so) is timed beside it."""
+    hbm, tf = peaks()
+    ref = None
+    if with_ref:
+        from oracle import ref_cuda
+        ref = ref_cuda.ops() if ref_cuda.available() else None
+    for name, (k, n) in LLAMA3_8B.items():
+        if LAYERS and name not in LAYERS:
+            continue
+        w_bytes = k * n // 2 + (k // 128) * n * 2 + (k // 128) * n // 2
+        copies = max(2, -(-2 * L2_BYTES // w_bytes))
+        g = torch.Generator(device="cuda").manual_seed(0)
+        qs = [torch.randint(-2**31, 2**31 - 1, (k, n // 8), dtype=torch.int32, device="cuda", generator=g)
+              for _ in range(copies)]
+        zs = [torch.randint(-2**31, 2**31 - 1, (k // 128, n // 8), dtype=torch.int32, device="cuda", generator=g)
+              for _ in range(copies)]
+        ss = [(torch.rand(k // 128, n, device="cuda", generator=g) * 0.02 + 0.001).half() for _ in range(copies)]
+        for m in ms:
+            a = torch.randn(m, k, dtype=torch.half, device="cuda")
+            t = time_calls(lambda i: ops.awq_gemm(a, qs[i], ss[i], zs[i], 8), copies, iters)
+            byts = w_bytes + m * (k + n) * 2
+            fl = 2.0 * m * k * n
+            r = {"op": "awq_gemm", "layer": name, "m": m, "k": k, "n": n, "us": t * 1e6,
+                 "GBps": byts / t / 1e9, "hbm_frac": byts / t / 1e9 / hbm, "TFLOPs": fl / t / 1e12,
+                 "tensor_frac": fl / t / 1e12 / tf}
+            r["roofline_frac"] = max(r["hbm_frac"], r["tensor_frac"])
+            if ref is not None:
+                r["reference_cuda_us"] = time_calls(lambda i: ref.awq_gemm(a, qs[i], ss[i], zs[i], 8), copies, iters) * 1e6
+            print(json.dumps(r), flush=True)
+        del qs, zs, ss
+
+
 def bench_scaled_mm(ops, ms, iters, shapes, tag, fp8=True):
     hbm, tf = peaks()
     out = []
@@ -165,7 +199,8 @@ def bench_scaled_mm(ops, ms, iters, shapes, tag, fp8=True):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--op", default="all", choices=["marlin", "marlin24", "scaled_mm", "all"])
+    ap.add_argument("--op", default="all", choices=["marlin", "marlin24", "scaled_mm", "awq", "all"])
+    ap.add_argument("--awq-ref", action="store_true", help="time the reference's AWQ kernel beside ours")
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--ms", default="1,16,64,256,2048")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches (host overhead included)")
@@ -182,6 +217,8 @@ def main():
         bench_marlin(ops, ms, args.iters)
     if args.op in ("marlin24", "all"):
         bench_marlin_24(ops, [m for m in ms if m <= 128], args.iters)
+    if args.op in ("awq", "all"):
+        bench_awq(ops, [m for m in ms if m <= 256], args.iters, args.awq_ref)
     if args.op in ("scaled_mm", "all"):
         bench_scaled_mm(ops, ms, args.iters, LLAMA3_70B_TP8, "70B/TP8")
         bench_scaled_mm(ops, ms, args.iters, LLAMA3_70B_TP2, "70B/TP2")

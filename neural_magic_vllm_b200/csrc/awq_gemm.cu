@@ -14,9 +14,11 @@
 // and tcgen05.mma reads them from there (D[n, token] = W^T[n, k] X^T[k, token]); no transpose, no
 // repack into the Marlin layout.
 //   warp 0     TMA producer: per 64-k stage the activation tile [BM x 64] (K-major, 128B swizzle),
-//              the packed words [64 x 16], and per 32-row half the group's scale row and zero words
-//   warp 1     MMA issuer (elected lane): four kind::f16 MMAs (K = 16) per stage, fp32 D in TMEM
-//   warps 2-5  dequant: LDS.32 word -> lop3 magic numbers -> (q - z) exactly (hsub2 / hfma2 against
+//              the packed words [64 x 32] (256 channels: a 128-byte line per k row), and per 32-row
+//              half the group's scale row and zero words
+//   warp 1     MMA issuer (elected lane): per stage four K = 16 steps x two 128-channel sub-tiles
+//              (kind::f16, fp32 D in TMEM)
+//   warps 2-9  dequant: LDS.32 word -> lop3 magic numbers -> (q - z) exactly (hsub2 / hfma2 against
 //              per-column constants built from the zero word) -> x scale -> STS.128; then the
 //              epilogue (TMEM lane = output channel)
 // Small M splits K over blockIdx.z with fp32 partials and a sum kernel.
@@ -29,17 +31,21 @@ namespace {
 using namespace umma;
 using namespace marlin;
 
-constexpr int kAwqTileN = 128;
+constexpr int kAwqTileN = 256;  // channels per CTA: one packed row segment = 128 bytes (a full line per k row)
+constexpr int kAwqSubN = 128;   // MMA M: two sub-tiles per CTA
+constexpr int kAwqSubs = kAwqTileN / kAwqSubN;
 constexpr int kAwqStageK = 64;
-constexpr int kAwqStages = 6;
-constexpr int kAwqAStages = 3;
-constexpr int kAwqDequantWarps = 4;
+constexpr int kAwqStages = 3;   // with 2 A tiles: ~101 KiB per CTA at BM <= 32, two CTAs (16 dequant warps) per SM
+constexpr int kAwqAStages = 2;
+constexpr int kAwqDequantWarps = 8;
 constexpr int kAwqThreads = 64 + kAwqDequantWarps * 32;
-constexpr int kAwqATileBytes = kAwqStageK * kAwqTileN * 2;  // 16 KiB: two 64-channel column blocks
-constexpr int kAwqQBytes = kAwqStageK * (kAwqTileN / 8) * 4;  // 4 KiB of packed words
+constexpr int kAwqATileBytes = kAwqStageK * kAwqTileN * 2;  // 32 KiB: four 64-channel column blocks of 8 KiB
+constexpr int kAwqABlockBytes = kAwqStageK * 128;
+constexpr int kAwqQBytes = kAwqStageK * (kAwqTileN / 8) * 4;  // 8 KiB of packed words
 constexpr int kAwqSBytes = 2 * kAwqTileN * 2;                 // scale rows of the two 32-row halves
 constexpr int kAwqZSlot = 128;                               // TMA destinations are 128-byte aligned
-constexpr int kAwqZBytes = 2 * kAwqZSlot;                     // zero words (64 B) of the two halves
+constexpr int kAwqZBytes = 2 * kAwqZSlot;                     // zero words (128 B) of the two halves
+static_assert((kAwqTileN / 8) * 4 <= kAwqZSlot, "zero words of a tile fit one slot");
 
 struct AwqArgs {
   void* c;
@@ -54,7 +60,8 @@ struct PlanAwq {
   static constexpr int kXBytes = BM * 128;
   static constexpr int kStageBytes = (kXBytes + kAwqQBytes + kAwqSBytes + kAwqZBytes + 1023) / 1024 * 1024;
   static constexpr int kBytes = kAwqStages * kStageBytes + kAwqAStages * kAwqATileBytes + 1024 + 512;
-  static constexpr uint32_t kTmemCols = BM < 32 ? 32 : BM;
+  static constexpr uint32_t kTmemCols = kAwqSubs * BM < 32 ? 32 : kAwqSubs * BM;
+  static constexpr int kCtasPerSm = BM <= 32 ? 2 : 1;
 };
 
 // MN-major operand tile: rows = k, 128 bytes = 64 elements of the M / N dimension per row, 8-row
@@ -68,6 +75,20 @@ __device__ __forceinline__ uint64_t awq_desc_mn_sw128(uint32_t smem_addr, uint32
   d |= (uint64_t)1 << 46;
   d |= (uint64_t)2 << 61;
   return d;
+}
+
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
 // Per-column constants from a zero word: zc[0], zc[2] = 1024 + z (subtracted from 1024 + q),
@@ -110,7 +131,7 @@ __global__ void __launch_bounds__(256) awq_dequantize_kernel(__half* __restrict_
 }
 
 template <int BM>
-__global__ void __launch_bounds__(kAwqThreads, 1)
+__global__ void __launch_bounds__(kAwqThreads, PlanAwq<BM>::kCtasPerSm)
 awq_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_q,
                 const __grid_constant__ CUtensorMap tm_s, const __grid_constant__ CUtensorMap tm_z,
                 const AwqArgs args) {
@@ -196,8 +217,8 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
   } else if (warp == 1) {
     // ======================= MMA issuer =======================
     const bool leader = elect_one();
-    // D[128 channels, BM tokens]; A = weights, MN-major (bit 15); B = activations, K-major
-    constexpr uint32_t idesc = instr_desc<KIND_F16>(kAwqTileN, BM) | (1u << 15);
+    // D_sub[128 channels, BM tokens]; A = weights, MN-major (bit 15); B = activations, K-major
+    constexpr uint32_t idesc = instr_desc<KIND_F16>(kAwqSubN, BM) | (1u << 15);
     int stage = 0, as = 0;
     uint32_t aphase = 0;
     for (int kb = kb_begin; kb < kb_end; ++kb) {
@@ -209,8 +230,11 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
       if (leader) {
 #pragma unroll
         for (int kk = 0; kk < kAwqStageK / 16; ++kk)  // 16 k rows = two 8-row atoms of 1 KiB
-          mma_ss<KIND_F16>(tmem_base, awq_desc_mn_sw128(aa + kk * 2048, kAwqATileBytes / 2), desc_advance(dx, kk * 32),
-                           idesc, (kb > kb_begin || kk > 0) ? 1u : 0u);
+#pragma unroll
+          for (int sub = 0; sub < kAwqSubs; ++sub)
+            mma_ss<KIND_F16>(tmem_base + sub * BM,
+                             awq_desc_mn_sw128(aa + sub * 2 * kAwqABlockBytes + kk * 2048, kAwqABlockBytes),
+                             desc_advance(dx, kk * 32), idesc, (kb > kb_begin || kk > 0) ? 1u : 0u);
         mma_commit(&empty_a[as]);
         mma_commit(&empty_p[stage]);
       }
@@ -222,39 +246,38 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
   } else {
     // ======================= dequant, then epilogue =======================
     const int qd = warp & 3;                 // TMEM quadrant of the epilogue
-    const int t = (warp - 2) * 32 + lane;    // 0 .. 127
-    const int c = t & 15;                    // word column: channels n0 + 8 c .. + 7
-    const int r0 = t >> 4;                   // rows r0 + 8 i
+    const int sub = (warp - 2) >> 2;         // epilogue: 128-channel sub-tile
+    const int t = (warp - 2) * 32 + lane;    // 0 .. 255
+    const int c = t & 31;                    // word column: channels n0 + 8 c .. + 7
+    const int r0 = t >> 5;                   // rows r0 + 8 i
     const int blk = c >> 3, chunk = c & 7;   // 64-channel column block, 16-byte chunk inside its 128-byte row
+    const uint32_t stages_u32 = smem_u32(stages), a_ring_u32 = smem_u32(a_ring);
     int stage = 0, as = 0;
     uint32_t phase = 0, aphase = 0;
     for (int kb = kb_begin; kb < kb_end; ++kb) {
       mbar_wait_bounded(&full_p[stage], phase);
-      const uint8_t* q_src = stages + stage * P::kStageBytes + P::kXBytes;
+      const uint32_t q_src = stages_u32 + stage * P::kStageBytes + P::kXBytes;  // shared-space address
       uint32_t words[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) words[i] = *reinterpret_cast<const uint32_t*>(q_src + (r0 + 8 * i) * 64 + c * 4);
+      for (int i = 0; i < 8; ++i) words[i] = lds32(q_src + (r0 + 8 * i) * (kAwqTileN / 2) + c * 4);
       uint4 sc[2];
       uint32_t zq[2];
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        sc[h] = *reinterpret_cast<const uint4*>(q_src + kAwqQBytes + h * (kAwqTileN * 2) + c * 16);
-        zq[h] = *reinterpret_cast<const uint32_t*>(q_src + kAwqQBytes + kAwqSBytes + h * kAwqZSlot + c * 4);
+        sc[h] = lds128(q_src + kAwqQBytes + h * (kAwqTileN * 2) + c * 16);
+        zq[h] = lds32(q_src + kAwqQBytes + kAwqSBytes + h * kAwqZSlot + c * 4);
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty_p[stage]);
       mbar_wait_bounded(&empty_a[as], aphase ^ 1);
-      uint8_t* a_dst = a_ring + as * kAwqATileBytes + blk * (kAwqATileBytes / 2);
+      const uint32_t a_dst = a_ring_u32 + as * kAwqATileBytes + blk * kAwqABlockBytes + r0 * 128 + ((chunk ^ r0) << 4);
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         uint32_t zc[4];
         awq_zero_consts(zq[h], zc);
 #pragma unroll
-        for (int i = 4 * h; i < 4 * h + 4; ++i) {
-          const int r = r0 + 8 * i;  // r % 8 == r0
-          *reinterpret_cast<uint4*>(a_dst + (r >> 3) * 1024 + r0 * 128 + ((chunk ^ r0) << 4)) =
-              awq_dequant_word(words[i], zc, sc[h]);
-        }
+        for (int i = 4 * h; i < 4 * h + 4; ++i)  // row r0 + 8 i: 8-row atom i, row r0 inside it
+          sts128(a_dst + i * 1024, awq_dequant_word(words[i], zc, sc[h]));
       }
       // generic-proxy stores -> visible to the tensor core (async proxy) before the arrival
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -264,10 +287,10 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
       if (++as == kAwqAStages) as = 0, aphase ^= 1;
     }
     // epilogue: TMEM lane = output channel, column = token
-    const int n = n0 + qd * 32 + lane;
+    const int n = n0 + sub * kAwqSubN + qd * 32 + lane;
     mbar_wait_bounded(tmem_full, 0);
     fence_after_sync();
-    const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16);
+    const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + sub * BM;
 #pragma unroll 1
     for (int cc = 0; cc < BM / 16; ++cc) {
       if (m0 + cc * 16 >= args.m) break;
@@ -335,9 +358,10 @@ int launch_awq(const b200_awq_gemm_params& p, cudaStream_t st) {
   a.group_size = p.group_size;
   a.num_kb = (p.size_k + kAwqStageK - 1) / kAwqStageK;
   const int m_tiles = (p.size_m + BM - 1) / BM, n_tiles = (p.size_n + kAwqTileN - 1) / kAwqTileN;
-  // weight streaming at small M: split K until about two CTAs per SM are in flight
+  // weight streaming at small M: split K until every resident-CTA slot of the GPU is taken
   const int tiles = m_tiles * n_tiles;
-  int splits = tiles >= 2 * num_sms() ? 1 : (2 * num_sms()) / tiles;
+  const int slots = P::kCtasPerSm * num_sms();
+  int splits = tiles >= slots ? 1 : slots / tiles;
   if (splits > a.num_kb / 4) splits = a.num_kb / 4;
   const int64_t per = (int64_t)p.size_m * p.size_n * 4;
   if (p.splitk_ws == nullptr || per <= 0) splits = 1;
@@ -409,10 +433,11 @@ int b200_awq_dequantize(void* out, const void* qweight, const void* scales, cons
 }
 
 int64_t b200_awq_gemm_workspace_bytes(int32_t m, int32_t n, int32_t k) {
-  if (m <= 0 || n <= 0 || k <= 0 || m > 64) return 0;
-  const int bm = m <= 16 ? 16 : m <= 32 ? 32 : 64;
+  if (m <= 0 || n <= 0 || k <= 0 || m > 1024) return 0;  // (awq.py:166-170 sends M >= 256 to dequantize + matmul)
+  const int bm = m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : 128;
   const int tiles = ((m + bm - 1) / bm) * ((n + b200::kAwqTileN - 1) / b200::kAwqTileN);
-  int splits = tiles >= 2 * b200::num_sms() ? 1 : (2 * b200::num_sms()) / tiles;
+  const int slots = (bm <= 32 ? 2 : 1) * b200::num_sms();
+  int splits = tiles >= slots ? 1 : slots / tiles;
   const int num_kb = (k + b200::kAwqStageK - 1) / b200::kAwqStageK;
   if (splits > num_kb / 4) splits = num_kb / 4;
   return splits > 1 ? (int64_t)splits * m * n * 4 : 0;
