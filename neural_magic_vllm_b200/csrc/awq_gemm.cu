@@ -35,7 +35,7 @@ constexpr int kAwqTileN = 256;  // channels per CTA: one packed row segment = 12
 constexpr int kAwqSubN = 128;   // MMA M: two sub-tiles per CTA
 constexpr int kAwqSubs = kAwqTileN / kAwqSubN;
 constexpr int kAwqStageK = 64;
-constexpr int kAwqStages = 3;   // with 2 A tiles: ~101 KiB per CTA at BM <= 32, two CTAs (16 dequant warps) per SM
+constexpr int kAwqStages = 3;   // weight ring; with 2 A tiles and 6 activation tiles ~107 KiB per CTA at BM = 16: two CTAs per SM
 constexpr int kAwqAStages = 2;
 constexpr int kAwqDequantWarps = 8;
 constexpr int kAwqThreads = 64 + kAwqDequantWarps * 32;
@@ -58,8 +58,11 @@ struct AwqArgs {
 template <int BM>
 struct PlanAwq {
   static constexpr int kXBytes = BM * 128;
-  static constexpr int kStageBytes = (kXBytes + kAwqQBytes + kAwqSBytes + kAwqZBytes + 1023) / 1024 * 1024;
-  static constexpr int kBytes = kAwqStages * kStageBytes + kAwqAStages * kAwqATileBytes + 1024 + 512;
+  // two rings: the packed words / scales / zeros are free again as soon as the dequant warps hold
+  // them in registers, the activation tile only once the MMAs that read it have completed
+  static constexpr int kXStages = BM <= 16 ? 6 : 4;
+  static constexpr int kQStageBytes = (kAwqQBytes + kAwqSBytes + kAwqZBytes + 1023) / 1024 * 1024;
+  static constexpr int kBytes = kXStages * kXBytes + kAwqStages * kQStageBytes + kAwqAStages * kAwqATileBytes + 1024 + 512;
   static constexpr uint32_t kTmemCols = kAwqSubs * BM < 32 ? 32 : kAwqSubs * BM;
   static constexpr int kCtasPerSm = BM <= 32 ? 2 : 1;
 };
@@ -137,12 +140,15 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
                 const AwqArgs args) {
   using P = PlanAwq<BM>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* a_ring = stages + kAwqStages * P::kStageBytes;  // dequantised weights, MN-major
+  uint8_t* x_ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* stages = x_ring + P::kXStages * P::kXBytes;     // packed words + scales + zeros
+  uint8_t* a_ring = stages + kAwqStages * P::kQStageBytes;  // dequantised weights, MN-major
   uint64_t* bars = reinterpret_cast<uint64_t*>(a_ring + kAwqAStages * kAwqATileBytes);
-  uint64_t* full_p = bars;
-  uint64_t* empty_p = full_p + kAwqStages;
-  uint64_t* full_a = empty_p + kAwqStages;
+  uint64_t* full_p = bars;                       // [kAwqStages] weights landed
+  uint64_t* empty_p = full_p + kAwqStages;       // [kAwqStages] weights in registers
+  uint64_t* full_x = empty_p + kAwqStages;       // [kXStages] activations landed
+  uint64_t* empty_x = full_x + P::kXStages;      // [kXStages] MMAs that read them completed
+  uint64_t* full_a = empty_x + P::kXStages;
   uint64_t* empty_a = full_a + kAwqAStages;
   uint64_t* tmem_full = empty_a + kAwqAStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
@@ -161,7 +167,11 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
     tma_prefetch_desc(&tm_z);
     for (int s = 0; s < kAwqStages; ++s) {
       mbar_init(&full_p[s], 1);
-      mbar_init(&empty_p[s], kAwqDequantWarps + 1);
+      mbar_init(&empty_p[s], kAwqDequantWarps);
+    }
+    for (int s = 0; s < P::kXStages; ++s) {
+      mbar_init(&full_x[s], 1);
+      mbar_init(&empty_x[s], 1);
     }
     for (int s = 0; s < kAwqAStages; ++s) {
       mbar_init(&full_a[s], kAwqDequantWarps);
@@ -181,9 +191,9 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
     const bool leader = elect_one();
     const uint64_t pol_w = l2_policy_evict_first();  // streamed once (per m tile)
     const uint64_t pol_x = l2_policy_evict_last();
-    constexpr uint32_t tx_bytes = P::kXBytes + kAwqQBytes + kAwqSBytes + 2 * (kAwqTileN / 8) * 4;
+    constexpr uint32_t tx_bytes = kAwqQBytes + kAwqSBytes + 2 * (kAwqTileN / 8) * 4;
     auto load_weights = [&](int stage, int kb) {
-      uint8_t* q_dst = stages + stage * P::kStageBytes + P::kXBytes;
+      uint8_t* q_dst = stages + stage * P::kQStageBytes;
       mbar_arrive_expect_tx(&full_p[stage], tx_bytes);
       tma_load_2d(q_dst, &tm_q, n0 / 8, kb * kAwqStageK, &full_p[stage], pol_w);
 #pragma unroll
@@ -193,39 +203,49 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
         tma_load_2d(q_dst + kAwqQBytes + kAwqSBytes + h * kAwqZSlot, &tm_z, n0 / 8, g, &full_p[stage], pol_x);
       }
     };
+    auto load_x = [&](int xs, int kb) {
+      mbar_arrive_expect_tx(&full_x[xs], P::kXBytes);
+      tma_load_2d(x_ring + xs * P::kXBytes, &tm_x, kb * kAwqStageK, m0, &full_x[xs], pol_x);
+    };
     // programmatic dependent launch: weights, scales and zeros of the first ring of stages stream
     // in before the wait; only the activation tiles depend on the predecessor
-    const int pre = min(kb_end - kb_begin, kAwqStages);
+    const int n_kb = kb_end - kb_begin;
+    const int pre = min(n_kb, kAwqStages), pre_x = min(n_kb, P::kXStages);
     if (leader)
       for (int i = 0; i < pre; ++i) load_weights(i, kb_begin + i);
     pdl_wait();
     if (leader)
-      for (int i = 0; i < pre; ++i)
-        tma_load_2d(stages + i * P::kStageBytes, &tm_x, (kb_begin + i) * kAwqStageK, m0, &full_p[i], pol_x);
+      for (int i = 0; i < pre_x; ++i) load_x(i, kb_begin + i);
     __syncwarp();
-    int stage = pre == kAwqStages ? 0 : pre;
-    uint32_t phase = pre == kAwqStages ? 1 : 0;
-    for (int kb = kb_begin + pre; kb < kb_end; ++kb) {
-      mbar_wait_bounded(&empty_p[stage], phase ^ 1);
-      if (leader) {
-        load_weights(stage, kb);
-        tma_load_2d(stages + stage * P::kStageBytes, &tm_x, kb * kAwqStageK, m0, &full_p[stage], pol_x);
+    // weights run `pre` steps ahead, activations `pre_x`: one loop, each ring with its own cursor
+    int stage = pre == kAwqStages ? 0 : pre, xs = pre_x == P::kXStages ? 0 : pre_x;
+    uint32_t phase = pre == kAwqStages ? 1 : 0, xphase = pre_x == P::kXStages ? 1 : 0;
+    for (int i = pre; i < n_kb + (pre_x - pre); ++i) {
+      if (i < n_kb) {
+        mbar_wait_bounded(&empty_p[stage], phase ^ 1);
+        if (leader) load_weights(stage, kb_begin + i);
+        if (++stage == kAwqStages) stage = 0, phase ^= 1;
+      }
+      const int ix = i + (pre_x - pre);  // the activation step this iteration may issue
+      if (ix >= pre_x && ix < n_kb) {
+        mbar_wait_bounded(&empty_x[xs], xphase ^ 1);
+        if (leader) load_x(xs, kb_begin + ix);
+        if (++xs == P::kXStages) xs = 0, xphase ^= 1;
       }
       __syncwarp();
-      if (++stage == kAwqStages) stage = 0, phase ^= 1;
     }
   } else if (warp == 1) {
     // ======================= MMA issuer =======================
     const bool leader = elect_one();
     // D_sub[128 channels, BM tokens]; A = weights, MN-major (bit 15); B = activations, K-major
     constexpr uint32_t idesc = instr_desc<KIND_F16>(kAwqSubN, BM) | (1u << 15);
-    int stage = 0, as = 0;
-    uint32_t aphase = 0;
+    int xs = 0, as = 0;
+    uint32_t aphase = 0, xphase = 0;
     for (int kb = kb_begin; kb < kb_end; ++kb) {
-      // a full_a arrival implies the stage's full_p: the dequant warps waited on it first
       mbar_wait_bounded(&full_a[as], aphase);
+      mbar_wait_bounded(&full_x[xs], xphase);
       fence_after_sync();
-      const uint64_t dx = smem_desc_sw128(smem_u32(stages + stage * P::kStageBytes));
+      const uint64_t dx = smem_desc_sw128(smem_u32(x_ring + xs * P::kXBytes));
       const uint32_t aa = smem_u32(a_ring + as * kAwqATileBytes);
       if (leader) {
 #pragma unroll
@@ -236,9 +256,9 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
                              awq_desc_mn_sw128(aa + sub * 2 * kAwqABlockBytes + kk * 2048, kAwqABlockBytes),
                              desc_advance(dx, kk * 32), idesc, (kb > kb_begin || kk > 0) ? 1u : 0u);
         mma_commit(&empty_a[as]);
-        mma_commit(&empty_p[stage]);
+        mma_commit(&empty_x[xs]);
       }
-      if (++stage == kAwqStages) stage = 0;
+      if (++xs == P::kXStages) xs = 0, xphase ^= 1;
       if (++as == kAwqAStages) as = 0, aphase ^= 1;
     }
     if (leader) mma_commit(tmem_full);
@@ -256,7 +276,7 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
     uint32_t phase = 0, aphase = 0;
     for (int kb = kb_begin; kb < kb_end; ++kb) {
       mbar_wait_bounded(&full_p[stage], phase);
-      const uint32_t q_src = stages_u32 + stage * P::kStageBytes + P::kXBytes;  // shared-space address
+      const uint32_t q_src = stages_u32 + stage * P::kQStageBytes;  // shared-space address
       uint32_t words[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) words[i] = lds32(q_src + (r0 + 8 * i) * (kAwqTileN / 2) + c * 4);
