@@ -80,6 +80,11 @@ class QLinear:
         return self.ops.gptq_marlin_gemm(x, self.q, self.s, self.e, self.e, self.ws, 4, x.shape[0], self.n,
                                          self.k, True)
 
+    def add_norm(self, x, res, w):
+        """gptq_marlin_gemm + fused_add_rms_norm(out, res, w) as one operator (TP = 1)."""
+        return self.ops.gptq_marlin_gemm_add_rms_norm(x, self.q, self.s, self.e, self.e, self.ws, 4, x.shape[0],
+                                                      self.n, self.k, True, res, w, 1e-5)
+
 
 class Layer:
     def __init__(self, ops, tp, rank, gen, num_blocks):
@@ -117,6 +122,10 @@ class Decoder:
         self.ops, self.tp, self.rank, self.batch, self.ctx = ops, tp, rank, batch, ctx
         self.car = car  # one-shot NVLink all-reduce (None: NCCL)
         self.fuse_ar_norm = True
+        # TP = 1: row-parallel GEMM + fused_add_rms_norm as one operator.  Off by default: measured
+        # neutral to slightly slower in the step (one CTA per token row sums the split-K planes, where the
+        # separate sum kernel spreads over the whole GPU and PDL already hides its launch)
+        self.fuse_gemm_norm = False
         self.step = self.step_fused if glue == "fused" else self.step_torch
         # one seed for every rank: each rank draws the full tensors and keeps its shard
         gen = torch.Generator(device="cuda").manual_seed(1234)
@@ -193,12 +202,15 @@ class Decoder:
         ops, tp = self.ops, self.tp
         x = self.embed[self.tokens]
         res = None
-        for L in self.layers:
+        fuse = tp == 1 and self.fuse_gemm_norm
+        for li, L in enumerate(self.layers):
             if res is None:
                 res, hn = x, torch.empty_like(x)
                 ops.rms_norm(hn, x, L.ln1, 1e-5)
             elif tp > 1:
                 hn = x = self.reduce_add_norm(x, res, L.ln1)  # previous layer's down_proj partial sums
+            elif fuse:
+                hn = x  # already normalised by the previous layer's down_proj + norm operator
             else:
                 ops.fused_add_rms_norm(x, res, L.ln1, 1e-5)
                 hn = x
@@ -214,18 +226,25 @@ class Decoder:
             else:
                 ops.paged_attention_v2(out, self.es, self.ml, self.tmp, q, L.kc, L.vc, L.kvh, HEAD ** -0.5,
                                        self.block_tables, self.seq_lens, BLOCK, self.ctx + 1, None, "auto", 1.0)
-            o = L.o(out.view(-1, L.h * HEAD))
-            if tp > 1:
-                o = self.reduce_add_norm(o, res, L.ln2)
+            if fuse:
+                o = L.o.add_norm(out.view(-1, L.h * HEAD), res, L.ln2)
             else:
-                ops.fused_add_rms_norm(o, res, L.ln2, 1e-5)
+                o = L.o(out.view(-1, L.h * HEAD))
+                if tp > 1:
+                    o = self.reduce_add_norm(o, res, L.ln2)
+                else:
+                    ops.fused_add_rms_norm(o, res, L.ln2, 1e-5)
             gu = L.gate_up(o)
             act = torch.empty(self.batch, INTER // tp, dtype=torch.half, device="cuda")
             ops.silu_and_mul(act, gu)
-            x = L.down(act)  # TP: partial sums, reduced together with the next norm
+            if fuse:  # the norm behind down_proj is the next layer's input norm (or the final norm)
+                nw = self.layers[li + 1].ln1 if li + 1 < len(self.layers) else self.norm
+                x = L.down.add_norm(act, res, nw)
+            else:
+                x = L.down(act)  # TP: partial sums, reduced together with the next norm
         if tp > 1:
             x = self.reduce_add_norm(x, res, self.norm)
-        else:
+        elif not fuse:
             ops.fused_add_rms_norm(x, res, self.norm, 1e-5)
         hn = x
         if self.lm_head is not None:
@@ -280,6 +299,8 @@ def main():
     ap.add_argument("--no-lm-head", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--glue", choices=["fused", "torch"], default="fused")
+    ap.add_argument("--fuse-gemm-norm", action="store_true",
+                    help="TP = 1: run the row-parallel GEMMs and the fused_add_rms_norm behind them as one operator")
     ap.add_argument("--no-fuse-ar-norm", action="store_true",
                     help="keep all_reduce and fused_add_rms_norm as two kernels")
     ap.add_argument("--ar", choices=["one_shot", "nccl"], default="one_shot",
@@ -308,6 +329,7 @@ def main():
     for batch in [int(b) for b in args.batches.split(",")]:
         dec = Decoder(ops, world, rank, batch, args.ctx, lm_head=not args.no_lm_head, glue=args.glue, car=car)
         dec.fuse_ar_norm = not args.no_fuse_ar_norm
+        dec.fuse_gemm_norm = args.fuse_gemm_norm
         with torch.no_grad():
             for _ in range(2):
                 dec.step()
@@ -347,6 +369,7 @@ def main():
                 "attention": "paged_attention_v1" if dec.use_v1 else "paged_attention_v2", "glue": args.glue,
                 "all_reduce": ("one_shot_nvlink" if car is not None else "nccl") if world > 1 else None,
                 "ar_norm_fused": bool(car is not None and dec.fuse_ar_norm),
+                "gemm_norm_fused": bool(world == 1 and dec.fuse_gemm_norm and args.glue == "fused"),
                 "hbm_bytes_per_step_per_gpu": byts, "linear_bytes_per_gpu": lin, "kv_bytes_per_gpu": kv,
                 "hbm_GBps": byts / ms / 1e6, "hbm_frac": byts / ms / 1e6 / hbm,
                 "excluded": "scheduler, tokenizer; sampler = greedy argmax over the vocab-parallel lm_head",

@@ -268,6 +268,13 @@ typedef struct {
 
 B200_API int b200_gptq_marlin_gemm(const b200_gptq_marlin_gemm_params* p, void* stream);
 B200_API int64_t b200_gptq_marlin_gemm_workspace_bytes(int32_t m, int32_t n, int32_t k);
+/* extension (no single reference op): the row-parallel linear and the
+ * fused_add_rms_norm behind it (csrc/layernorm_kernels.cu:199-249) as one call:
+ *   residual [size_m, size_n] += gemm(a, w);  c = rms_norm(residual) * norm_weight
+ * Where the GEMM splits K, the fp32 partial sums are reduced inside the norm kernel (one kernel
+ * less per layer); otherwise the two operators run back to back.  Same bits as the unfused pair. */
+B200_API int b200_gptq_marlin_gemm_add_rms_norm(const b200_gptq_marlin_gemm_params* p, void* residual,
+                                                const void* norm_weight, float epsilon, void* stream);
 /* test hook: which W4A16/W8A16 decode kernel gptq_marlin_gemm takes at M <= 64 (0 heuristic,
  * 1 first-generation split-K kernel, 2 stream-K kernel wherever eligible, -1 environment) */
 B200_API void b200_debug_set_marlin_decode_kernel(int32_t choice);

@@ -172,6 +172,15 @@ def gptq_marlin_gemm(a, b_q_weight, b_scales, g_idx, perm, workspace, num_bits: 
                                size_n, size_k, is_k_full)
 
 
+def gptq_marlin_gemm_add_rms_norm(a, b_q_weight, b_scales, g_idx, perm, workspace, num_bits: int, size_m: int,
+                                  size_n: int, size_k: int, is_k_full: bool, residual: torch.Tensor,
+                                  norm_weight: torch.Tensor, epsilon: float) -> torch.Tensor:
+    """Extension: ``gptq_marlin_gemm`` followed by ``fused_add_rms_norm(out, residual, norm_weight, epsilon)``
+    (residual updated in place, returns the normalised rows) -- one kernel less where the GEMM splits K."""
+    return _C.gptq_marlin_gemm_add_rms_norm(a, b_q_weight, b_scales, g_idx, perm, workspace, num_bits, size_m,
+                                            size_n, size_k, is_k_full, residual, norm_weight, epsilon)
+
+
 # awq (vllm/_custom_ops.py:167-177; the parameter NAMES of awq_gemm are swapped there, the positional
 # order -- input, qweight, scales, qzeros -- is what awq.py:172 passes and what the C++ op takes)
 def awq_dequantize(qweight: torch.Tensor, scales: torch.Tensor, zeros: torch.Tensor, split_k_iters: int,

@@ -72,11 +72,16 @@ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 // input = T(z * rstd) * weight.  Plain: out = T(x * rstd) * weight.   (layernorm_kernels.cu:21-45,
 // 199-249).  VEC: 16-byte accesses, the row parked in shared memory between the two passes.
 // ---------------------------------------------------------------------------------------------
-template <typename T, bool FUSED, bool VEC>
+// SPLITK: `in` does not exist yet -- it is the sum of `splits` fp32 partial planes that a split-K
+// GEMM left in its workspace (ws[s * plane + row * hidden + i], summed s = 0, 1, ... in that order
+// and rounded to T exactly as the GEMM's own split-K sum kernel would); the rest of the kernel is
+// unchanged, so GEMM -> fused_add_rms_norm and this fused form agree bit for bit.
+template <typename T, bool FUSED, bool VEC, bool SPLITK = false>
 __global__ void __launch_bounds__(1024) rms_norm_kernel(T* out, const T* in,
                                                         T* __restrict__ residual,
                                                         const T* __restrict__ weight, const float eps,
-                                                        const int hidden) {
+                                                        const int hidden, const float* __restrict__ ws,
+                                                        const int splits, const int64_t plane) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ float red[32];
   pdl_wait();
@@ -88,7 +93,21 @@ __global__ void __launch_bounds__(1024) rms_norm_kernel(T* out, const T* in,
     constexpr int N = V16<T>::N;
     for (int i = threadIdx.x * N; i < hidden; i += blockDim.x * N) {
       V16<T> a;
-      a.load(in + base + i);
+      if constexpr (SPLITK) {
+        static_assert(V16<T>::N == 8, "two float4 per vector");
+        float4 lo = *reinterpret_cast<const float4*>(ws + base + i);
+        float4 hi = *reinterpret_cast<const float4*>(ws + base + i + 4);
+        for (int sp = 1; sp < splits; ++sp) {
+          const float4 l2 = *reinterpret_cast<const float4*>(ws + sp * plane + base + i);
+          const float4 h2 = *reinterpret_cast<const float4*>(ws + sp * plane + base + i + 4);
+          lo.x += l2.x, lo.y += l2.y, lo.z += l2.z, lo.w += l2.w;
+          hi.x += h2.x, hi.y += h2.y, hi.z += h2.z, hi.w += h2.w;
+        }
+        a.set(0, lo.x), a.set(1, lo.y), a.set(2, lo.z), a.set(3, lo.w);
+        a.set(4, hi.x), a.set(5, hi.y), a.set(6, hi.z), a.set(7, hi.w);
+      } else {
+        a.load(in + base + i);
+      }
       if constexpr (FUSED) {
         V16<T> r;
         r.load(residual + base + i);
@@ -143,15 +162,43 @@ int launch_rms(void* out, const void* in, void* residual, const void* weight, fl
     int threads = ((hidden / N + 31) / 32) * 32;
     threads = threads > 1024 ? 1024 : threads;
     launch_pdl(rms_norm_kernel<T, FUSED, true>, dim3(tokens), dim3(threads), row_bytes, st, (T*)out,
-               (const T*)in, (T*)residual, (const T*)weight, eps, hidden);
+               (const T*)in, (T*)residual, (const T*)weight, eps, hidden, (const float*)nullptr, 0, (int64_t)0);
   } else {
     int threads = ((hidden + 31) / 32) * 32;
     threads = threads > 1024 ? 1024 : threads;
     launch_pdl(rms_norm_kernel<T, FUSED, false>, dim3(tokens), dim3(threads), 0, st, (T*)out,
-               (const T*)in, (T*)residual, (const T*)weight, eps, hidden);
+               (const T*)in, (T*)residual, (const T*)weight, eps, hidden, (const float*)nullptr, 0, (int64_t)0);
   }
   return check_launch(FUSED ? "fused_add_rms_norm" : "rms_norm");
 }
+
+// split-K sum + residual add + RMSNorm in one kernel behind a split-K GEMM (marlin_gemm.cu):
+// out = norm(round(sum of partials) + residual) * weight, residual updated in place
+template <typename T>
+int launch_splitk_add_rms(void* out, const float* ws, int splits, void* residual, const void* weight, float eps,
+                          int tokens, int hidden, cudaStream_t st) {
+  constexpr int N = V16<T>::N;
+  int threads = ((hidden / N + 31) / 32) * 32;
+  threads = threads > 1024 ? 1024 : threads;
+  launch_pdl(rms_norm_kernel<T, true, true, true>, dim3(tokens), dim3(threads), (size_t)hidden * sizeof(T), st, (T*)out,
+             (const T*)nullptr, (T*)residual, (const T*)weight, eps, hidden, ws, splits, (int64_t)tokens * hidden);
+  return check_launch("gptq_marlin_gemm_add_rms_norm (split-K sum + add + norm)");
+}
+
+}  // namespace
+
+bool splitk_add_rms_eligible(int hidden, const void* out, const void* residual, const void* weight) {
+  return hidden % 8 == 0 && (size_t)hidden * 2 <= 48 * 1024 && aligned16(out) && aligned16(residual) &&
+         aligned16(weight);
+}
+int splitk_add_rms_norm(int dtype, void* out, const float* ws, int splits, void* residual, const void* weight,
+                        float eps, int tokens, int hidden, cudaStream_t st) {
+  return dtype == B200_F16
+             ? launch_splitk_add_rms<__half>(out, ws, splits, residual, weight, eps, tokens, hidden, st)
+             : launch_splitk_add_rms<__nv_bfloat16>(out, ws, splits, residual, weight, eps, tokens, hidden, st);
+}
+
+namespace {
 
 // ---------------------------------------------------------------------------------------------
 // (fused_add_)rms_norm + activation quantisation in one pass: the W8A8

@@ -19,6 +19,10 @@
 #include "umma.cuh"
 
 namespace b200 {
+// layer_glue.cu
+bool splitk_add_rms_eligible(int hidden, const void* out, const void* residual, const void* weight);
+int splitk_add_rms_norm(int dtype, void* out, const float* ws, int splits, void* residual, const void* weight,
+                        float eps, int tokens, int hidden, cudaStream_t st);
 namespace {
 
 using namespace umma;
@@ -831,6 +835,15 @@ inline int make_weight_maps(const b200_gptq_marlin_gemm_params& p, bool staged_s
   return B200_OK;
 }
 
+// gptq_marlin_gemm_add_rms_norm: when set (by that entry point, for the duration of one call), a
+// launch that would run the split-K sum kernel leaves the fp32 partials in the workspace instead
+// and reports them here; the caller sums them inside the norm kernel
+struct SplitKHandOff {
+  const float* partial = nullptr;
+  int splits = 0;
+};
+thread_local SplitKHandOff* tl_splitk_handoff = nullptr;
+
 template <int BITS, int BM, typename T>
 int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   using P = PlanT<BITS, BM>;
@@ -888,6 +901,11 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
     cudaGetLastError();
     set_error("gptq_marlin_gemm: launch failed: %s", cudaGetErrorString(le));
     return B200_ECUDA;
+  }
+  if (splits > 1 && a.locks == nullptr && tl_splitk_handoff != nullptr) {
+    tl_splitk_handoff->partial = a.partial;  // the caller's kernel sums the planes
+    tl_splitk_handoff->splits = splits;
+    return B200_OK;
   }
   if (splits > 1 && a.locks == nullptr) {
     const int64_t total = (int64_t)p.size_m * p.size_n;
@@ -1034,6 +1052,28 @@ void b200_debug_set_marlin_decode_kernel(int32_t choice) { b200::g_decode_choice
 
 // debug: per-CTA cycle accounting of the stream-K decode kernel (all zeros unless the library was
 // built with -DB200_STREAM_PROF).  dst = 160 x 32 uint64 on the host.
+// extension (fused decode-side glue): the row-parallel linear followed by
+// fused_add_rms_norm (layernorm_kernels.cu:199-249) -- c = norm(gemm(a, w) + residual) * weight,
+// residual += gemm(a, w) in place.  Where the GEMM splits K, its fp32 partial planes are summed
+// inside the norm kernel (one kernel less, and the GEMM output never goes to HBM in 16 bits);
+// otherwise the two operators run back to back.  Bit-identical to the unfused pair either way.
+int b200_gptq_marlin_gemm_add_rms_norm(const b200_gptq_marlin_gemm_params* pp, void* residual, const void* norm_weight,
+                                       float epsilon, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(pp != nullptr && residual != nullptr && norm_weight != nullptr, B200_EINVAL,
+               "gptq_marlin_gemm_add_rms_norm: null pointer");
+  SplitKHandOff h;
+  const bool can_fuse = pp->g_idx == nullptr && splitk_add_rms_eligible(pp->size_n, pp->c, residual, norm_weight);
+  tl_splitk_handoff = can_fuse ? &h : nullptr;
+  const int rc = b200_gptq_marlin_gemm(pp, stream);
+  tl_splitk_handoff = nullptr;
+  if (rc != B200_OK || pp->size_m == 0) return rc;
+  if (h.splits > 1)
+    return splitk_add_rms_norm(pp->dtype, pp->c, h.partial, h.splits, residual, norm_weight, epsilon, pp->size_m,
+                               pp->size_n, static_cast<cudaStream_t>(stream));
+  return b200_fused_add_rms_norm(pp->c, residual, norm_weight, epsilon, pp->size_m, pp->size_n, pp->dtype, stream);
+}
+
 int b200_debug_stream_prof(unsigned long long* dst, int32_t n) {
 #ifdef B200_STREAM_PROF
   if (n > 160 * 32) n = 160 * 32;

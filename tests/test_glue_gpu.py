@@ -390,3 +390,36 @@ def test_pdl_chain_matches_serial(ops):
             s.synchronize()
         assert torch.equal(out_x, ref_x) and torch.equal(out_r, ref_r)
         assert torch.isfinite(out_x.float()).all()
+
+
+# ---- gptq_marlin_gemm + fused_add_rms_norm as one operator (extension) ----
+
+@pytest.mark.parametrize("dtype", [torch.half, torch.bfloat16])
+@pytest.mark.parametrize("m", [1, 4, 5, 16, 33, 64, 128])
+@pytest.mark.parametrize("k,n", [(4096, 4096), (14336, 4096), (512, 256)])
+def test_marlin_gemm_add_rms_norm_matches_the_unfused_pair(m, k, n, dtype):
+    """Bit-identical to gptq_marlin_gemm followed by fused_add_rms_norm, whichever path the GEMM takes
+    (in-kernel reduce at M <= 4, split-K partials summed inside the norm kernel, or no split)."""
+    import neural_magic_vllm_b200 as pkg
+    from oracle import quant_ref as qr
+    ops = pkg.ops
+    torch.manual_seed(m + n)
+    w = torch.randn(k, n, dtype=dtype) * 0.05
+    _, mq, ms, _, _, _ = qr.marlin_quantize(w, 4, 128, False)
+    mq, ms = mq.to(DEV), ms.to(DEV)
+    e = torch.empty(0, dtype=torch.int32, device=DEV)
+    ws = torch.zeros(n // 64 * 16, dtype=torch.int32, device=DEV)
+    a = torch.randn(m, k, dtype=dtype, device=DEV)
+    res0 = torch.randn(m, n, dtype=dtype, device=DEV)
+    nw = (torch.rand(n, device=DEV) + 0.5).to(dtype)
+    # unfused
+    c = ops.gptq_marlin_gemm(a, mq, ms, e, e, ws, 4, m, n, k, True)
+    res_a = res0.clone()
+    ops.fused_add_rms_norm(c, res_a, nw, 1e-5)
+    # fused, twice (the workspace / lock buffer must come back clean)
+    for _ in range(2):
+        res_b = res0.clone()
+        out = ops.gptq_marlin_gemm_add_rms_norm(a, mq, ms, e, e, ws, 4, m, n, k, True, res_b, nw, 1e-5)
+        assert torch.equal(res_a, res_b)
+        assert torch.equal(c, out)
+    assert int(ws.abs().max()) == 0
