@@ -357,8 +357,27 @@ static int run_paged_attention(const b200_paged_attention_params* p, bool v2, cu
       if (v == 1 || v == 2 || v == 4 || v == 8) cluster = v;
     }
     a.cluster = cluster;
+    // A CTA is latency-bound (one 16-token item per warp per memory round trip: ~25 us for 1024
+    // tokens whatever the load), so a grid of slightly more than one wave of 4-warp CTAs (3 per SM)
+    // takes two full CTA times -- batch 64 x 8 kv heads = 512 CTAs on 444 slots: 52 us, where batch
+    // 96 takes 63.  With 3 warps a CTA needs 48 KiB and four fit an SM: when that makes the whole
+    // grid resident at once, it runs as one HBM-bound wave instead.
+    int warps = kAttnWarps;
+    {
+      static int knob_w[2] = {0, 0};
+      const bool fast = hs == 128 && p->block_size == 16 && G <= 8;
+      const int64_t ctas = (int64_t)base_ctas * cluster;
+      const int64_t slots4 = 3 * num_sms(), slots3 = 4 * num_sms();  // resident CTAs with 4 / 3 warps
+      const int64_t waves4 = (ctas + slots4 - 1) / slots4, waves3 = (ctas + slots3 - 1) / slots3;
+      const int cap = env_int_once("B200_ATTN_WARPS3_MAX_WAVES", knob_w, 2);
+      if (fast && cluster == 1 && waves3 < waves4 && waves3 <= cap) warps = 3;
+      static int knob[2] = {0, 0};  // tuning knob (bench sweeps): 3 / 4 forces the CTA shape
+      const int v = env_int_once("B200_ATTN_WARPS", knob, 0);
+      if (fast && (v == 3 || v == 4)) warps = v;
+    }
+    a.warps = warps;
     const int nh = 8 * nt;
-    const size_t smem = 256 + (size_t)kAttnWarps * stages * a.stage_bytes +
+    const size_t smem = 256 + (size_t)warps * stages * a.stage_bytes +
                         (cluster > 1 ? (size_t)nh * (hs + 2) * sizeof(float) : 0);
     dim3 grid(p->num_kv_heads * a.q_tiles, p->num_seqs, a.max_num_partitions * cluster);
     rc = p->dtype == B200_F16 ? launch_paged_attn_mma<__half>(a, p->kv_dtype, grid, smem, stream)

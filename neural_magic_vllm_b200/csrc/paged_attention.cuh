@@ -41,6 +41,7 @@ struct AttnArgs {
   int q_tiles;         // CTAs per kv head (group size split into tiles of 8*NT heads)
   int stages, stage_bytes;
   int cluster;         // CTAs (thread-block cluster along z) that split one partition's tokens; 1 = none
+  int warps;           // warps per CTA of the tensor-core kernel: kAttnWarps, or 3 (one-wave grids)
   int e5m2;  // fp8 flavour of the cache (only read when FP8)
   int64_t q_stride, kv_block_stride, kv_head_stride;
   float scale;        // softmax scale

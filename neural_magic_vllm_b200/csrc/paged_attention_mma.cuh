@@ -80,8 +80,9 @@ __device__ __forceinline__ void fp8x4_to_frag(uint32_t w, uint32_t& lo, uint32_t
   hi = fp8x2_to_T2<T, KV>(w >> 16);
 }
 
-template <typename T, int KV, int NT, int HMAX, bool FAST>
-__global__ void __launch_bounds__(kAttnThreads)
+// NW: warps per CTA (4; 3 where that lets the whole grid be resident at once, see paged_attention.cu)
+template <typename T, int KV, int NT, int HMAX, bool FAST, int NW>
+__global__ void __launch_bounds__(NW * 32)
     paged_attn_mma_kernel(const AttnArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr bool FP8 = KV != B200_KV_AUTO;
@@ -124,10 +125,10 @@ __global__ void __launch_bounds__(kAttnThreads)
     item_end = min(item_end, item_begin + per);
   }
   const int n_total = max(item_end - item_begin, 0);
-  const int n_items = n_total > warp ? (n_total - warp + kAttnWarps - 1) / kAttnWarps : 0;
+  const int n_items = n_total > warp ? (n_total - warp + NW - 1) / NW : 0;
   const int num_seq_blocks = (seq_len + BS - 1) / BS;
 
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem);  // [kAttnWarps][kAttnMaxStages]
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);  // [NW][kAttnMaxStages]
   const int S = a.stages;
   const uint32_t stage_bytes = FAST ? 2u * HMAX * 16 * ESZ : (uint32_t)a.stage_bytes;
   const uint32_t tile_bytes = (uint32_t)D * BS * ESZ;  // one (block, kv head) K or V tile
@@ -136,7 +137,7 @@ __global__ void __launch_bounds__(kAttnThreads)
   uint64_t* wbar = &full[warp * kAttnMaxStages];
 
   if (tid == 0) {
-    for (int i = 0; i < kAttnWarps * kAttnMaxStages; ++i) mbar_init(&full[i], 1);
+    for (int i = 0; i < NW * kAttnMaxStages; ++i) mbar_init(&full[i], 1);
     fence_mbar_init();
   }
   __syncthreads();
@@ -145,7 +146,7 @@ __global__ void __launch_bounds__(kAttnThreads)
   const int32_t* bt_row = a.bt + (int64_t)seq * a.max_blocks_per_seq;
   int bt0 = 0, bt1 = 0, bt_grp = -1;
   auto load_bt = [&](int grp) {
-    const int item = item_begin + warp + kAttnWarps * (grp * 32 + lane);
+    const int item = item_begin + warp + NW * (grp * 32 + lane);
     if (BS >= 16) {
       bt0 = item < num_seq_blocks ? __ldg(bt_row + item) : 0;
     } else {
@@ -175,7 +176,7 @@ __global__ void __launch_bounds__(kAttnThreads)
         bulk_g2s(dst, kc + p0 * blk_bytes, tile_bytes, bar);
         bulk_g2s(dst + (stage_bytes >> 1), vc + p0 * blk_bytes, tile_bytes, bar);
       } else {
-        const int item = item_begin + warp + kAttnWarps * i;
+        const int item = item_begin + warp + NW * i;
         const bool two = 2 * item + 1 < num_seq_blocks;
         mbar_arrive_expect_tx(bar, two ? 4 * tile_bytes : 2 * tile_bytes);
         bulk_g2s(dst, kc + p0 * blk_bytes, tile_bytes, bar);
@@ -261,7 +262,7 @@ __global__ void __launch_bounds__(kAttnThreads)
   for (int it = 0; it < n_items; ++it) {
     mbar_wait(&wbar[cs], cphase);
     const uint32_t st = wbase_s + (uint32_t)cs * stage_bytes;
-    const int item = item_begin + warp + kAttnWarps * it;
+    const int item = item_begin + warp + NW * it;
     const int n_chunks = (FAST || BS <= 16) ? 1 : (BS >> 4);
     for (int c = 0; c < n_chunks; ++c) {
       const int tok0 = item * IT + 16 * c;
@@ -503,7 +504,7 @@ __global__ void __launch_bounds__(kAttnThreads)
   const float* base = reinterpret_cast<const float*>(smem + 256);
   const int half_d = D >> 1;
   // cluster exchange area behind the rings: [NH][D] unnormalised output, then m[NH], l[NH]
-  float* xo = reinterpret_cast<float*>(smem + 256 + (size_t)kAttnWarps * S * stage_bytes);
+  float* xo = reinterpret_cast<float*>(smem + 256 + (size_t)NW * S * stage_bytes);
   float* xm = xo + NH * D;
   float* xl = xm + NH;
   auto finish = [&](int h, int d2, float M, float L, float o0, float o1) {
@@ -526,19 +527,19 @@ __global__ void __launch_bounds__(kAttnThreads)
       *reinterpret_cast<uint32_t*>(dst + 2 * d2) = packed;
     }
   };
-  for (int idx = tid; idx < NH * half_d; idx += kAttnThreads) {
+  for (int idx = tid; idx < NH * half_d; idx += (NW * 32)) {
     const int h = idx / half_d;
     const int d2 = idx - h * half_d;
     if (head_in_group0 + h >= G) continue;
-    float mw[kAttnWarps], M = -INFINITY;
+    float mw[NW], M = -INFINITY;
 #pragma unroll
-    for (int w = 0; w < kAttnWarps; ++w) {
+    for (int w = 0; w < NW; ++w) {
       mw[w] = base[w * wstride + NH * DP + h];
       M = fmaxf(M, mw[w]);
     }
     float L = 0.f, o0 = 0.f, o1 = 0.f;
 #pragma unroll
-    for (int w = 0; w < kAttnWarps; ++w) {
+    for (int w = 0; w < NW; ++w) {
       const float f = mw[w] == -INFINITY ? 0.f : exp2f(mw[w] - M);
       L = fmaf(base[w * wstride + NH * DP + NH + h], f, L);
       const float2 v = *reinterpret_cast<const float2*>(&base[w * wstride + h * DP + 2 * d2]);
@@ -567,7 +568,7 @@ __global__ void __launch_bounds__(kAttnThreads)
         asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr));
         return v;
       };
-      for (int idx = tid; idx < NH * half_d; idx += kAttnThreads) {
+      for (int idx = tid; idx < NH * half_d; idx += (NW * 32)) {
         const int h = idx / half_d;
         const int d2 = idx - h * half_d;
         if (head_in_group0 + h >= G) continue;
@@ -590,9 +591,9 @@ __global__ void __launch_bounds__(kAttnThreads)
   }
 }
 
-template <typename T, int KV, int NT, int HMAX, bool FAST>
+template <typename T, int KV, int NT, int HMAX, bool FAST, int NW = kAttnWarps>
 static int launch_one(const AttnArgs& a, dim3 grid, size_t smem, cudaStream_t stream) {
-  auto kern = paged_attn_mma_kernel<T, KV, NT, HMAX, FAST>;
+  auto kern = paged_attn_mma_kernel<T, KV, NT, HMAX, FAST, NW>;
   static size_t configured[kMaxDevices] = {};  // per instantiation and device; grows monotonically
   cudaError_t e = ensure_dyn_smem(kern, smem, configured);
   if (e != cudaSuccess) {
@@ -602,7 +603,7 @@ static int launch_one(const AttnArgs& a, dim3 grid, size_t smem, cudaStream_t st
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid;
-  cfg.blockDim = dim3(kAttnThreads);
+  cfg.blockDim = dim3(NW * 32);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
@@ -634,6 +635,7 @@ static int launch_kv(const AttnArgs& a, dim3 grid, size_t smem, cudaStream_t str
     if (a.head_size <= 128) return launch_one<T, KV, 2, 128, false>(a, grid, smem, stream);
     return launch_one<T, KV, 2, 256, false>(a, grid, smem, stream);
   }
+  if (fast && a.warps == 3) return launch_one<T, KV, 1, 128, true, 3>(a, grid, smem, stream);
   if (fast) return launch_one<T, KV, 1, 128, true>(a, grid, smem, stream);
   if (a.head_size <= 128) return launch_one<T, KV, 1, 128, false>(a, grid, smem, stream);
   return launch_one<T, KV, 1, 256, false>(a, grid, smem, stream);

@@ -163,23 +163,18 @@ void paged_attention_v1(Tensor& out, Tensor& query, Tensor& key_cache, Tensor& v
                  block_size, max_seq_len, alibi_slopes, kv_cache_dtype, kv_scale, tp_rank, bs_local,
                  bs_vert, bs_block, bs_step);
   // v1 has no scratch in its signature, so one CTA per (kv head, sequence) walks the whole
-  // context.  When that grid is only a few CTAs per SM (one partial wave of long CTAs), the op is
-  // served by the partitioned kernel instead, with scratch from the torch caching allocator
-  // (stream-ordered, CUDA-graph safe): same arithmetic as paged_attention_v2 on the same inputs.
-  // Measured (decode step, ctx 1024, ms): batch 32 (256 CTAs) 3.23 -> 3.43 with the split, batch 64
-  // (512 CTAs) 4.23 -> 4.17, batch 256 (2048 CTAs) 11.2 -> 11.8; a sweep of other partition sizes
-  // (128 .. 384 tokens) moved batch 64 by < 1 % and lost everywhere else.  So the split is taken
-  // only between one full wave (3 CTAs per SM) and four CTAs per SM.  B200_ATTN_V1_SPLIT = 0 / 1
-  // forces it.
+  // context.  B200_ATTN_V1_SPLIT = 1 serves the op with the partitioned kernel instead (scratch from
+  // the torch caching allocator: stream-ordered, CUDA-graph safe; same arithmetic as
+  // paged_attention_v2).  It was the default for grids between three and four CTAs per SM until
+  // the kernel learned to run those as one wave of 3-warp CTAs (paged_attention.cu: batch 64 step
+  // 4.17 -> 4.01 ms); measured slower than v1 everywhere else (batch 32: 3.23 -> 3.43 ms, batch
+  // 256: 11.2 -> 11.8 ms; other partition sizes, 128 .. 384 tokens, no better).
   const int64_t parts = (max_seq_len + B200_PARTITION_SIZE - 1) / B200_PARTITION_SIZE;
   static const int split_knob = [] {
     const char* e = std::getenv("B200_ATTN_V1_SPLIT");
     return e ? std::atoi(e) : -1;
   }();
-  const int64_t v1_ctas = (int64_t)num_kv_heads * query.size(0);
-  const bool split = split_knob >= 0 ? split_knob != 0 && parts > 1
-                                     : parts > 1 && v1_ctas > 3 * 148 && v1_ctas <= 4 * 148 &&
-                                           query.scalar_type() != at::ScalarType::Float;
+  const bool split = split_knob > 0 && parts > 1 && query.scalar_type() != at::ScalarType::Float;
   if (split) {
     Tensor tmp_out = at::empty({query.size(0), query.size(1), parts, query.size(2)}, query.options());
     Tensor exp_sums = at::empty({query.size(0), query.size(1), parts}, query.options().dtype(at::ScalarType::Float));

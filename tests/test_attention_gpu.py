@@ -247,3 +247,17 @@ def test_c1_opt125m_decode_replay_vs_reference_cpu(ops, dtype):
                                None, "auto", 1.0)
         torch.testing.assert_close(out.cpu().float(), ref.float(), atol=1e-3, rtol=1e-2)
     assert torch.equal(kcd.cpu(), kc) and torch.equal(vcd.cpu(), vc)
+
+
+@pytest.mark.parametrize("version", ["v1", "v2"])
+@pytest.mark.parametrize("kv", ["auto", "fp8"])
+@pytest.mark.parametrize("dtype", ["half", "bf16"])
+def test_one_wave_grid_takes_three_warp_ctas(ops, version, kv, dtype):
+    """64 sequences x 8 kv heads = 512 CTAs: between three and four CTAs per SM, where the tensor-core
+    kernel runs 3-warp CTAs (four per SM) so that the grid is one wave (paged_attention.cu).  Ragged
+    lengths, including ones that leave a warp without any 16-token item."""
+    dt = DTYPES[dtype]
+    g = torch.Generator().manual_seed(7)
+    lens = torch.randint(1, 400, (64,), generator=g).tolist()
+    lens[0], lens[1], lens[2], lens[3] = 1, 16, 17, 48
+    run_case(ops, version, dt, 32, 8, 128, 16, lens, kv_cache_dtype=kv, seed=11)
