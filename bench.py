@@ -337,6 +337,57 @@ def time_dominant_kernel(dec, batch, torch, steps, peak):
             "frac": gbs / peak, "share_of_step": None}
 
 
+def step_traffic(kern):
+    """dram bytes per launch of the dominant kernel from the committed ncu --set full capture, if one
+    exists for it (profiles/traffic.json), else None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+    except OSError:
+        return None
+    key = "step_attention_b64" if kern["kernel"].startswith("paged_attn") else "step_gate_up_m64"
+    return t.get(key, {}).get("bytes")
+
+
+def time_attention_in_step(dec, ops, batch, torch, steps, peak):
+    """The decode attention of the headline step, timed alone with CUDA events: the same op the
+    step calls (paged_attention_v1 / v2 by the reference's rule), rotating over the layers' KV
+    caches (268 MB per layer per call at batch 64 x ctx 1024: every launch streams from HBM)."""
+    L0 = dec.layers[0]
+    q = torch.randn(batch, L0.h, HEAD, dtype=torch.half, device="cuda")
+    out = torch.empty_like(q)
+
+    def call(L):
+        if dec.use_v1:
+            ops.paged_attention_v1(out, q, L.kc, L.vc, L.kvh, HEAD ** -0.5, dec.block_tables, dec.seq_lens,
+                                   BLOCK, dec.ctx + 1, None, "auto", 1.0)
+        else:
+            ops.paged_attention_v2(out, dec.es, dec.ml, dec.tmp, q, L.kc, L.vc, L.kvh, HEAD ** -0.5,
+                                   dec.block_tables, dec.seq_lens, BLOCK, dec.ctx + 1, None, "auto", 1.0)
+
+    with torch.no_grad():
+        for L in dec.layers:
+            call(L)
+        torch.cuda.synchronize()
+        reps = max(1, steps // 8)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for _ in range(reps):
+            for L in dec.layers:
+                call(L)
+        ev1.record()
+        torch.cuda.synchronize()
+    us = ev0.elapsed_time(ev1) * 1e3 / (reps * len(dec.layers))
+    nbytes = 2 * int(dec.seq_lens.sum().item()) * L0.kvh * HEAD * 2 + 2 * batch * L0.h * HEAD * 2
+    gbs = nbytes / us / 1e3
+    return {"kernel": "paged_attn_mma_kernel (%s: duration is the whole op)" %
+                      ("paged_attention_v1" if dec.use_v1 else "paged_attention_v2 incl. its reduce kernel"),
+            "shape": {"num_seqs": batch, "ctx": dec.ctx + 1, "heads": L0.h, "kv_heads": L0.kvh, "head_size": HEAD},
+            "us_per_launch": us, "launches_timed": reps * len(dec.layers),
+            "algorithmic_bytes_per_launch": nbytes, "achieved": gbs, "peak": peak, "unit": "GB/s",
+            "frac": gbs / peak, "share_of_step": None}
+
+
 def check_all_reduce(car, torch, dist, world, rank):
     """One-shot all-reduce: bit-identical on every rank and equal to the fp32 sum of the ranks'
     inputs rounded once (benchmarks/ar_check.py holds the full matrix of sizes / dtypes)."""
@@ -500,6 +551,7 @@ def main():
     dec = head.pop("_dec")
     graph = head.pop("_graph")
     dom = time_dominant_kernel(dec, HEADLINE_BATCH, torch, args.steps, peak)
+    dom_attn = time_attention_in_step(dec, ops, HEADLINE_BATCH, torch, args.steps, peak)
     if rank == 0:
         checks.update(check_vs_reference_cuda(dec, HEADLINE_BATCH, torch))
     # keep the headline graph replaying ~1.5 s so the 100 ms nvidia-smi sampler sees it under load
@@ -544,6 +596,9 @@ def main():
         ms = head["ms_per_step"]
         per_gpu_gbs = head["bytes_per_gpu"] / (ms * 1e-3) / 1e9
         dom["share_of_step"] = dom["us_per_launch"] * 32 / (ms * 1e3)
+        dom_attn["share_of_step"] = dom_attn["us_per_launch"] * 32 / (ms * 1e3)
+        # the dominant kernel is whichever of the two has the larger share of the step
+        top, second = (dom_attn, dom) if dom_attn["share_of_step"] >= dom["share_of_step"] else (dom, dom_attn)
         line = {
             "metric": METRIC, "value": HEADLINE_BATCH / (ms * 1e-3), "unit": "tokens/s", "n_gpus": world,
             "steps": args.steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True,
@@ -551,12 +606,17 @@ def main():
             "data": "synthetic: random-init packed int4 weights + scales, random KV, random token ids",
             "config": config,
             "tokens_per_s_per_gpu": HEADLINE_BATCH / (ms * 1e-3) / world,
-            "roofline": {"bound": "hbm", "achieved": per_gpu_gbs, "peak": peak, "unit": "GB/s",
-                         "frac": per_gpu_gbs / peak, "traffic": None, "peak_kind": peak_kind,
-                         "what": "whole decode step on one GPU: (packed weights + scales + KV + lm_head shard bytes) / step time",
-                         "algorithmic_bytes_per_step_per_gpu": head["bytes_per_gpu"],
-                         "linear_bytes": head["linear_bytes_per_gpu"], "kv_bytes": head["kv_bytes_per_gpu"],
-                         "lm_head_bytes": head["lm_head_bytes_per_gpu"], "dominant_kernel": dom},
+            "roofline": {"bound": "hbm", "achieved": top["achieved"], "peak": peak, "unit": "GB/s",
+                         "frac": top["frac"], "traffic": step_traffic(top), "peak_kind": peak_kind,
+                         "what": "dominant kernel of the step, timed alone with CUDA events inside this run: "
+                                 "algorithmic bytes per launch / average launch duration",
+                         "dominant_kernel": top, "second_kernel": second,
+                         "step": {"what": "whole decode step on one GPU: (packed weights + scales + KV + lm_head "
+                                          "shard bytes) / step time",
+                                  "achieved": per_gpu_gbs, "frac": per_gpu_gbs / peak,
+                                  "algorithmic_bytes_per_step_per_gpu": head["bytes_per_gpu"],
+                                  "linear_bytes": head["linear_bytes_per_gpu"], "kv_bytes": head["kv_bytes_per_gpu"],
+                                  "lm_head_bytes": head["lm_head_bytes_per_gpu"]}},
             "e2e": {"value": HEADLINE_BATCH / (head["e2e_ms_per_step"] * 1e-3), "unit": "tokens/s",
                     "h2d_bytes_per_step": head["h2d_bytes_per_step"], "d2h_bytes_per_step": head["d2h_bytes_per_step"],
                     "ms_per_step": head["e2e_ms_per_step"]},
