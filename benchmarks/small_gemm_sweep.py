@@ -4,6 +4,9 @@ import json, os, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SHAPES = {"qkv_tp8": (4096, 768), "o_tp8": (512, 4096), "gate_up_tp8": (4096, 3584), "down_tp8": (1792, 4096),
           "qkv_tp2": (4096, 3072), "o_tp2": (2048, 4096)}
+if os.environ.get("SWEEP_SHAPES") == "tp1":  # the unsharded Llama-3-8B layers that take the split-K kernel
+    SHAPES = {"qkv": (4096, 6144), "o": (4096, 4096), "down": (14336, 4096)}
+MS = tuple(int(x) for x in os.environ.get("SWEEP_MS", "1,64").split(","))
 CHILD = r'''
 import sys, json, torch
 sys.path.insert(0, %r)
@@ -17,7 +20,7 @@ for name, (k, n) in shapes.items():
     ss = [(torch.rand(k // 128, n, device="cuda", generator=g) * 0.02 + 0.001).half() for _ in range(copies)]
     e = torch.empty(0, dtype=torch.int32, device="cuda")
     ws = torch.zeros(max(n // 64 * 16, 16), dtype=torch.int32, device="cuda")
-    for m in (1, 64):
+    for m in %r:
         a = torch.randn(m, k, dtype=torch.half, device="cuda")
         for i in range(copies): ops.gptq_marlin_gemm(a, qs[i], ss[i], e, e, ws, 4, m, n, k, True)
         torch.cuda.synchronize()
@@ -33,10 +36,10 @@ for name, (k, n) in shapes.items():
 '''
 def main():
     res = {}
-    for splits in (0, 1, 2, 4, 8):
+    for splits in tuple(int(x) for x in os.environ.get("SWEEP_SPLITS", "0,1,2,4,8").split(",")):
         env = dict(os.environ)
         if splits: env["B200_MARLIN_SPLITS"] = str(splits)
-        out = subprocess.run([sys.executable, "-c", CHILD % (ROOT, SHAPES)], env=env, capture_output=True, text=True).stdout
+        out = subprocess.run([sys.executable, "-c", CHILD % (ROOT, SHAPES, MS)], env=env, capture_output=True, text=True).stdout
         for l in out.splitlines():
             if l.startswith("{"):
                 d = json.loads(l); res.setdefault((d["layer"], d["m"]), {})[splits] = round(d["us"], 2)

@@ -752,7 +752,10 @@ inline int pick_splits(int m, int n, int num_kb, int64_t ws_bytes) {
   // CTAs that are resident at once: 4 per SM for the decode kernel at BM <= 32, 2 at BM = 64, 1 for
   // the large tiles.  Split K until one resident wave covers the grid (never past it: a second,
   // partial wave costs more than idle SM slots).
-  const int per_sm = bm <= 32 ? 4 : bm <= 64 ? 2 : 1;
+  // Measured exception (benchmarks/small_gemm_sweep.py, Llama-3-8B qkv / o / down): at 4 < M <= 16
+  // -- the split-K sum kernel instead of the in-kernel reduce of M <= 4, short k ranges per CTA --
+  // half as many splits win (M = 16: qkv 10.6 -> 9.0 us, o 10.0 -> 7.6, down 16.5 -> 14.8).
+  const int per_sm = bm <= 32 ? ((bm == 16 && m > 4) ? 2 : 4) : bm <= 64 ? 2 : 1;
   const int target = per_sm * num_sms();
   if (tiles >= target || tiles == 0) return 1;
   int splits = target / tiles;
