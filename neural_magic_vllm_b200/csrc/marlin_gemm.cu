@@ -741,6 +741,8 @@ __global__ void __launch_bounds__(32) marlin_dequant_kernel(T* __restrict__ out,
   }
 }
 
+constexpr int kLockMaxM = 1;  // largest M whose split-K partials are reduced in-kernel by the last CTA to arrive
+
 inline int pick_bm(int m) { return m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : m <= 128 ? 128 : 256; }
 
 inline int pick_nt(int bm) { return bm >= 128 ? 2 : 1; }
@@ -752,10 +754,10 @@ inline int pick_splits(int m, int n, int num_kb, int64_t ws_bytes) {
   // CTAs that are resident at once: 4 per SM for the decode kernel at BM <= 32, 2 at BM = 64, 1 for
   // the large tiles.  Split K until one resident wave covers the grid (never past it: a second,
   // partial wave costs more than idle SM slots).
-  // Measured exception (benchmarks/small_gemm_sweep.py, Llama-3-8B qkv / o / down): at 4 < M <= 16
-  // -- the split-K sum kernel instead of the in-kernel reduce of M <= 4, short k ranges per CTA --
+  // Measured exception (benchmarks/small_gemm_sweep.py, Llama-3-8B qkv / o / down): at 1 < M <= 16
+  // -- the split-K sum kernel instead of the in-kernel reduce of M = 1, short k ranges per CTA --
   // half as many splits win (M = 16: qkv 10.6 -> 9.0 us, o 10.0 -> 7.6, down 16.5 -> 14.8).
-  const int per_sm = bm <= 32 ? ((bm == 16 && m > 4) ? 2 : 4) : bm <= 64 ? 2 : 1;
+  const int per_sm = bm <= 32 ? ((bm == 16 && m > kLockMaxM) ? 2 : 4) : bm <= 64 ? 2 : 1;
   const int target = per_sm * num_sms();
   if (tiles >= target || tiles == 0) return 1;
   int splits = target / tiles;
@@ -880,8 +882,11 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
     set_error("gptq_marlin_gemm: cannot reserve %d B of shared memory", (int)P::kBytes);
     return B200_ECUDA;
   }
-  // tiny M: the last split to arrive reduces in-kernel; otherwise a grid-wide reduce kernel
-  a.locks = (splits > 1 && m_tiles == 1 && p.size_m <= 4) ? p.workspace : nullptr;
+  // M = 1: the last split to arrive reduces in-kernel; otherwise a grid-wide reduce kernel (measured:
+  // at M = 2 .. 4 the in-kernel reduce loses -- qkv 11.4 vs 8.4 us, o 8.8 vs 7.0, down 15.9 vs 14.2 at M = 4)
+  static int lock_knob[2] = {0, 0};
+  const int lock_max_m = env_int_once("B200_MARLIN_LOCK_MAX_M", lock_knob, kLockMaxM);
+  a.locks = (splits > 1 && m_tiles == 1 && p.size_m <= lock_max_m) ? p.workspace : nullptr;
   // Programmatic dependent launch: behind a short producer kernel (RMSNorm, SiLU*mul, the attention
   // reduce) this grid's prologue and first ring of weight stages overlap the producer.  (Back to
   // back behind ANOTHER GEMM it was measured to lose -- early-resident dependents take TMEM /
