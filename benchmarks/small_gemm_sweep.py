@@ -6,6 +6,8 @@ SHAPES = {"qkv_tp8": (4096, 768), "o_tp8": (512, 4096), "gate_up_tp8": (4096, 35
           "qkv_tp2": (4096, 3072), "o_tp2": (2048, 4096)}
 if os.environ.get("SWEEP_SHAPES") == "tp1":  # the unsharded Llama-3-8B layers that take the split-K kernel
     SHAPES = {"qkv": (4096, 6144), "o": (4096, 4096), "down": (14336, 4096)}
+if os.environ.get("SWEEP_SHAPES", "").startswith("{"):  # e.g. '{"a": [4096, 18944]}'
+    SHAPES = {k: tuple(v) for k, v in json.loads(os.environ["SWEEP_SHAPES"]).items()}
 MS = tuple(int(x) for x in os.environ.get("SWEEP_MS", "1,64").split(","))
 CHILD = r'''
 import sys, json, torch
