@@ -202,3 +202,26 @@ def test_torch_ops_registered_with_reference_schemas():
         assert hasattr(getattr(torch.ops, ns), name), w
     s = str(torch.ops._C.cutlass_scaled_mm.default._schema)
     assert "Tensor(a0!) out" in s or "Tensor! out" in s or "out" in s
+
+
+def test_awq_pack_roundtrip_and_dequantize_ref():
+    """AWQ restatement (oracle/quant_ref.py): nibble j of a word holds channel 8c + {0,2,4,6,1,3,5,7}[j]
+    (csrc/quantization/awq/dequantize.cuh:17-101), w = (q - z) * s rounded to fp16 once."""
+    import torch
+    from oracle import quant_ref as qr
+    g = torch.Generator().manual_seed(0)
+    q = torch.randint(0, 16, (64, 32), generator=g)
+    packed = qr.awq_pack(q)
+    assert packed.dtype == torch.int32 and tuple(packed.shape) == (64, 4)
+    assert torch.equal(qr.awq_unpack(packed), q)
+    # the reference's lop3 pairs nibbles (0,4) (1,5) (2,6) (3,7) into consecutive channels
+    word = int(packed[0, 0]) & 0xFFFFFFFF
+    pairs = [((word >> (4 * j)) & 0xF, (word >> (4 * (j + 4))) & 0xF) for j in range(4)]
+    assert [v for p in pairs for v in p] == q[0, :8].tolist()
+    w = torch.randn(128, 64, generator=g) * 0.1
+    w_ref, qw, s, qz = qr.awq_quantize(w, 32)
+    assert w_ref.dtype == torch.half and tuple(qz.shape) == (4, 8) and tuple(s.shape) == (4, 64)
+    assert float((w_ref.float() - w).abs().max()) < float(s.float().max()) * 0.51 + 1e-3
+    manual = ((qr.awq_unpack(qw) - qr.awq_unpack(qz).repeat_interleave(32, 0)).float()
+              * s.float().repeat_interleave(32, 0)).half()
+    assert torch.equal(manual, w_ref)
