@@ -211,12 +211,14 @@ varlen_attention_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_c
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
-  const int seq = blockIdx.y, head = blockIdx.z;
+  const int seq = blockIdx.y, head = blockIdx.x;
   const int q_begin = args.cu_q[seq], q_len = args.cu_q[seq + 1] - q_begin;
   const int k_begin = args.cu_k[seq], k_len = args.cu_k[seq + 1] - k_begin;
-  // first query of tile A inside the sequence (tile B = q0 + 128).  Causal work grows with q0, and
-  // CTAs are dispatched in blockIdx order: the longest tiles go first (longest-processing-time order)
-  const int q0 = (int)(gridDim.x - 1 - blockIdx.x) * (2 * kBQ);
+  // first query of tile A inside the sequence (tile B = q0 + 128).  Causal work grows with q0 and
+  // CTAs are dispatched x-fastest, then y, then z: with the query tile in z (reversed), the longest
+  // tiles of ALL heads and sequences go first (longest-processing-time order over the whole grid,
+  // not per head), and the heads of one kv group run side by side and share K / V in L2
+  const int q0 = (int)(gridDim.z - 1 - blockIdx.z) * (2 * kBQ);
   if (q0 >= q_len) return;                // uniform over the CTA: nothing allocated yet
   const int shift = k_len - q_len;        // bottom-right causal alignment
   // kv tiles each query tile walks: keys [0, k_end_t)
@@ -583,7 +585,7 @@ int launch_fa_poly(const b200_varlen_attention_params& p, cudaStream_t st) {
     return B200_ECUDA;
   }
   const int q_tiles = (p.max_seqlen_q + 2 * kBQ - 1) / (2 * kBQ);  // a CTA owns two query tiles
-  cudaError_t le = launch_pdl(kern, dim3(q_tiles, p.num_seqs, p.num_heads), dim3(kFaThreads), (size_t)P::kBytes, st,
+  cudaError_t le = launch_pdl(kern, dim3(p.num_heads, p.num_seqs, q_tiles), dim3(kFaThreads), (size_t)P::kBytes, st,
                               tm_q, tm_k, tm_v, a);
   if (le != cudaSuccess) {
     cudaGetLastError();
