@@ -362,8 +362,15 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 //   warps of a quadrant split the four 16-row k tiles of a stage between them.
 // ------------------------------------------------------------------------------------------------
 constexpr int kTmemAStageCols = kStageK / 2;  // 32
-constexpr int kTDequantWarps = 4;          // one per TMEM quadrant
-constexpr int kTThreads = 64 + kTDequantWarps * 32;
+// dequant warps: one per TMEM quadrant; at BM = 64 -- two CTAs per SM instead of four -- two per
+// quadrant, each taking half of the stage's k range, so that an SM still has 16 of them
+#ifndef B200_TMEM_DW64
+#define B200_TMEM_DW64 8
+#endif
+template <int BM>
+__host__ __device__ constexpr int tmem_dequant_warps() { return BM >= 64 ? B200_TMEM_DW64 : 4; }
+template <int BM>
+__host__ __device__ constexpr int tmem_threads() { return 64 + tmem_dequant_warps<BM>() * 32; }
 constexpr int kTmemDCol = kAStages * kTmemAStageCols;
 
 template <int BITS, int BM>
@@ -384,11 +391,13 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
 }
 
 template <int BITS, int BM, typename T>
-__global__ void __launch_bounds__(kTThreads, (BM <= 32 ? 4 : 2))
+__global__ void __launch_bounds__(tmem_threads<BM>(), (BM <= 32 ? 4 : 2))
 marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                         const __grid_constant__ CUtensorMap tm_s, const MarlinArgs args) {
   using P = PlanT<BITS, BM>;
   constexpr int kStages = P::kStages;
+  constexpr int kTDequantWarps = tmem_dequant_warps<BM>();
+  constexpr int kKtPerWarp = 4 / (kTDequantWarps / 4);  // 16-k sub-steps of a stage per dequant warp
   constexpr int KIND = DT<T>::id == B200_F16 ? KIND_F16 : KIND_BF16;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -511,6 +520,7 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
     }
   } else {
     const int qd = warp & 3;          // TMEM quadrant = rows 32 qd .. 32 qd + 31
+    const int kt0 = ((warp - 2) >> 2) * kKtPerWarp;  // first 16-k sub-step of the stage this warp takes
     const int nt = qd >> 1;           // 64-column Marlin tile inside the 128-row n tile
     const int j0 = (qd & 1) * 2;      // first of its two 16-row fragments
     const int a_row = lane >> 2;
@@ -550,15 +560,15 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
       const uint32_t aphase = (u / kAStages) & 1;
       mbar_wait_bounded(&full_p[stage], phase);
       const uint32_t w_src = lane_src + stage * P::kStageBytes;
-      uint32_t words[4][BITS == 4 ? 2 : 4];
+      uint32_t words[kKtPerWarp][BITS == 4 ? 2 : 4];
 #pragma unroll
-      for (int kt = 0; kt < 4; ++kt) {
+      for (int kk = 0; kk < kKtPerWarp; ++kk) {
         if constexpr (BITS == 4) {
-          const uint2 v = lds64(w_src + kt * 1024);
-          words[kt][0] = v.x, words[kt][1] = v.y;
+          const uint2 v = lds64(w_src + (kt0 + kk) * 1024);
+          words[kk][0] = v.x, words[kk][1] = v.y;
         } else {
-          const uint4 v = lds128(w_src + kt * 1024);
-          words[kt][0] = v.x, words[kt][1] = v.y, words[kt][2] = v.z, words[kt][3] = v.w;
+          const uint4 v = lds128(w_src + (kt0 + kk) * 1024);
+          words[kk][0] = v.x, words[kk][1] = v.y, words[kk][2] = v.z, words[kk][3] = v.w;
         }
       }
       if (grouped) {
@@ -575,19 +585,20 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
       fence_after_sync();
       const uint32_t t_dst = t_lane + as * kTmemAStageCols;
 #pragma unroll
-      for (int kt = 0; kt < 4; ++kt) {
+      for (int kk = 0; kk < kKtPerWarp; ++kk) {
+        const int kt = kt0 + kk;
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {
           uint32_t rg[4];
           if constexpr (BITS == 4) {
-            unpack4<T>(words[kt][jj], rg);
+            unpack4<T>(words[kk][jj], rg);
           } else {
             if (args.fp8) {
-              unpack8_fp8<T>(words[kt][2 * jj], rg[0], rg[1]);
-              unpack8_fp8<T>(words[kt][2 * jj + 1], rg[2], rg[3]);
+              unpack8_fp8<T>(words[kk][2 * jj], rg[0], rg[1]);
+              unpack8_fp8<T>(words[kk][2 * jj + 1], rg[2], rg[3]);
             } else {
-              unpack8<T>(words[kt][2 * jj], rg[0], rg[1]);
-              unpack8<T>(words[kt][2 * jj + 1], rg[2], rg[3]);
+              unpack8<T>(words[kk][2 * jj], rg[0], rg[1]);
+              unpack8<T>(words[kk][2 * jj + 1], rg[2], rg[3]);
             }
           }
           rg[0] = mul2<T>(rg[0], sc[2 * jj]);
@@ -611,7 +622,7 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
       const uint32_t taddr = t_lane + kTmemDCol;
       const bool split_k = args.partial != nullptr;
 #pragma unroll 1
-      for (int c = 0; c < BM / 16; ++c) {
+      for (int c = (warp - 2) >> 2; c < BM / 16; c += kTDequantWarps / 4) {  // token chunks interleaved over the quadrant's warps
         if (m0 + c * 16 >= args.m) break;
         uint32_t rr[16];
         tmem_ld16(taddr + c * 16, rr);
@@ -640,12 +651,12 @@ marlin_gemm_tmem_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
         // and hands the counter back as zero -- no second kernel behind the GEMM
         uint32_t* flag = tmem_slot + 1;
         __threadfence();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(kTDequantWarps * 32) : "memory");
         if (warp == 2 && lane == 0) {
           const int old = atomicAdd(&args.locks[blockIdx.y], 1);
           *flag = (old == (int)gridDim.z - 1) ? 1u : 0u;
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(kTDequantWarps * 32) : "memory");
         if (*flag != 0 && n < args.n) {
           __threadfence();
           const int splits = gridDim.z;
@@ -894,7 +905,7 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   // never does: the glue kernels in between release their dependents only after their own wait.)
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(m_tiles, n_tiles, splits);
-  cfg.blockDim = dim3(kTThreads);
+  cfg.blockDim = dim3(tmem_threads<BM>());
   cfg.dynamicSmemBytes = P::kBytes;
   cfg.stream = st;
   cudaLaunchAttribute pdl_attr[1];
