@@ -758,8 +758,24 @@ inline int pick_bm(int m) { return m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : 
 
 inline int pick_nt(int bm) { return bm >= 128 ? 2 : 1; }
 
-inline int pick_splits(int m, int n, int num_kb, int64_t ws_bytes) {
-  const int bm = pick_bm(m);
+// 64 < M <= 256 may still take the decode kernel (registers -> TMEM dequant, BM = 64, several m
+// tiles) instead of the prefill kernel (shared-memory-staged dequant, 256-wide tiles, one CTA per
+// SM).  The decode kernel re-reads and re-dequantises the weights once per m tile, so it wins
+// while K x N x m_tiles is small -- measured on the Llama-3-8B layers (us, prefill -> decode kernel):
+// M = 128: qkv 18.6 -> 13.8, o 17.0 -> 11.6, down 25.7 -> 25.3, gate_up 40.4 -> 47.1 (kept on the
+// prefill kernel); M = 256: qkv 29.2 -> 24.4, o 26.6 -> 17.2, down 39.5 -> 43.3 (kept), gate_up
+// 59.8 -> 84.4 (kept).  B200_MARLIN_TMEM_MAX_WORK (weights x m tiles, in millions) overrides.
+inline int decode_bm(int m, int n, int k) {
+  if (m > 64 && m <= 256) {
+    static int knob[2] = {0, 0};
+    const int64_t limit = (int64_t)env_int_once("B200_MARLIN_TMEM_MAX_WORK", knob, 200) * 1000000;
+    if ((int64_t)k * n * ((m + 63) / 64) <= limit) return 64;
+  }
+  return pick_bm(m);
+}
+
+inline int pick_splits(int m, int n, int num_kb, int64_t ws_bytes, int bm_used = 0) {
+  const int bm = bm_used > 0 ? bm_used : pick_bm(m);
   const int cta_n = kTileN * pick_nt(bm);
   const int tiles = ((m + bm - 1) / bm) * ((n + cta_n - 1) / cta_n);
   // CTAs that are resident at once: 4 per SM for the decode kernel at BM <= 32, 2 at BM = 64, 1 for
@@ -879,7 +895,7 @@ int launch_tmem(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
   CUtensorMap tm_w, tm_s;
   rc = make_weight_maps(p, p.num_groups > 1, kTileN, &tm_w, &tm_s, &a);
   if (rc != B200_OK) return rc;
-  int splits = pick_splits(p.size_m, p.size_n, a.num_kb, p.splitk_ws ? p.splitk_ws_bytes : 0);
+  int splits = pick_splits(p.size_m, p.size_n, a.num_kb, p.splitk_ws ? p.splitk_ws_bytes : 0, BM);
   if ((int64_t)p.size_m * p.size_n % 4 != 0) splits = 1;
   a.kb_per_split = (a.num_kb + splits - 1) / splits;
   splits = (a.num_kb + a.kb_per_split - 1) / a.kb_per_split;
@@ -985,7 +1001,7 @@ int dispatch_bm(const b200_gptq_marlin_gemm_params& p, const void* a_used, int64
     }
   }
   if (!ACT && one_group_per_stage) {
-    switch (pick_bm(p.size_m)) {
+    switch (decode_bm(p.size_m, p.size_n, p.size_k)) {
       case 16: return launch_tmem<BITS, 16, T>(p, st);
       case 32: return launch_tmem<BITS, 32, T>(p, st);
       case 64: return launch_tmem<BITS, 64, T>(p, st);
@@ -1026,7 +1042,11 @@ int run(const b200_gptq_marlin_gemm_params& p, cudaStream_t st) {
 extern "C" {
 
 int64_t b200_gptq_marlin_gemm_workspace_bytes(int32_t m, int32_t n, int32_t k) {
-  const int splits = b200::pick_splits(m, n, k / b200::kStageK, -1);
+  int splits = b200::pick_splits(m, n, k / b200::kStageK, -1);
+  if (b200::decode_bm(m, n, k) != b200::pick_bm(m)) {  // the decode kernel serves this shape
+    const int s2 = b200::pick_splits(m, n, k / b200::kStageK, -1, b200::decode_bm(m, n, k));
+    if (s2 > splits) splits = s2;
+  }
   const int64_t v1 = splits > 1 ? (int64_t)splits * m * n * 4 : 0;
   const int64_t v2 = m <= 64 ? b200::stream_ws_bytes(m) : 0;  // stream-K decode kernel: 2 slots per CTA
   return v1 > v2 ? v1 : v2;
