@@ -57,8 +57,12 @@ constexpr int kACols = kStageK / 4;          // 16 TMEM columns per stage: 32 ke
 constexpr int kECol = kAStages * kACols;     // 48: metadata ring, two columns (even, odd) per stage
 constexpr int kDCol = (kECol + 2 * kAStages + 15) / 16 * 16;  // 64: accumulator behind the A and metadata rings
 static_assert(kECol % 2 == 0 && kECol + 2 * kAStages <= kDCol, "TMEM layout");
-constexpr int kWarps = 4;                    // dequant warps
-constexpr int kThreads = 64 + kWarps * 32;
+// dequant warps: one per TMEM quadrant; at BM = 64 (two CTAs per SM instead of four) two per quadrant,
+// one for each 32-k half of a stage, so that an SM keeps 16 of them (as in marlin_gemm_tmem_kernel)
+template <int BM>
+__host__ __device__ constexpr int dequant_warps24() { return BM >= 64 ? 8 : 4; }
+template <int BM>
+__host__ __device__ constexpr int threads24() { return 64 + dequant_warps24<BM>() * 32; }
 constexpr int kMetaBytes = 2 * 512;
 constexpr int kScaleBytes = 1024;            // one row (256 B) padded: stages stay 1 KiB aligned
 
@@ -108,7 +112,7 @@ __device__ __forceinline__ void tmem_st_32x32b_x2(uint32_t taddr, uint32_t r0, u
 }
 
 template <int BM, int BITS>
-__global__ void __launch_bounds__(kThreads, (BM <= 32 ? 4 : 2))
+__global__ void __launch_bounds__(threads24<BM>(), (BM <= 32 ? 4 : 2))
 marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                      const __grid_constant__ CUtensorMap tm_m, const __grid_constant__ CUtensorMap tm_s,
                      const Args24 args) {
@@ -139,10 +143,10 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
     tma_prefetch_desc(&tm_m);
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&full_p[s], 1);
-      mbar_init(&empty_p[s], kWarps + 1);
+      mbar_init(&empty_p[s], dequant_warps24<BM>() + 1);
     }
     for (int s = 0; s < kAStages; ++s) {
-      mbar_init(&full_a[s], kWarps);
+      mbar_init(&full_a[s], dequant_warps24<BM>());
       mbar_init(&empty_a[s], 1);
     }
     mbar_init(tmem_full, 1);
@@ -230,6 +234,8 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
     }
   } else {
     const int qd = warp & 3;  // TMEM quadrant
+    constexpr int kKtPerWarp = 2 / (dequant_warps24<BM>() / 4);  // 32-k halves of a stage per warp
+    const int kt0 = ((warp - 2) >> 2) * kKtPerWarp;
     const int nt = qd >> 1, hb = qd & 1;
     const int c = lane >> 2, r = lane & 3;
     (void)r;
@@ -271,19 +277,20 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
       const uint32_t base = stage0 + stage * P::kStageBytes;
       uint32_t words[2][4], mword[2];
 #pragma unroll
-      for (int kt = 0; kt < 2; ++kt) {
+      for (int kk = 0; kk < kKtPerWarp; ++kk) {  // registers indexed by kk (compile time), addresses by kt
+        const int kt = kt0 + kk;
         if constexpr (BITS == 4) {
           const uint4 w = lds128(base + val_off + kt * 1024);
-          words[kt][0] = w.x >> (8 * hb), words[kt][1] = w.y >> (8 * hb);
-          words[kt][2] = w.z >> (8 * hb), words[kt][3] = w.w >> (8 * hb);
+          words[kk][0] = w.x >> (8 * hb), words[kk][1] = w.y >> (8 * hb);
+          words[kk][2] = w.z >> (8 * hb), words[kk][3] = w.w >> (8 * hb);
         } else {  // word 2 j + b of the lane's eight
           const uint4 w0 = lds128(base + val_off + kt * 1024), w1 = lds128(base + val_off + kt * 1024 + 16);
-          words[kt][0] = hb ? w0.y : w0.x, words[kt][1] = hb ? w0.w : w0.z;
-          words[kt][2] = hb ? w1.y : w1.x, words[kt][3] = hb ? w1.w : w1.z;
+          words[kk][0] = hb ? w0.y : w0.x, words[kk][1] = hb ? w0.w : w0.z;
+          words[kk][2] = hb ? w1.y : w1.x, words[kk][3] = hb ? w1.w : w1.z;
         }
         // [row j = 2 bb': k half 0, k half 1][row j = 2 bb' + 1: k half 0, k half 1], each word = b0 | b1 << 16
         const uint4 mw = lds128(base + meta_off + kt * 512);
-        mword[kt] = __byte_perm(khalf ? mw.y : mw.x, khalf ? mw.w : mw.z, meta_sel);
+        mword[kk] = __byte_perm(khalf ? mw.y : mw.x, khalf ? mw.w : mw.z, meta_sel);
       }
       if (grouped) {
         const int g = (kb * kStageK) >> args.group_shift;
@@ -299,7 +306,8 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
       fence_after_sync();
       const uint32_t t_dst = t_lane + as * kACols;
 #pragma unroll
-      for (int kt = 0; kt < 2; ++kt) {
+      for (int kk = 0; kk < kKtPerWarp; ++kk) {
+        const int kt = kt0 + kk;
 #pragma unroll
         for (int bb = 0; bb < 2; ++bb) {
           uint32_t lo[2], hi[2];  // [row c | row c + 8]: kept pairs of groups r (lo) and r + 4 (hi)
@@ -308,7 +316,7 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
             const int j = 2 * bb + u;
             constexpr uint32_t LO = 0x000f000f, HI = 0x00f000f0, EX = 0x64006400;
             constexpr uint32_t SUB = 0x64086408, MUL = 0x2c002c00, ADD = 0xd480d480;
-            const uint32_t q = words[kt][j];
+            const uint32_t q = words[kk][j];
             // exact q - zp, x scale (one rounding)
             if constexpr (BITS == 4) {
               lo[u] = mul2<__half>(h2_sub(lop3<kAndOr>(q, LO, EX), SUB), sc[j]);
@@ -323,7 +331,13 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
           tmem_st_16x128b_x2(t_dst + ((uint32_t)(16 * bb) << 16) + kt * 8, lo[0], lo[1], hi[0], hi[1]);
         }
       }
-      tmem_st_32x32b_x2(t_lane + kECol + as * 2, mword[0], mword[1]);
+      if constexpr (kKtPerWarp == 2) {
+        tmem_st_32x32b_x2(t_lane + kECol + as * 2, mword[0], mword[1]);
+      } else {  // this warp's k half only: one metadata column
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(t_lane + kECol + as * 2 + kt0),
+                     "r"(mword[0])
+                     : "memory");
+      }
       tmem_st_wait();
       fence_before_sync();
       __syncwarp();
@@ -337,7 +351,7 @@ marlin24_gemm_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_cons
       fence_after_sync();
       const uint32_t taddr = t_lane + kDCol;
 #pragma unroll 1
-      for (int cc = 0; cc < BM / 16; ++cc) {
+      for (int cc = (warp - 2) >> 2; cc < BM / 16; cc += dequant_warps24<BM>() / 4) {  // token chunks interleaved over the quadrant's warps
         if (m0 + cc * 16 >= args.m) break;
         uint32_t rr[16];
         tmem_ld16(taddr + cc * 16, rr);
@@ -434,7 +448,7 @@ int launch24(const b200_gptq_marlin_24_gemm_params& p, cudaStream_t st) {
     set_error("gptq_marlin_24_gemm: cannot reserve %d B of shared memory", (int)P::kBytes);
     return B200_ECUDA;
   }
-  launch_pdl(kern, dim3(m_tiles, n_tiles, splits), dim3(kThreads), P::kBytes, st, tm_x, tm_w, tm_m, tm_s, a);
+  launch_pdl(kern, dim3(m_tiles, n_tiles, splits), dim3(threads24<BM>()), P::kBytes, st, tm_x, tm_w, tm_m, tm_s, a);
   rc = check_launch("gptq_marlin_24_gemm");
   if (rc != B200_OK) return rc;
   if (splits > 1) {
