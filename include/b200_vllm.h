@@ -342,6 +342,8 @@ typedef struct {
 } b200_gptq_marlin_24_gemm_params;
 
 B200_API int b200_gptq_marlin_24_gemm(const b200_gptq_marlin_24_gemm_params* p, void* stream);
+/* bytes of splitk_ws that let b200_gptq_marlin_24_gemm fill the GPU for this shape (0 = none needed) */
+B200_API int64_t b200_gptq_marlin_24_gemm_workspace_bytes(int32_t m, int32_t n, int32_t k);
 
 /* ------------------------------------------------------------------------------------------
  * Decode-side glue between the linears and attention.
