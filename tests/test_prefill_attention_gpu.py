@@ -102,3 +102,27 @@ def test_varlen_attention_rejects(ops):
     k = torch.zeros(4, 2, 128, dtype=torch.half, device=DEV)
     with pytest.raises(RuntimeError):
         ops.flash_attn_varlen_func(q, k, k, cu, cu, 4, 4, 0.1, True)             # 3 heads over 2 kv heads
+
+
+@pytest.mark.parametrize("d", [64, 128])
+def test_varlen_attention_writes_only_its_rows(ops, d):
+    """NaN canaries around the output and past the last token of q / k / v: nothing outside
+    out[0 : total_q] is written, and rows the TMA boxes read past the tensors' ends (zero-filled) never
+    reach a result (lengths that leave partly empty 128-row tiles)."""
+    torch.manual_seed(3)
+    lens = [130, 1, 257]
+    t, h, kvh = sum(lens), 4, 2
+    pad = 300
+    buf = torch.full((pad + t + pad, h, d), float("nan"), dtype=torch.half, device=DEV)
+    out = buf[pad:pad + t]
+    q = torch.randn(t, h, d, dtype=torch.half, device=DEV)
+    k = torch.randn(t, kvh, d, dtype=torch.half, device=DEV)
+    v = torch.randn(t, kvh, d, dtype=torch.half, device=DEV)
+    cu = torch.tensor([0, 130, 131, 388], dtype=torch.int32, device=DEV)
+    ops.flash_attn_varlen_func(q, k, v, cu, cu, max(lens), max(lens), d ** -0.5, True, out)
+    torch.cuda.synchronize()
+    assert torch.isnan(buf[:pad]).all() and torch.isnan(buf[pad + t:]).all()
+    assert not torch.isnan(out).any()
+    from oracle import attention_ref as ar
+    ref = ar.varlen_attention_ref(q.cpu(), k.cpu(), v.cpu(), cu.cpu(), cu.cpu(), d ** -0.5, True)
+    torch.testing.assert_close(out.cpu().float(), ref, rtol=1e-2, atol=1e-3)
