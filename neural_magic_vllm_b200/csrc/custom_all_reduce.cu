@@ -133,7 +133,13 @@ __device__ __forceinline__ void st_volatile16(uint4* p, uint4 v) {
 }
 
 // unit = 8 bytes of payload = one 16-byte line.  Thread-independent: push, poll, sum.
-template <typename T, int W>
+// TWO (two-shot, the reference's second algorithm: custom_all_reduce.cuh:255-300): rank o owns the
+// units [o * units / W, (o + 1) * units / W).  Every rank pushes its input units to their owners,
+// the owner sums them in rank order and pushes the result into every rank's gather area (the upper
+// half of the same per-source receive block), and every rank reads all results from there: 2 (W - 1)
+// / W of the message crosses NVLink per rank instead of W - 1 times the message, for two flag waits
+// instead of one.  Same bits as one-shot (fp32 sum in rank order, rounded once, by one rank).
+template <typename T, int W, bool TWO>
 __global__ void __launch_bounds__(kArThreads) ll_all_reduce_kernel(
     const ArPeers peers, const int rank, const T* in, T* out, const int64_t units, const int active,
     const int64_t ll_off) {
@@ -154,6 +160,61 @@ __global__ void __launch_bounds__(kArThreads) ll_all_reduce_kernel(
   const int64_t par_off = ll_off + (int64_t)(epoch & 1) * kArMaxRanks * kLLSrcBytes;
   const uint2* src = reinterpret_cast<const uint2*>(in);
   const int64_t first = (int64_t)b * kArThreads + tid, step = (int64_t)active * kArThreads;
+  if constexpr (TWO) {
+    const int64_t seg = units / W;  // the host guarantees units % W == 0
+    auto poll = [&](const uint4* slot) {
+      uint4 l = ld_volatile16(slot);
+      uint32_t spins = 0;
+      while (l.y != epoch || l.w != epoch) {
+        if (++spins > (1u << 26)) __trap();
+        l = ld_volatile16(slot);
+      }
+      return make_uint2(l.x, l.z);
+    };
+    // A: my units of every other owner's segment -> that owner
+    for (int64_t i = first; i < units; i += step) {
+      const int o = (int)(i / seg);
+      if (o == rank) continue;
+      const uint2 d = src[i];
+      st_volatile16(reinterpret_cast<uint4*>(peers.base[o] + par_off + (int64_t)rank * kLLSrcBytes) + (i - o * seg),
+                    make_uint4(d.x, epoch, d.y, epoch));
+    }
+    // B: my segment -- sum in rank order, result to every rank's gather area (mine included)
+    for (int64_t li = first; li < seg; li += step) {
+      float acc[N];
+#pragma unroll
+      for (int j = 0; j < N; ++j) acc[j] = 0.f;
+#pragma unroll
+      for (int r = 0; r < W; ++r) {
+        union {
+          uint2 u;
+          T e[N];
+        } v;
+        v.u = r == rank ? src[rank * seg + li]
+                        : poll(reinterpret_cast<const uint4*>(peers.base[rank] + par_off + (int64_t)r * kLLSrcBytes) + li);
+#pragma unroll
+        for (int j = 0; j < N; ++j) acc[j] += DT<T>::to_f(v.e[j]);
+      }
+      union {
+        uint2 u;
+        T e[N];
+      } o;
+#pragma unroll
+      for (int j = 0; j < N; ++j) o.e[j] = DT<T>::from_f(acc[j]);
+      const uint4 line = make_uint4(o.u.x, epoch, o.u.y, epoch);
+#pragma unroll
+      for (int r = 0; r < W; ++r)
+        st_volatile16(reinterpret_cast<uint4*>(peers.base[r] + par_off + (int64_t)rank * kLLSrcBytes + kLLSrcBytes / 2) + li,
+                      line);
+    }
+    // C: all results from the local gather area
+    for (int64_t i = first; i < units; i += step) {
+      const int o = (int)(i / seg);
+      reinterpret_cast<uint2*>(out)[i] = poll(reinterpret_cast<const uint4*>(
+          peers.base[rank] + par_off + (int64_t)o * kLLSrcBytes + kLLSrcBytes / 2) + (i - o * seg));
+    }
+    return;
+  }
   // pass 1: push everything (posted stores: NVLink bandwidth, not round trips, bounds this)
   for (int64_t i = first; i < units; i += step) {
     const uint2 d = src[i];
@@ -200,15 +261,33 @@ __global__ void __launch_bounds__(kArThreads) ll_all_reduce_kernel(
   }
 }
 
+// Two-shot pays once the W - 1 copies of the message that one-shot pulls per rank cost more than a
+// second flag round trip: world >= 4 and >= 128 KiB (measured, profiles/r2c_all_reduce.md).
+// B200_AR_TWO_SHOT = 0 / 1 forces it off / on (tests run it at world 2).
+inline bool use_two_shot(int world, int64_t bytes, bool divisible) {
+  if (!divisible) return false;
+  static const int knob = [] {
+    const char* e = getenv("B200_AR_TWO_SHOT");
+    return e ? atoi(e) : -1;
+  }();
+  if (knob >= 0) return knob != 0;
+  return world >= 4 && bytes >= 128 * 1024;
+}
+
 template <typename T>
 int launch_ll(const ArPeers& peers, int rank, int world, const void* in, void* out, int64_t units,
               int64_t ll_off, cudaStream_t st) {
   int64_t active = (units + kArThreads - 1) / kArThreads;
   active = active < 1 ? 1 : (active > kArGrid ? kArGrid : active);
+  const bool two = use_two_shot(world, units * 8, units % world == 0);
 #define LL_CASE(W)                                                       \
   case W:                                                                \
-    launch_pdl(ll_all_reduce_kernel<T, W>, dim3(kArGrid), dim3(kArThreads), 0, st, peers, rank, \
-               (const T*)in, (T*)out, units, (int)active, ll_off);                             \
+    if (two)                                                             \
+      launch_pdl(ll_all_reduce_kernel<T, W, true>, dim3(kArGrid), dim3(kArThreads), 0, st, peers, rank, \
+                 (const T*)in, (T*)out, units, (int)active, ll_off);                                   \
+    else                                                                 \
+      launch_pdl(ll_all_reduce_kernel<T, W, false>, dim3(kArGrid), dim3(kArThreads), 0, st, peers, rank, \
+                 (const T*)in, (T*)out, units, (int)active, ll_off);                                    \
     break;
   switch (world) {
     LL_CASE(2)
@@ -236,7 +315,7 @@ int launch_ll(const ArPeers& peers, int rank, int world, const void* in, void* o
 // ---------------------------------------------------------------------------------------------
 constexpr int kRowUnits = 8;  // 8-byte units per thread per row: hidden <= 16384 (fp16/bf16)
 
-template <typename T, int W>
+template <typename T, int W, bool TWO>
 __global__ void __launch_bounds__(kArThreads) ll_all_reduce_add_rms_norm_kernel(
     const ArPeers peers, const int rank, T* x, T* residual, const T* __restrict__ weight,
     const float eps, const int tokens, const int hidden, const int64_t ll_off) {
@@ -254,17 +333,76 @@ __global__ void __launch_bounds__(kArThreads) ll_all_reduce_add_rms_norm_kernel(
   if (b >= tokens) return;
   const int64_t par_off = ll_off + (int64_t)(epoch & 1) * kArMaxRanks * kLLSrcBytes;
   const int row_units = hidden / N;
-  // pass 1: push this CTA's rows to every peer
-  for (int t = b; t < tokens; t += gridDim.x) {
-    const uint2* src = reinterpret_cast<const uint2*>(x + (int64_t)t * hidden);
-    for (int u = tid; u < row_units; u += kArThreads) {
-      const uint2 d = src[u];
-      const uint4 line = make_uint4(d.x, epoch, d.y, epoch);
-      const int64_t i = (int64_t)t * row_units + u;
+  // TWO (two-shot): rank o owns the units [o * seg, (o + 1) * seg) of every row (seg = row_units / W,
+  // a multiple of 32: a warp's units have one owner); see ll_all_reduce_kernel
+  const int seg = TWO ? row_units / W : row_units;
+  auto poll = [&](const uint4* slot) {
+    uint4 l = ld_volatile16(slot);
+    uint32_t spins = 0;
+    while (l.y != epoch || l.w != epoch) {
+      if (++spins > (1u << 26)) __trap();
+      l = ld_volatile16(slot);
+    }
+    return make_uint2(l.x, l.z);
+  };
+  if constexpr (TWO) {
+    // A: the units other ranks own -> their owners
+    for (int t = b; t < tokens; t += gridDim.x) {
+      const uint2* src = reinterpret_cast<const uint2*>(x + (int64_t)t * hidden);
+      for (int u = tid; u < row_units; u += kArThreads) {
+        const int o = u / seg;
+        if (o == rank) continue;
+        const uint2 d = src[u];
+        st_volatile16(reinterpret_cast<uint4*>(peers.base[o] + par_off + (int64_t)rank * kLLSrcBytes) +
+                          ((int64_t)t * seg + (u - o * seg)),
+                      make_uint4(d.x, epoch, d.y, epoch));
+      }
+    }
+    // B: the units this rank owns -- sum in rank order, result into every rank's gather area
+    for (int t = b; t < tokens; t += gridDim.x) {
+      const uint2* src = reinterpret_cast<const uint2*>(x + (int64_t)t * hidden);
+      for (int lu = tid; lu < seg; lu += kArThreads) {
+        const int64_t li = (int64_t)t * seg + lu;
+        float acc[N];
 #pragma unroll
-      for (int r = 0; r < W; ++r) {
-        if (r == rank) continue;
-        st_volatile16(reinterpret_cast<uint4*>(peers.base[r] + par_off + (int64_t)rank * kLLSrcBytes) + i, line);
+        for (int j = 0; j < N; ++j) acc[j] = 0.f;
+#pragma unroll
+        for (int r = 0; r < W; ++r) {
+          union {
+            uint2 u2;
+            T e[N];
+          } v;
+          v.u2 = r == rank ? src[rank * seg + lu]
+                           : poll(reinterpret_cast<const uint4*>(peers.base[rank] + par_off + (int64_t)r * kLLSrcBytes) + li);
+#pragma unroll
+          for (int j = 0; j < N; ++j) acc[j] += DT<T>::to_f(v.e[j]);
+        }
+        union {
+          uint2 u2;
+          T e[N];
+        } o;
+#pragma unroll
+        for (int j = 0; j < N; ++j) o.e[j] = DT<T>::from_f(acc[j]);  // the all-reduce's output rounding
+        const uint4 line = make_uint4(o.u2.x, epoch, o.u2.y, epoch);
+#pragma unroll
+        for (int r = 0; r < W; ++r)
+          st_volatile16(reinterpret_cast<uint4*>(peers.base[r] + par_off + (int64_t)rank * kLLSrcBytes + kLLSrcBytes / 2) + li,
+                        line);
+      }
+    }
+  } else {
+    // pass 1: push this CTA's rows to every peer
+    for (int t = b; t < tokens; t += gridDim.x) {
+      const uint2* src = reinterpret_cast<const uint2*>(x + (int64_t)t * hidden);
+      for (int u = tid; u < row_units; u += kArThreads) {
+        const uint2 d = src[u];
+        const uint4 line = make_uint4(d.x, epoch, d.y, epoch);
+        const int64_t i = (int64_t)t * row_units + u;
+#pragma unroll
+        for (int r = 0; r < W; ++r) {
+          if (r == rank) continue;
+          st_volatile16(reinterpret_cast<uint4*>(peers.base[r] + par_off + (int64_t)rank * kLLSrcBytes) + i, line);
+        }
       }
     }
   }
@@ -288,28 +426,30 @@ __global__ void __launch_bounds__(kArThreads) ll_all_reduce_add_rms_norm_kernel(
       if (u < row_units) {
         const int64_t i = (int64_t)t * row_units + u;
         float acc[N];
-#pragma unroll
-        for (int j = 0; j < N; ++j) acc[j] = 0.f;
-#pragma unroll
-        for (int r = 0; r < W; ++r) {
+        if constexpr (TWO) {  // the owner's rounded sum, from the local gather area
+          const int o = u / seg;
           union {
             uint2 u2;
             T e[N];
           } v;
-          if (r == rank) {
-            v.u2 = xrow[u];
-          } else {
-            const uint4* slot = reinterpret_cast<const uint4*>(peers.base[rank] + par_off + (int64_t)r * kLLSrcBytes) + i;
-            uint4 l = ld_volatile16(slot);
-            uint32_t spins = 0;
-            while (l.y != epoch || l.w != epoch) {
-              if (++spins > (1u << 26)) __trap();
-              l = ld_volatile16(slot);
-            }
-            v.u2 = make_uint2(l.x, l.z);
-          }
+          v.u2 = poll(reinterpret_cast<const uint4*>(peers.base[rank] + par_off + (int64_t)o * kLLSrcBytes + kLLSrcBytes / 2) +
+                      ((int64_t)t * seg + (u - o * seg)));
 #pragma unroll
-          for (int j = 0; j < N; ++j) acc[j] += DT<T>::to_f(v.e[j]);
+          for (int j = 0; j < N; ++j) acc[j] = DT<T>::to_f(v.e[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < N; ++j) acc[j] = 0.f;
+#pragma unroll
+          for (int r = 0; r < W; ++r) {
+            union {
+              uint2 u2;
+              T e[N];
+            } v;
+            v.u2 = r == rank ? xrow[u]
+                             : poll(reinterpret_cast<const uint4*>(peers.base[rank] + par_off + (int64_t)r * kLLSrcBytes) + i);
+#pragma unroll
+            for (int j = 0; j < N; ++j) acc[j] += DT<T>::to_f(v.e[j]);
+          }
         }
         union {
           uint2 u2;
@@ -357,10 +497,18 @@ __global__ void __launch_bounds__(kArThreads) ll_all_reduce_add_rms_norm_kernel(
 template <typename T>
 int launch_ll_norm(const ArPeers& peers, int rank, int world, void* x, void* residual, const void* weight,
                    float eps, int tokens, int hidden, int64_t ll_off, cudaStream_t st) {
+  constexpr int N = 8 / (int)sizeof(T);
+  const int row_units = hidden / N;
+  const bool two = use_two_shot(world, (int64_t)tokens * hidden * (int64_t)sizeof(T),
+                                row_units % world == 0 && (row_units / world) % 32 == 0);
 #define LLN_CASE(W)                                                                          \
   case W:                                                                                    \
-    launch_pdl(ll_all_reduce_add_rms_norm_kernel<T, W>, dim3(kArGrid), dim3(kArThreads), 0, st,  \
-               peers, rank, (T*)x, (T*)residual, (const T*)weight, eps, tokens, hidden, ll_off); \
+    if (two)                                                                                 \
+      launch_pdl(ll_all_reduce_add_rms_norm_kernel<T, W, true>, dim3(kArGrid), dim3(kArThreads), 0, st,  \
+                 peers, rank, (T*)x, (T*)residual, (const T*)weight, eps, tokens, hidden, ll_off);      \
+    else                                                                                     \
+      launch_pdl(ll_all_reduce_add_rms_norm_kernel<T, W, false>, dim3(kArGrid), dim3(kArThreads), 0, st, \
+                 peers, rank, (T*)x, (T*)residual, (const T*)weight, eps, tokens, hidden, ll_off);      \
     break;
   switch (world) {
     LLN_CASE(2)
