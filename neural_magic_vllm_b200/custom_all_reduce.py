@@ -73,7 +73,11 @@ class CustomAllreduce:
         # beats NCCL shrinks with the world size (the reference makes the same cut:
         # custom_all_reduce.cu:37-48 -- any size at world 2, < 512 KiB beyond).  Measured on B200
         # (profiles/r1c_all_reduce.md): world 2 wins through 2 MiB, world 4 through 512 KiB-1 MiB.
-        self.one_shot_limit = {2: self.max_size, 4: 1024 * 1024}.get(self.world_size, 512 * 1024)
+        # Round 2: from world 4 up, messages >= 128 KiB take the two-shot flag-in-data path inside the
+        # same kernels (2 (W - 1) / W of the message per rank instead of W - 1 copies), which wins
+        # through the 2 MiB the flag-in-data receive areas hold (world 8: 2 MiB 18.7 us vs NCCL 34.0;
+        # profiles/r2c_all_reduce.md); above that the staged one-shot kernel loses to NCCL.
+        self.one_shot_limit = self.max_size if self.world_size == 2 else 2 * 1024 * 1024
         self.one_shot_limit = min(self.one_shot_limit, self.max_size)
         self._lib = _lib()
         self._own = ctypes.c_void_p()
