@@ -59,3 +59,19 @@ def test_one_shot_all_reduce_two_gpus():
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert '"all_reduce_check": "ok"' in r.stdout
+
+
+@pytest.mark.gpu
+def test_two_shot_all_reduce_two_gpus():
+    """The two-shot path (taken from world 4 up by default) forced at world 2: the same check matrix --
+    bit-identical on every rank, equal to the fp32 rank-order sum rounded once, plain and fused with
+    add + RMSNorm, eager and under graph replay."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run: gpurun --gpus 2 -- python -m pytest tests/test_custom_ar.py -m gpu)")
+    env = dict(os.environ, B200_AR_TWO_SHOT="1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29579",
+                        os.path.join(ROOT, "benchmarks", "ar_check.py")],
+                       capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert '"all_reduce_check": "ok"' in r.stdout
